@@ -1,0 +1,149 @@
+/* pcp.h — C ABI of libpcp_b200.so: the B200-native (sm_100a) per-frame colorization hot path.
+ *
+ * The reference (ChunLI-666/PointCloudProcessor) has no FFI/plugin layer: its boundary is a C++ class API.
+ * Each entry point below names the reference interface it replaces (paths relative to
+ * /root/reference/PointCloudProcessor/).  The C++ facade in include/pcp/*.hpp re-creates those classes on
+ * top of this ABI; INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Conventions: plain pointers and sizes only; every function returns a pcp_status (never throws);
+ * pcp_last_error() gives the message.  All matrices are 4x4 column-major (Eigen's default storage).
+ * One context per GPU; a context is not thread-safe.  There is NO CPU fallback: without a CUDA device
+ * pcp_create fails with PCP_ECUDA.
+ */
+#ifndef PCP_PCP_H_
+#define PCP_PCP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCP_ABI_VERSION 1
+
+typedef enum { PCP_OK = 0, PCP_EINVAL = 1, PCP_EIO = 2, PCP_ECUDA = 3, PCP_ENCCL = 4, PCP_ENOMEM = 5 } pcp_status;
+
+typedef struct pcp_ctx pcp_ctx;
+typedef struct pcp_nid pcp_nid;
+
+/* camera::create_camera("pinhole", intrinsics{fx,fy,cx,cy}, distortion{k1,k2,p1,p2,k3})
+ * include/camera/create_camera.hpp:14, include/camera/pinhole.hpp:12-51 */
+typedef struct {
+  double fx, fy, cx, cy;
+  double dist[5]; /* k1, k2, p1, p2, k3 (plumb_bob order) */
+} pcp_camera;
+
+enum { PCP_ACCUM_SUM = 0, PCP_ACCUM_TOP5 = 1 };
+enum { PCP_SAMPLE_NEAREST = 0, PCP_SAMPLE_BILINEAR = 1 };
+
+/* Every constant the reference hard-codes on this path, lifted into one POD.  pcp_default_params() fills the
+ * reference values. */
+typedef struct {
+  int image_width, image_height;   /* actual image size: bounds of the colour gather (src/PointCloudProcessor.cpp:754) */
+  int cull_width, cull_height;     /* image_size handed to ViewCulling (reference hard-codes 4096x3000, cpp:525) */
+  int downsample;                  /* z-buffer downsample factor, 14 (src/vlcal/calib/view_culling.cpp:63) */
+  double depth_tolerance;          /* 0.05 (view_culling.cpp:157) */
+  int enable_depth_buffer_culling; /* ViewCullingParams (include/vlcal/calib/view_culling.hpp:13) */
+  int accum_mode;                  /* PCP_ACCUM_SUM (u32 sums+count, all-reducible) | PCP_ACCUM_TOP5 (cpp:604-631) */
+  int sample_mode;                 /* PCP_SAMPLE_NEAREST (reference, cpp:752-762) | PCP_SAMPLE_BILINEAR (extension) */
+  int top_m;                       /* 5 (cpp:615) */
+  int prebin;                      /* 1: sort the cloud into spatial blocks at set_cloud and cull blocks per frame */
+  int reserved[7];
+} pcp_params;
+
+/* Optional per-frame outputs (host buffers, caller-owned; any pointer may be NULL). */
+typedef struct {
+  uint32_t* visible_bits; /* ceil(N/32) words; bit i = point i survived ViewCulling::view_culling (view_culling.cpp:52-174) */
+  int32_t* pixel_index;   /* N entries: v*W+u of the sampled pixel (cpp:752-754) or -1 */
+  int64_t n_candidates;   /* points recorded by pass 1 (view_culling.cpp:96) */
+  int64_t n_visible;      /* points kept by pass 2 (view_culling.cpp:167) */
+  int64_t n_colored;      /* points pushed by generateColorMap (cpp:763) */
+} pcp_frame_out;
+
+void pcp_default_params(pcp_params* p);
+int pcp_abi_version(void);
+
+/* PointCloudProcessor::PointCloudProcessor (include/PointCloudProcessor.hpp:17-25): owns the device state. */
+int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_params* params);
+void pcp_destroy(pcp_ctx* ctx);
+const char* pcp_last_error(const pcp_ctx* ctx); /* ctx may be NULL: message of the last failed pcp_create */
+
+/* Use an existing CUDA stream (cudaStream_t) for all work of this context; NULL restores the internal one. */
+int pcp_set_stream(pcp_ctx* ctx, void* cuda_stream);
+void* pcp_get_stream(pcp_ctx* ctx);
+int pcp_synchronize(pcp_ctx* ctx);
+
+/* Pinned host memory for images/clouds, so that submit_frame's copies are asynchronous. */
+int pcp_host_alloc(void** out, size_t bytes);
+int pcp_host_free(void* p);
+
+/* loadPointCloud (cpp:92-154) hands over the map: `n` points, x,y,z floats at byte offsets 0,4,8 of each
+ * `stride_bytes` record and intensity at `intensity_offset` (pcl::PointXYZI: stride 32, intensity at 16).
+ * Copies; converts to float4 SoA on the device; resets the accumulators. */
+int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset);
+/* Same with a device-resident float4 {x,y,z,intensity} array (no host copy). */
+int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n);
+size_t pcp_num_points(const pcp_ctx* ctx);
+
+/* One iteration of the keyframe loop of pcdColorizationAndSmooth (cpp:488-595):
+ * pose7 = {x,y,z,qw,qx,qy,qz} (include/FrameData.hpp:9-12); T_opt16 = T_camera_lidar_optimized or
+ * initTLidarCamera (cpp:504-519), NULL when neither NID nor manual guess is enabled; bgr = the (already
+ * HSV-adjusted, cpp:716-741) 8-bit image, `pitch` bytes per row; mask = 8-bit segmentation image or NULL
+ * (generateSegmentMap, cpp:769-816).  Host buffers; the copy is asynchronous when they are pinned.
+ * Returns after enqueueing unless `out` is given. */
+int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* bgr, size_t pitch,
+                     const uint8_t* mask, size_t mask_pitch, pcp_frame_out* out);
+/* Same with device-resident image/mask (used to time the kernels with inputs already in HBM). */
+int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
+                            const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out);
+
+/* vlcal::ViewCulling::cull(points, T_camera_lidar) (include/vlcal/calib/view_culling.hpp:34, z-buffer variant
+ * view_culling.cpp:52-174) on the context's cloud.  w2c16: optional float pre-transform
+ * (pcl::transformPointCloud, cpp:196/521); T16: optional double T_camera_lidar (view_culling.cpp:37).
+ * idx_out: room for N int32; receives the kept indices in ascending order; *m_out their number. */
+int pcp_cull(pcp_ctx* ctx, const float* w2c16, const double* T16, int32_t* idx_out, size_t* m_out);
+/* Loop body of viewCullingAndSaveFilteredPcds (cpp:178-224): pose -> w2c -> cull. */
+int pcp_cull_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, int32_t* idx_out, size_t* m_out);
+/* Host helper: the float matrices the reference derives from a pose (cpp:495-519). */
+int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[16], float c2w16[16]);
+
+/* Raw accumulators: acc4 = N x {sum_r, sum_g, sum_b, count} u32; mask_hits/mask_max = N u32 (may be NULL). */
+int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint32_t* mask_max);
+/* Device pointer of the N x 4 u32 accumulator array (original point order), e.g. for an external all-reduce. */
+void* pcp_accumulators_device(pcp_ctx* ctx);
+int pcp_reset_accumulators(pcp_ctx* ctx);
+
+/* Multi-GPU: frames are sharded across ranks; one NCCL all-reduce (sum, u32) of the accumulators at the end.
+ * pcp_nccl_unique_id fills 128 bytes on rank 0; every rank then calls pcp_nccl_init with the same bytes. */
+int pcp_nccl_unique_id(uint8_t id128[128]);
+int pcp_nccl_init(pcp_ctx* ctx, const uint8_t id128[128], int rank, int nranks);
+int pcp_allreduce(pcp_ctx* ctx);
+
+/* smoothColors + removePointsWithNoColor inputs (cpp:604-631, hpp:238-252): rgb_out = N x 3 (r,g,b) u8,
+ * count_out = N u32 observations (either may be NULL).  SUM mode: integer mean; TOP5: the reference's top-M
+ * weighted mean. */
+int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out);
+
+/* vlcal::NIDCost (include/vlcal/costs/nid_cost.hpp:24-126).  points: m x {x,y,z,intensity} floats with
+ * `stride_bytes` per record; image: W x H doubles in [0,1] (the CV_64F plane of
+ * visual_camera_calibration.cpp:173), row-major. */
+int pcp_nid_create(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const double* image,
+                   int width, int height, int bins, pcp_nid** out);
+void pcp_nid_destroy(pcp_nid* nid);
+/* NIDCost::operator()<double> for B candidate poses at once.  se3: B x 7 doubles in Sophus order
+ * {qx,qy,qz,qw,tx,ty,tz}; nid_out: B doubles; ok_out: B bytes, 0 where the reference returns false
+ * (non-finite NID, nid_cost.hpp:107-111). */
+int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_t* ok_out);
+/* MultiNIDCost::operator()<double> (src/vlcal/calib/visual_camera_calibration.cpp:93-124): pose gate
+ * (0.2 m / 2 deg from init_se3) then the sum over `n_costs` frames. */
+int pcp_nid_eval_multi(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
+                       uint8_t* ok_out);
+
+/* Counters for benches: kernels launched by this context since creation. */
+uint64_t pcp_launch_count(const pcp_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCP_PCP_H_ */

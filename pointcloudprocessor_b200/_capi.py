@@ -1,0 +1,96 @@
+"""ctypes binding of libpcp_b200.so (include/pcp/pcp.h).  No torch types cross this boundary.
+
+The library is never rebuilt at import time and there is no CPU fallback: a missing library or a missing
+CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpcp_b200.so")
+
+PCP_OK, PCP_EINVAL, PCP_EIO, PCP_ECUDA, PCP_ENCCL, PCP_ENOMEM = range(6)
+ACCUM_SUM, ACCUM_TOP5 = 0, 1
+SAMPLE_NEAREST, SAMPLE_BILINEAR = 0, 1
+
+
+class Camera(C.Structure):
+    _fields_ = [("fx", C.c_double), ("fy", C.c_double), ("cx", C.c_double), ("cy", C.c_double), ("dist", C.c_double * 5)]
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("image_width", C.c_int), ("image_height", C.c_int), ("cull_width", C.c_int), ("cull_height", C.c_int),
+        ("downsample", C.c_int), ("depth_tolerance", C.c_double), ("enable_depth_buffer_culling", C.c_int),
+        ("accum_mode", C.c_int), ("sample_mode", C.c_int), ("top_m", C.c_int), ("prebin", C.c_int), ("reserved", C.c_int * 7),
+    ]
+
+
+class FrameOut(C.Structure):
+    _fields_ = [("visible_bits", C.c_void_p), ("pixel_index", C.c_void_p), ("n_candidates", C.c_int64), ("n_visible", C.c_int64),
+                ("n_colored", C.c_int64)]
+
+
+# every symbol include/pcp/pcp.h declares
+SYMBOLS = [
+    "pcp_default_params", "pcp_abi_version", "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_set_stream", "pcp_get_stream",
+    "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_device", "pcp_num_points",
+    "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
+    "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize",
+    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count",
+]
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(the CUDA library is the only implementation; there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    vp, sz, i32, dbl = C.c_void_p, C.c_size_t, C.c_int, C.c_double
+    L.pcp_default_params.argtypes = [C.POINTER(Params)]
+    L.pcp_default_params.restype = None
+    L.pcp_abi_version.restype = i32
+    L.pcp_create.argtypes = [C.POINTER(vp), i32, C.POINTER(Camera), C.POINTER(Params)]
+    L.pcp_destroy.argtypes = [vp]
+    L.pcp_destroy.restype = None
+    L.pcp_last_error.argtypes = [vp]
+    L.pcp_last_error.restype = C.c_char_p
+    L.pcp_set_stream.argtypes = [vp, vp]
+    L.pcp_get_stream.argtypes = [vp]
+    L.pcp_get_stream.restype = vp
+    L.pcp_synchronize.argtypes = [vp]
+    L.pcp_host_alloc.argtypes = [C.POINTER(vp), sz]
+    L.pcp_host_free.argtypes = [vp]
+    L.pcp_set_cloud.argtypes = [vp, vp, sz, sz, sz]
+    L.pcp_set_cloud_device.argtypes = [vp, vp, sz]
+    L.pcp_num_points.argtypes = [vp]
+    L.pcp_num_points.restype = sz
+    L.pcp_submit_frame.argtypes = [vp, vp, vp, vp, sz, vp, sz, C.POINTER(FrameOut)]
+    L.pcp_submit_frame_device.argtypes = [vp, vp, vp, vp, sz, vp, sz, C.POINTER(FrameOut)]
+    L.pcp_cull.argtypes = [vp, vp, vp, vp, C.POINTER(sz)]
+    L.pcp_cull_pose.argtypes = [vp, vp, vp, vp, C.POINTER(sz)]
+    L.pcp_pose_matrices.argtypes = [vp, vp, vp, vp]
+    L.pcp_get_accumulators.argtypes = [vp, vp, vp, vp]
+    L.pcp_accumulators_device.argtypes = [vp]
+    L.pcp_accumulators_device.restype = vp
+    L.pcp_reset_accumulators.argtypes = [vp]
+    L.pcp_nccl_unique_id.argtypes = [vp]
+    L.pcp_nccl_init.argtypes = [vp, vp, i32, i32]
+    L.pcp_allreduce.argtypes = [vp]
+    L.pcp_finalize.argtypes = [vp, vp, vp]
+    L.pcp_nid_create.argtypes = [vp, vp, sz, sz, sz, vp, i32, i32, i32, C.POINTER(vp)]
+    L.pcp_nid_destroy.argtypes = [vp]
+    L.pcp_nid_destroy.restype = None
+    L.pcp_nid_eval.argtypes = [vp, vp, i32, vp, vp]
+    L.pcp_nid_eval_multi.argtypes = [C.POINTER(vp), i32, vp, vp, i32, vp, vp]
+    L.pcp_launch_count.argtypes = [vp]
+    L.pcp_launch_count.restype = C.c_uint64
+    _lib = L
+    return L

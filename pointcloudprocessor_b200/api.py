@@ -1,0 +1,301 @@
+"""Python harness over the C ABI (numpy in, numpy out).  Names follow the reference's C++ API:
+PointCloudProcessor (include/PointCloudProcessor.hpp), vlcal::ViewCulling (include/vlcal/calib/view_culling.hpp),
+vlcal::NIDCost (include/vlcal/costs/nid_cost.hpp), camera::create_camera (include/camera/create_camera.hpp).
+
+Every call goes through libpcp_b200.so; nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import ACCUM_SUM, ACCUM_TOP5, Camera, FrameOut, Params
+
+
+class PcpError(RuntimeError):
+    pass
+
+
+def create_camera(camera_model: str, intrinsics, distortion_coeffs) -> Camera:
+    """camera::create_camera (src/camera/create_camera.cpp:33-49): only "pinhole" exists; missing distortion
+    coefficients are zero-filled (create_camera.cpp:23-26)."""
+    if camera_model != "pinhole":
+        raise PcpError(f"error: unknown camera model {camera_model}")
+    if len(intrinsics) != 4:
+        raise PcpError("error: num of intrinsic parameters mismatch!!")
+    d = [float(x) for x in list(distortion_coeffs)[:5]]
+    d += [0.0] * (5 - len(d))
+    return Camera(float(intrinsics[0]), float(intrinsics[1]), float(intrinsics[2]), float(intrinsics[3]), (C.c_double * 5)(*d))
+
+
+def default_params(image_size=None, cull_size=None, **kw) -> Params:
+    p = Params()
+    _capi.load().pcp_default_params(C.byref(p))
+    if image_size is not None:
+        p.image_width, p.image_height = int(image_size[0]), int(image_size[1])
+        p.cull_width, p.cull_height = p.image_width, p.image_height
+    if cull_size is not None:
+        p.cull_width, p.cull_height = int(cull_size[0]), int(cull_size[1])
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise PcpError(f"unknown param {k}")
+        setattr(p, k, v)
+    return p
+
+
+def _ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+class Colorizer:
+    """Device-resident state of pcdColorizationAndSmooth (src/PointCloudProcessor.cpp:474-602) on one GPU."""
+
+    def __init__(self, camera: Camera, params: Params, device: int = 0):
+        self._L = _capi.load()
+        self._h = C.c_void_p()
+        rc = self._L.pcp_create(C.byref(self._h), int(device), C.byref(camera), C.byref(params))
+        if rc != _capi.PCP_OK:
+            msg = self._L.pcp_last_error(None)
+            self._h = None
+            raise PcpError(f"pcp_create failed ({rc}): {msg.decode() if msg else ''}")
+        self.params = params
+        self.camera = camera
+        self.n = 0
+        self._keep = []
+
+    # -- lifecycle -------------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pcp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc, what):
+        if rc != _capi.PCP_OK:
+            msg = self._L.pcp_last_error(self._h)
+            raise PcpError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    @property
+    def handle(self):
+        return self._h
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._L.pcp_set_stream(self._h, C.c_void_p(cuda_stream_ptr or 0)), "pcp_set_stream")
+
+    def synchronize(self):
+        self._check(self._L.pcp_synchronize(self._h), "pcp_synchronize")
+
+    def launch_count(self) -> int:
+        return int(self._L.pcp_launch_count(self._h))
+
+    # -- cloud -----------------------------------------------------------------------------------------
+    def set_cloud(self, points: np.ndarray, intensity_offset: int | None = None):
+        """points: (N,4) float32 {x,y,z,intensity} or any (N,k) float32 record array (pcl::PointXYZI: k=8,
+        intensity at float index 4)."""
+        pts = np.ascontiguousarray(points, np.float32)
+        if pts.ndim != 2 or pts.shape[1] < 3:
+            raise PcpError("set_cloud: expected (N,k>=3) float32")
+        stride = pts.shape[1] * 4
+        if intensity_offset is None:
+            intensity_offset = 12 if pts.shape[1] == 4 else (16 if pts.shape[1] >= 5 else 8)
+        self._check(self._L.pcp_set_cloud(self._h, _ptr(pts), pts.shape[0], stride, intensity_offset), "pcp_set_cloud")
+        self.n = pts.shape[0]
+
+    def set_cloud_device(self, dptr: int, n: int):
+        self._check(self._L.pcp_set_cloud_device(self._h, C.c_void_p(dptr), n), "pcp_set_cloud_device")
+        self.n = n
+
+    # -- frames ----------------------------------------------------------------------------------------
+    @staticmethod
+    def _mat16(T):
+        return None if T is None else np.ascontiguousarray(np.asarray(T, np.float64).T.reshape(-1))
+
+    def submit_frame(self, pose7, bgr: np.ndarray, mask: np.ndarray | None = None, T_opt=None, want_vis=False, want_pix=False,
+                     want_counts=False):
+        pose = np.ascontiguousarray(pose7, np.float64)
+        T = self._mat16(T_opt)
+        if bgr.dtype != np.uint8 or bgr.ndim != 3 or bgr.shape[2] != 3 or bgr.strides[2] != 1 or bgr.strides[1] != 3:
+            raise PcpError("submit_frame: bgr must be HxWx3 uint8 with packed pixels")
+        if bgr.shape[0] != self.params.image_height or bgr.shape[1] != self.params.image_width:
+            raise PcpError("submit_frame: image size differs from params")
+        mp = 0
+        if mask is not None:
+            if mask.dtype != np.uint8 or mask.shape != bgr.shape[:2] or mask.strides[1] != 1:
+                raise PcpError("submit_frame: mask must be HxW uint8 of the image size")
+            mp = mask.strides[0]
+        out = None
+        vis = pix = None
+        if want_vis or want_pix or want_counts:
+            out = FrameOut()
+            if want_vis:
+                vis = np.zeros((self.n + 31) // 32, np.uint32)
+                out.visible_bits = vis.ctypes.data
+            if want_pix:
+                pix = np.empty(self.n, np.int32)
+                out.pixel_index = pix.ctypes.data
+        rc = self._L.pcp_submit_frame(self._h, _ptr(pose), _ptr(T), _ptr(bgr), bgr.strides[0], _ptr(mask), mp,
+                                      C.byref(out) if out is not None else None)
+        self._check(rc, "pcp_submit_frame")
+        if out is None:
+            self._keep.append((bgr, mask))  # the copy is asynchronous: keep the host buffers alive until synchronize()
+            if len(self._keep) > 8:
+                self._keep.pop(0)
+            return None
+        res = {"n_candidates": int(out.n_candidates), "n_visible": int(out.n_visible), "n_colored": int(out.n_colored)}
+        if vis is not None:
+            res["vis_bits"] = vis
+            res["vis"] = np.unpackbits(vis.view(np.uint8), bitorder="little")[: self.n]
+        if pix is not None:
+            res["pix"] = pix
+        return res
+
+    def submit_frame_device(self, pose7, d_bgr: int, pitch: int, d_mask: int = 0, mask_pitch: int = 0, T_opt=None):
+        pose = np.ascontiguousarray(pose7, np.float64)
+        T = self._mat16(T_opt)
+        rc = self._L.pcp_submit_frame_device(self._h, _ptr(pose), _ptr(T), C.c_void_p(d_bgr), pitch, C.c_void_p(d_mask or 0), mask_pitch,
+                                             None)
+        self._check(rc, "pcp_submit_frame_device")
+
+    # -- ViewCulling -----------------------------------------------------------------------------------
+    def cull(self, w2c=None, T=None) -> np.ndarray:
+        idx = np.empty(max(self.n, 1), np.int32)
+        m = C.c_size_t(0)
+        w = None if w2c is None else np.ascontiguousarray(np.asarray(w2c, np.float32).T.reshape(-1))
+        rc = self._L.pcp_cull(self._h, _ptr(w), _ptr(self._mat16(T)), _ptr(idx), C.byref(m))
+        self._check(rc, "pcp_cull")
+        return idx[: m.value].copy()
+
+    def cull_pose(self, pose7, T_opt=None) -> np.ndarray:
+        pose = np.ascontiguousarray(pose7, np.float64)
+        idx = np.empty(max(self.n, 1), np.int32)
+        m = C.c_size_t(0)
+        rc = self._L.pcp_cull_pose(self._h, _ptr(pose), _ptr(self._mat16(T_opt)), _ptr(idx), C.byref(m))
+        self._check(rc, "pcp_cull_pose")
+        return idx[: m.value].copy()
+
+    # -- accumulators / finalize -----------------------------------------------------------------------
+    def accumulators(self):
+        acc = np.empty((self.n, 4), np.uint32)
+        mh = np.empty(self.n, np.uint32)
+        mm = np.empty(self.n, np.uint32)
+        self._check(self._L.pcp_get_accumulators(self._h, _ptr(acc), _ptr(mh), _ptr(mm)), "pcp_get_accumulators")
+        return acc, mh, mm
+
+    def accumulators_device(self) -> int:
+        return int(self._L.pcp_accumulators_device(self._h) or 0)
+
+    def reset_accumulators(self):
+        self._check(self._L.pcp_reset_accumulators(self._h), "pcp_reset_accumulators")
+
+    def finalize(self, want_count=True):
+        rgb = np.empty((self.n, 3), np.uint8)
+        cnt = np.empty(self.n, np.uint32) if want_count else None
+        self._check(self._L.pcp_finalize(self._h, _ptr(rgb), _ptr(cnt)), "pcp_finalize")
+        return (rgb, cnt) if want_count else rgb
+
+    # -- multi-GPU -------------------------------------------------------------------------------------
+    def nccl_unique_id(self) -> bytes:
+        buf = (C.c_uint8 * 128)()
+        self._check(self._L.pcp_nccl_unique_id(buf), "pcp_nccl_unique_id")
+        return bytes(buf)
+
+    def nccl_init(self, id128: bytes, rank: int, nranks: int):
+        buf = (C.c_uint8 * 128).from_buffer_copy(id128)
+        self._check(self._L.pcp_nccl_init(self._h, buf, rank, nranks), "pcp_nccl_init")
+
+    def allreduce(self):
+        self._check(self._L.pcp_allreduce(self._h), "pcp_allreduce")
+
+
+def pose_matrices(pose7, T_opt=None):
+    """(w2c, c2w) float32 4x4 as derived at src/PointCloudProcessor.cpp:495-519 (host helper of the library)."""
+    pose = np.ascontiguousarray(pose7, np.float64)
+    T = Colorizer._mat16(T_opt)
+    w = np.zeros(16, np.float32)
+    c = np.zeros(16, np.float32)
+    rc = _capi.load().pcp_pose_matrices(_ptr(pose), _ptr(T), _ptr(w), _ptr(c))
+    if rc != _capi.PCP_OK:
+        raise PcpError("pcp_pose_matrices failed")
+    return w.reshape(4, 4).T.copy(), c.reshape(4, 4).T.copy()
+
+
+class ViewCulling:
+    """vlcal::ViewCulling(proj, image_size, params).cull(points, T_camera_lidar) — z-buffer variant
+    (src/vlcal/calib/view_culling.cpp:52-174).  Returns the culled cloud like the reference (view_culling.cpp:176-185)."""
+
+    def __init__(self, proj: Camera, image_size, enable_depth_buffer_culling: bool = True, device: int = 0):
+        p = default_params(image_size=image_size)
+        p.enable_depth_buffer_culling = int(enable_depth_buffer_culling)
+        self._c = Colorizer(proj, p, device)
+
+    def cull(self, points: np.ndarray, T_camera_lidar=None, return_indices=False):
+        self._c.set_cloud(points)
+        idx = self._c.cull(None, T_camera_lidar)
+        return idx if return_indices else np.ascontiguousarray(points)[idx]
+
+    def close(self):
+        self._c.close()
+
+
+class NIDCost:
+    """vlcal::NIDCost(proj, normalized_image, points, bins) (include/vlcal/costs/nid_cost.hpp:26-40)."""
+
+    def __init__(self, ctx: Colorizer, normalized_image: np.ndarray, points: np.ndarray, bins: int = 16):
+        self._ctx = ctx
+        self._L = ctx._L
+        img = np.ascontiguousarray(normalized_image, np.float64)
+        if img.ndim != 2:
+            raise PcpError("NIDCost: normalized_image must be a single-channel HxW float64 plane")
+        pts = np.ascontiguousarray(points, np.float32)
+        ioff = 12 if pts.shape[1] == 4 else 16
+        self._h = C.c_void_p()
+        rc = self._L.pcp_nid_create(ctx.handle, _ptr(pts), pts.shape[0], pts.shape[1] * 4, ioff, _ptr(img), img.shape[1], img.shape[0],
+                                    int(bins), C.byref(self._h))
+        ctx._check(rc, "pcp_nid_create")
+
+    def __call__(self, se3_params):
+        """NIDCost::operator()<double>: se3 (7,) or (B,7) in Sophus order -> (nid, ok)."""
+        se3 = np.ascontiguousarray(np.atleast_2d(se3_params), np.float64)
+        B = se3.shape[0]
+        out = np.empty(B, np.float64)
+        ok = np.empty(B, np.uint8)
+        self._ctx._check(self._L.pcp_nid_eval(self._h, _ptr(se3), B, _ptr(out), _ptr(ok)), "pcp_nid_eval")
+        return out, ok.astype(bool)
+
+    def close(self):
+        if self._h:
+            self._L.pcp_nid_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def multi_nid(costs, init_se3, se3_params):
+    """MultiNIDCost::operator()<double> (src/vlcal/calib/visual_camera_calibration.cpp:93-124)."""
+    L = _capi.load()
+    se3 = np.ascontiguousarray(np.atleast_2d(se3_params), np.float64)
+    init = np.ascontiguousarray(init_se3, np.float64)
+    B = se3.shape[0]
+    arr = (C.c_void_p * len(costs))(*[c._h for c in costs])
+    out = np.empty(B, np.float64)
+    ok = np.empty(B, np.uint8)
+    rc = L.pcp_nid_eval_multi(arr, len(costs), _ptr(init), _ptr(se3), B, _ptr(out), _ptr(ok))
+    costs[0]._ctx._check(rc, "pcp_nid_eval_multi")
+    return out, ok.astype(bool)

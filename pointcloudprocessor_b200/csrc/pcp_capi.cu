@@ -1,0 +1,247 @@
+// pcp_capi.cu — the C ABI of include/pcp/pcp.h: context lifecycle, cloud ingest, per-frame submission, culling,
+// finalize.  Host code only orchestrates; all arithmetic on points runs in the kernels of pcp_kernels.cu.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/pcp/pcp.h"
+#include "pcp_ctx.hpp"
+
+using namespace pcp;
+
+static thread_local std::string g_create_error;
+
+void pcp_ctx::fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  err = buf;
+}
+
+#define CU(call)                                                                             \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess) {                                                                 \
+      ctx->fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return PCP_ECUDA;                                                                      \
+    }                                                                                        \
+  } while (0)
+
+extern "C" {
+
+void pcp_default_params(pcp_params* p) {
+  if (!p) return;
+  std::memset(p, 0, sizeof(*p));
+  p->image_width = 4096;  // the reference camera (src/PointCloudProcessor.cpp:57-62, :525)
+  p->image_height = 3000;
+  p->cull_width = 4096;
+  p->cull_height = 3000;
+  p->downsample = 14;
+  p->depth_tolerance = 0.05;
+  p->enable_depth_buffer_culling = 1;
+  p->accum_mode = PCP_ACCUM_SUM;
+  p->sample_mode = PCP_SAMPLE_NEAREST;
+  p->top_m = 5;
+  p->prebin = 0;
+}
+
+int pcp_abi_version(void) { return PCP_ABI_VERSION; }
+
+const char* pcp_last_error(const pcp_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_params* params) {
+  if (!out || !cam || !params) { g_create_error = "pcp_create: null argument"; return PCP_EINVAL; }
+  *out = nullptr;
+  if (params->image_width <= 0 || params->image_height <= 0 || params->cull_width <= 0 || params->cull_height <= 0 ||
+      params->downsample <= 0 || params->top_m < 1 || params->top_m > 16 ||
+      (params->accum_mode != PCP_ACCUM_SUM && params->accum_mode != PCP_ACCUM_TOP5) ||
+      (params->sample_mode != PCP_SAMPLE_NEAREST && params->sample_mode != PCP_SAMPLE_BILINEAR)) {
+    g_create_error = "pcp_create: invalid params";
+    return PCP_EINVAL;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("pcp_create: no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e);
+    return PCP_ECUDA;
+  }
+  if (device < 0 || device >= ndev) { g_create_error = "pcp_create: bad device index"; return PCP_EINVAL; }
+  pcp_ctx* ctx = new pcp_ctx();
+  ctx->device = device;
+  ctx->cam = *cam;
+  ctx->prm = *params;
+  ctx->Wc = params->cull_width / params->downsample;   // view_culling.cpp:64 integer division
+  ctx->Hc = params->cull_height / params->downsample;
+  auto bail = [&](const char* what, cudaError_t ce) {
+    g_create_error = std::string("pcp_create: ") + what + ": " + cudaGetErrorString(ce);
+    pcp_destroy(ctx);
+    return PCP_ECUDA;
+  };
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
+  ctx->sm_count = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+  ctx->stream = ctx->own_stream;
+  if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+  for (int i = 0; i < pcp_ctx::kSlots; i++) {
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_free[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+  }
+  const size_t cells = (size_t)ctx->Wc * ctx->Hc;
+  if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
+  if ((e = cudaMalloc(&ctx->d_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+  if ((e = cudaMemset(ctx->d_counters, 0, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMemset", e);
+  if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
+  if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
+  ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
+  ctx->resolve_grid = ctx->sm_count * 4;
+  *out = ctx;
+  return PCP_OK;
+}
+
+void pcp_destroy(pcp_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  nccl_teardown(ctx);
+  ctx->free_cloud();
+  for (int i = 0; i < pcp_ctx::kSlots; i++) {
+    if (ctx->d_img[i]) cudaFree(ctx->d_img[i]);
+    if (ctx->d_mask[i]) cudaFree(ctx->d_mask[i]);
+    if (ctx->ev_copied[i]) cudaEventDestroy(ctx->ev_copied[i]);
+    if (ctx->ev_free[i]) cudaEventDestroy(ctx->ev_free[i]);
+  }
+  if (ctx->d_zgrid) cudaFree(ctx->d_zgrid);
+  if (ctx->d_counters) cudaFree(ctx->d_counters);
+  if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+  if (ctx->d_total) cudaFree(ctx->d_total);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  delete ctx;
+}
+
+int pcp_set_stream(pcp_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  return PCP_OK;
+}
+void* pcp_get_stream(pcp_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int pcp_synchronize(pcp_ctx* ctx) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->copy_stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+int pcp_host_alloc(void** out, size_t bytes) {
+  if (!out) return PCP_EINVAL;
+  return cudaMallocHost(out, bytes ? bytes : 1) == cudaSuccess ? PCP_OK : PCP_ENOMEM;
+}
+int pcp_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? PCP_OK : PCP_ECUDA; }
+
+size_t pcp_num_points(const pcp_ctx* ctx) { return ctx ? ctx->n : 0; }
+uint64_t pcp_launch_count(const pcp_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[16], float c2w16[16]) {
+  if (!pose7 || !w2c16 || !c2w16) return PCP_EINVAL;
+  host::M4f a, b;
+  host::pose_matrices(pose7, T_opt16, a, b);
+  std::memcpy(w2c16, a.a, sizeof(a.a));
+  std::memcpy(c2w16, b.a, sizeof(b.a));
+  return PCP_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// cloud
+// ---------------------------------------------------------------------------------------------------------------------
+void pcp_ctx::free_cloud() {
+  auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
+  F(d_cloud); F(d_perm); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
+  F(d_pix); F(d_idx); F(d_scratch);
+  n = 0;
+}
+
+static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
+  const size_t n1 = n ? n : 1;
+  CU(cudaMalloc(&ctx->d_acc, sizeof(uint4) * n1));
+  CU(cudaMalloc(&ctx->d_records, sizeof(Record) * (n1 + 64)));
+  if (ctx->prm.accum_mode == PCP_ACCUM_TOP5) {
+    CU(cudaMalloc(&ctx->d_top_score, sizeof(float) * n1 * ctx->prm.top_m));
+    CU(cudaMalloc(&ctx->d_top_rgbf, sizeof(uint32_t) * n1 * ctx->prm.top_m));
+    CU(cudaMalloc(&ctx->d_top_frame, sizeof(uint32_t) * n1 * ctx->prm.top_m));
+  }
+  ctx->n = n;
+  return pcp_reset_accumulators(ctx);
+}
+
+extern "C" {
+
+int pcp_reset_accumulators(pcp_ctx* ctx) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  const size_t n1 = ctx->n ? ctx->n : 1;
+  if (ctx->d_acc) CU(cudaMemsetAsync(ctx->d_acc, 0, sizeof(uint4) * n1, ctx->stream));
+  if (ctx->d_mask_acc) CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * n1, ctx->stream));
+  if (ctx->d_top_frame) {
+    CU(cudaMemsetAsync(ctx->d_top_frame, 0xff, sizeof(uint32_t) * n1 * ctx->prm.top_m, ctx->stream));
+    CU(cudaMemsetAsync(ctx->d_top_score, 0, sizeof(float) * n1 * ctx->prm.top_m, ctx->stream));
+    CU(cudaMemsetAsync(ctx->d_top_rgbf, 0, sizeof(uint32_t) * n1 * ctx->prm.top_m, ctx->stream));
+  }
+  ctx->frame_index = 0;
+  return PCP_OK;
+}
+
+int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset) {
+  if (!ctx) return PCP_EINVAL;
+  if ((!points && n) || stride_bytes < 12 || (stride_bytes & 3) || (intensity_offset & 3) || intensity_offset + 4 > stride_bytes ||
+      n >= 0xfffffff0ull) {
+    ctx->fail("pcp_set_cloud: invalid layout (n=%zu stride=%zu intensity_offset=%zu)", n, stride_bytes, intensity_offset);
+    return PCP_EINVAL;
+  }
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->free_cloud();
+  const size_t n1 = n ? n : 1;
+  CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * n1));
+  if (n) {
+    if (stride_bytes == 16 && intensity_offset == 12) {
+      CU(cudaMemcpyAsync(ctx->d_cloud, points, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+      uint8_t* d_aos = nullptr;
+      CU(cudaMalloc(&d_aos, n * stride_bytes));
+      cudaError_t e = cudaMemcpyAsync(d_aos, points, n * stride_bytes, cudaMemcpyHostToDevice, ctx->stream);
+      if (e == cudaSuccess) {
+        launch_aos_to_soa(d_aos, n, stride_bytes, intensity_offset, ctx->d_cloud, ctx->stream);
+        ctx->launches++;
+        e = cudaStreamSynchronize(ctx->stream);
+      }
+      cudaFree(d_aos);
+      if (e != cudaSuccess) { ctx->fail("pcp_set_cloud: upload failed: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+    }
+  }
+  return alloc_cloud_state(ctx, n);
+}
+
+int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n) {
+  if (!ctx || (!d_xyzi && n) || n >= 0xfffffff0ull) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->free_cloud();
+  CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * (n ? n : 1)));
+  if (n) CU(cudaMemcpyAsync(ctx->d_cloud, d_xyzi, sizeof(float4) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+  return alloc_cloud_state(ctx, n);
+}
+
+}  // extern "C"

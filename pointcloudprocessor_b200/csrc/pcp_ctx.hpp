@@ -1,0 +1,62 @@
+// pcp_ctx.hpp — the opaque context behind the C ABI (one per GPU).
+#pragma once
+#include <cstdint>
+#include <string>
+
+#include <cuda_runtime.h>
+
+#include "../../include/pcp/pcp.h"
+#include "pcp_host_math.hpp"
+#include "pcp_internal.cuh"
+
+struct pcp_ctx {
+  static constexpr int kSlots = 3;  // image staging slots: copy of frame f+1 overlaps the kernels of frame f
+
+  int device = 0;
+  int sm_count = 148;
+  pcp_camera cam{};
+  pcp_params prm{};
+  int Wc = 0, Hc = 0;
+
+  cudaStream_t own_stream = nullptr, stream = nullptr, copy_stream = nullptr;
+  cudaEvent_t ev_copied[kSlots] = {}, ev_free[kSlots] = {};
+  uint8_t* d_img[kSlots] = {};
+  uint8_t* d_mask[kSlots] = {};
+  size_t img_bytes = 0, mask_bytes = 0;
+  int slot = 0;
+
+  // cloud + per-point state (HBM layout: see DESIGN.md)
+  size_t n = 0;
+  float4* d_cloud = nullptr;      // N x 16 B  {x,y,z,intensity}
+  uint32_t* d_perm = nullptr;     // N x 4 B   sorted position -> original index (pre-binned mode)
+  uint4* d_acc = nullptr;         // N x 16 B  {sum_r,sum_g,sum_b,count}
+  uint2* d_mask_acc = nullptr;    // N x 8 B   {hits, max}; allocated at the first frame that carries a mask
+  float* d_top_score = nullptr;   // top_m x N
+  uint32_t* d_top_rgbf = nullptr;
+  uint32_t* d_top_frame = nullptr;
+  pcp::Record* d_records = nullptr;  // N x 32 B worst case
+  uint32_t* d_vis_bits = nullptr;    // ceil(N/32) words, lazily allocated
+  int32_t* d_pix = nullptr;          // N, lazily allocated
+  int32_t* d_idx = nullptr;          // N, lazily allocated (pcp_cull)
+  uint32_t* d_scratch = nullptr;     // compaction tile sums
+
+  unsigned long long* d_zgrid = nullptr;
+  pcp::FrameCounters* d_counters = nullptr;
+  pcp::FrameCounters* h_counters = nullptr;  // pinned
+  uint32_t* d_total = nullptr;
+
+  int scan_grid = 148 * 4, resolve_grid = 148 * 4;
+  int frame_index = 0;
+  uint64_t launches = 0;
+  std::string err;
+
+  // NCCL (resolved with dlopen at first use; see pcp_nccl.cpp)
+  void* nccl_comm = nullptr;
+  int nccl_rank = 0, nccl_nranks = 1;
+
+  void fail(const char* fmt, ...);
+  void free_cloud();
+};
+
+int scan_ctas_per_sm();
+void nccl_teardown(pcp_ctx* ctx);

@@ -1,0 +1,250 @@
+// pcp_frames.cu — per-frame submission (the keyframe loop body), ViewCulling::cull drop-in, accumulators, finalize.
+#include <cstring>
+#include <vector>
+
+#include "../../include/pcp/pcp.h"
+#include "pcp_ctx.hpp"
+
+using namespace pcp;
+
+#define CU(call)                                                                             \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess) {                                                                 \
+      ctx->fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return PCP_ECUDA;                                                                      \
+    }                                                                                        \
+  } while (0)
+
+namespace {
+
+void fill_xf(Xf34& x, const float m16[16]) {  // column-major 4x4 -> row-major 3x4
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 4; c++) x.r[r * 4 + c] = m16[c * 4 + r];
+}
+void fill_xd(Xd34& x, const double m16[16]) {
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 4; c++) x.r[r * 4 + c] = m16[c * 4 + r];
+}
+
+FrameParams base_params(const pcp_ctx* ctx) {
+  FrameParams fp;
+  std::memset(&fp, 0, sizeof(fp));
+  const pcp_camera& c = ctx->cam;
+  fp.cam = CamD{c.fx, c.fy, c.cx, c.cy, c.dist[0], c.dist[1], c.dist[2], c.dist[3], c.dist[4]};
+  fp.tol = ctx->prm.depth_tolerance;
+  fp.cullW = ctx->prm.cull_width;
+  fp.cullH = ctx->prm.cull_height;
+  fp.Wc = ctx->Wc;
+  fp.Hc = ctx->Hc;
+  fp.dsf = (float)ctx->prm.downsample;
+  fp.imgW = ctx->prm.image_width;
+  fp.imgH = ctx->prm.image_height;
+  fp.depth_culling = ctx->prm.enable_depth_buffer_culling;
+  return fp;
+}
+
+int ensure_outputs(pcp_ctx* ctx, bool vis, bool pix) {
+  const size_t n1 = ctx->n ? ctx->n : 1;
+  if (vis && !ctx->d_vis_bits) CU(cudaMalloc(&ctx->d_vis_bits, sizeof(uint32_t) * ((n1 + 31) / 32)));
+  if (pix && !ctx->d_pix) CU(cudaMalloc(&ctx->d_pix, sizeof(int32_t) * n1));
+  return PCP_OK;
+}
+
+// Enqueue init + scan + resolve for one frame on ctx->stream.
+int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t pitch, const uint8_t* d_mask, size_t mask_pitch,
+              bool want_vis, bool want_pix, bool accumulate) {
+  if (!ctx->d_cloud) { ctx->fail("no cloud: call pcp_set_cloud first"); return PCP_EINVAL; }
+  int rc = ensure_outputs(ctx, want_vis, want_pix);
+  if (rc != PCP_OK) return rc;
+  if (d_mask && !ctx->d_mask_acc) {
+    CU(cudaMalloc(&ctx->d_mask_acc, sizeof(uint2) * (ctx->n ? ctx->n : 1)));
+    CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * (ctx->n ? ctx->n : 1), ctx->stream));
+  }
+  if (want_vis) CU(cudaMemsetAsync(ctx->d_vis_bits, 0, sizeof(uint32_t) * ((ctx->n + 31) / 32), ctx->stream));
+  if (want_pix) CU(cudaMemsetAsync(ctx->d_pix, 0xff, sizeof(int32_t) * ctx->n, ctx->stream));
+
+  launch_zgrid_init(ctx->d_zgrid, ctx->Wc * ctx->Hc, ctx->d_counters, ctx->stream);
+  ScanArgs sa;
+  std::memset(&sa, 0, sizeof(sa));
+  sa.cloud = ctx->d_cloud;
+  sa.perm = nullptr;
+  sa.active_blocks = nullptr;
+  sa.zgrid = ctx->d_zgrid;
+  sa.records = ctx->d_records;
+  sa.counters = ctx->d_counters;
+  sa.n = (uint32_t)ctx->n;
+  launch_scan(sa, fp, ctx->scan_grid, ctx->stream);
+
+  ResolveArgs ra;
+  std::memset(&ra, 0, sizeof(ra));
+  ra.records = ctx->d_records;
+  ra.zgrid = ctx->d_zgrid;
+  ra.counters = ctx->d_counters;
+  ra.bgr = accumulate ? d_bgr : nullptr;
+  ra.pitch = pitch;
+  ra.mask = accumulate ? d_mask : nullptr;
+  ra.mask_pitch = mask_pitch;
+  ra.acc = ctx->d_acc;
+  ra.mask_acc = ctx->d_mask_acc;
+  ra.top_score = ctx->d_top_score;
+  ra.top_rgbf = ctx->d_top_rgbf;
+  ra.top_frame = ctx->d_top_frame;
+  ra.vis_bits = want_vis ? ctx->d_vis_bits : nullptr;
+  ra.pix_out = want_pix ? ctx->d_pix : nullptr;
+  ra.n = (uint32_t)ctx->n;
+  ra.top_m = ctx->prm.top_m;
+  ra.accum_mode = ctx->prm.accum_mode;
+  ra.sample_mode = ctx->prm.sample_mode;
+  launch_resolve(ra, fp, ctx->resolve_grid, ctx->stream);
+  ctx->launches += 3;
+  CU(cudaGetLastError());
+  return PCP_OK;
+}
+
+int fetch_outputs(pcp_ctx* ctx, pcp_frame_out* out) {
+  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+  if (out->visible_bits) CU(cudaMemcpyAsync(out->visible_bits, ctx->d_vis_bits, sizeof(uint32_t) * ((ctx->n + 31) / 32), cudaMemcpyDeviceToHost, ctx->stream));
+  if (out->pixel_index) CU(cudaMemcpyAsync(out->pixel_index, ctx->d_pix, sizeof(int32_t) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  out->n_candidates = ctx->h_counters->n_candidates;
+  out->n_visible = ctx->h_counters->n_visible;
+  out->n_colored = ctx->h_counters->n_colored;
+  return PCP_OK;
+}
+
+int frame_params_for_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, FrameParams& fp) {
+  if (!pose7) { ctx->fail("null pose"); return PCP_EINVAL; }
+  fp = base_params(ctx);
+  host::M4f w2c, c2w;
+  host::pose_matrices(pose7, T_opt16, w2c, c2w);  // cpp:495-519
+  fill_xf(fp.w2c, w2c.a);
+  fp.use_w2c = 1;
+  fp.use_T = 0;                                   // cull(cloudInCameraPose, Identity)  cpp:527
+  fp.cam_pos[0] = pose7[0]; fp.cam_pos[1] = pose7[1]; fp.cam_pos[2] = pose7[2];  // hpp:208
+  fp.frame_index = ctx->frame_index;
+  return PCP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
+                            const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out) {
+  if (!ctx) return PCP_EINVAL;
+  if (!d_bgr || pitch < (size_t)ctx->prm.image_width * 3 || (d_mask && mask_pitch < (size_t)ctx->prm.image_width)) {
+    ctx->fail("pcp_submit_frame: bad image/pitch");
+    return PCP_EINVAL;
+  }
+  CU(cudaSetDevice(ctx->device));
+  FrameParams fp;
+  int rc = frame_params_for_pose(ctx, pose7, T_opt16, fp);
+  if (rc != PCP_OK) return rc;
+  rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true);
+  if (rc != PCP_OK) return rc;
+  ctx->frame_index++;
+  if (out) return fetch_outputs(ctx, out);
+  return PCP_OK;
+}
+
+int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* bgr, size_t pitch,
+                     const uint8_t* mask, size_t mask_pitch, pcp_frame_out* out) {
+  if (!ctx) return PCP_EINVAL;
+  const size_t W = ctx->prm.image_width, H = ctx->prm.image_height;
+  if (!bgr || pitch < W * 3 || (mask && mask_pitch < W)) { ctx->fail("pcp_submit_frame: bad image/pitch"); return PCP_EINVAL; }
+  CU(cudaSetDevice(ctx->device));
+  const int s = ctx->slot;
+  ctx->slot = (ctx->slot + 1) % pcp_ctx::kSlots;
+  if (!ctx->d_img[s]) CU(cudaMalloc(&ctx->d_img[s], W * 3 * H));
+  if (mask && !ctx->d_mask[s]) CU(cudaMalloc(&ctx->d_mask[s], W * H));
+  // copy stream: wait until the kernels that last read this slot are done, then stage the image
+  CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_free[s], 0));
+  CU(cudaMemcpy2DAsync(ctx->d_img[s], W * 3, bgr, pitch, W * 3, H, cudaMemcpyHostToDevice, ctx->copy_stream));
+  if (mask) CU(cudaMemcpy2DAsync(ctx->d_mask[s], W, mask, mask_pitch, W, H, cudaMemcpyHostToDevice, ctx->copy_stream));
+  CU(cudaEventRecord(ctx->ev_copied[s], ctx->copy_stream));
+  CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[s], 0));
+  const int rc = pcp_submit_frame_device(ctx, pose7, T_opt16, ctx->d_img[s], W * 3, mask ? ctx->d_mask[s] : nullptr, W, out);
+  if (rc != PCP_OK) return rc;
+  CU(cudaEventRecord(ctx->ev_free[s], ctx->stream));
+  return PCP_OK;
+}
+
+static int cull_common(pcp_ctx* ctx, const FrameParams& fp, int32_t* idx_out, size_t* m_out) {
+  if (!idx_out || !m_out) { ctx->fail("pcp_cull: null output"); return PCP_EINVAL; }
+  int rc = run_frame(ctx, fp, nullptr, 0, nullptr, 0, true, false, false);
+  if (rc != PCP_OK) return rc;
+  const size_t n1 = ctx->n ? ctx->n : 1;
+  if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n1));
+  if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)ctx->n)));
+  launch_compact_bits(ctx->d_vis_bits, (uint32_t)ctx->n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
+  ctx->launches += 3;
+  uint32_t total = 0;
+  CU(cudaMemcpyAsync(&total, ctx->d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (total) CU(cudaMemcpyAsync(idx_out, ctx->d_idx, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *m_out = total;
+  return PCP_OK;
+}
+
+int pcp_cull(pcp_ctx* ctx, const float* w2c16, const double* T16, int32_t* idx_out, size_t* m_out) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  FrameParams fp = base_params(ctx);
+  if (w2c16) { fill_xf(fp.w2c, w2c16); fp.use_w2c = 1; }
+  if (T16) { fill_xd(fp.T, T16); fp.use_T = 1; }
+  return cull_common(ctx, fp, idx_out, m_out);
+}
+
+int pcp_cull_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, int32_t* idx_out, size_t* m_out) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  FrameParams fp;
+  const int rc = frame_params_for_pose(ctx, pose7, T_opt16, fp);
+  if (rc != PCP_OK) return rc;
+  return cull_common(ctx, fp, idx_out, m_out);
+}
+
+int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint32_t* mask_max) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  if (acc4) CU(cudaMemcpyAsync(acc4, ctx->d_acc, sizeof(uint4) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (mask_hits || mask_max) {
+    std::vector<uint2> tmp(ctx->n);
+    if (ctx->d_mask_acc) CU(cudaMemcpy(tmp.data(), ctx->d_mask_acc, sizeof(uint2) * ctx->n, cudaMemcpyDeviceToHost));
+    else std::memset(tmp.data(), 0, sizeof(uint2) * ctx->n);
+    for (size_t i = 0; i < ctx->n; i++) {
+      if (mask_hits) mask_hits[i] = tmp[i].x;
+      if (mask_max) mask_max[i] = tmp[i].y;
+    }
+  }
+  return PCP_OK;
+}
+
+void* pcp_accumulators_device(pcp_ctx* ctx) { return ctx ? (void*)ctx->d_acc : nullptr; }
+
+int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  const size_t n = ctx->n;
+  if (n == 0) return PCP_OK;
+  uint8_t* d_rgb = nullptr;
+  uint32_t* d_cnt = nullptr;
+  if (rgb_out) CU(cudaMallocAsync(&d_rgb, n * 3, ctx->stream));
+  if (count_out) CU(cudaMallocAsync(&d_cnt, n * sizeof(uint32_t), ctx->stream));
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, (uint32_t)n, d_rgb, d_cnt, ctx->stream);
+  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
+  ctx->launches++;
+  if (rgb_out) CU(cudaMemcpyAsync(rgb_out, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream));
+  if (count_out) CU(cudaMemcpyAsync(count_out, d_cnt, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  if (d_rgb) CU(cudaFreeAsync(d_rgb, ctx->stream));
+  if (d_cnt) CU(cudaFreeAsync(d_cnt, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return PCP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,90 @@
+// pcp_internal.cuh — device-side data layout and kernel launch prototypes (not part of the ABI).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "pcp_math.cuh"
+
+namespace pcp {
+
+// Initial z-grid key: fl32 FLT_MAX in the high word (view_culling.cpp:64), index 0xffffffff (= -1, :65).
+static constexpr unsigned long long kZInit = (0x7f7fffffull << 32) | 0xffffffffull;
+
+// One candidate that may still be visible after pass 1 (32 bytes, written/read as two 16-byte words).
+struct __align__(16) Record {
+  float x, y, z;      // camera-frame float point (cloudInCameraPose, cpp:521)
+  uint32_t idx;       // original point index
+  double dist;        // ||p|| in double (view_culling.cpp:102)
+  int32_t cell;       // cy*Wc+cx, or -1 when outside the grid (only emitted when depth culling is off)
+  int32_t pix;        // generateColorMap pixel v*W+u or -1 (cpp:752-754)
+};
+static_assert(sizeof(Record) == 32, "Record must be 32 bytes");
+
+// Per-frame device counters (one 64-byte block per frame slot).
+struct FrameCounters {
+  unsigned int n_records;     // records emitted by the scan kernel
+  unsigned int n_candidates;  // gate-passers (view_culling.cpp:96)
+  unsigned int n_visible;     // kept by pass 2 (view_culling.cpp:167)
+  unsigned int n_colored;     // generateColorMap pushes (cpp:763)
+  unsigned int n_active_blocks;
+  unsigned int pad[11];
+};
+
+struct FrameParams {
+  Xf34 w2c;          // float pre-transform (identity when absent)
+  Xd34 T;            // double T_camera_lidar (view_culling.cpp:37)
+  CamD cam;
+  double tol;        // 0.05
+  double cam_pos[3]; // keyframe->pose x,y,z for the orientation score (hpp:208)
+  int use_w2c, use_T;
+  int cullW, cullH;  // image_size given to ViewCulling
+  int Wc, Hc;        // cullW/ds, cullH/ds (integer division, view_culling.cpp:64)
+  float dsf;         // (float)ds
+  int imgW, imgH;    // actual image size
+  int depth_culling;
+  int frame_index;
+};
+
+struct ScanArgs {
+  const float4* __restrict__ cloud;   // N x {x,y,z,intensity}, possibly block-sorted
+  const uint32_t* __restrict__ perm;  // sorted position -> original index (null when not pre-binned)
+  const uint32_t* __restrict__ active_blocks;  // list of block ids to scan (null = all points)
+  unsigned long long* zgrid;          // Wc*Hc packed keys
+  Record* records;
+  FrameCounters* counters;
+  uint32_t n;
+  uint32_t block_points;              // points per spatial block (pre-binned mode)
+};
+
+struct ResolveArgs {
+  const Record* __restrict__ records;
+  const unsigned long long* __restrict__ zgrid;
+  FrameCounters* counters;
+  const uint8_t* __restrict__ bgr; size_t pitch;
+  const uint8_t* __restrict__ mask; size_t mask_pitch;
+  uint4* acc;                 // N x {sum_r,sum_g,sum_b,count}
+  uint2* mask_acc;            // N x {hits(==255), max}
+  float* top_score;           // top_m x N   (TOP5 mode)
+  uint32_t* top_rgbf;         // top_m x N : r | g<<8 | b<<16  (frame index kept in top_frame)
+  uint32_t* top_frame;        // top_m x N
+  uint32_t* vis_bits;         // optional
+  int32_t* pix_out;           // optional
+  uint32_t n;
+  int top_m;
+  int accum_mode;
+  int sample_mode;
+};
+
+void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s);
+void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
+void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
+void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
+void launch_finalize_sum(const uint4* acc, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);
+void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, uint32_t n, int top_m, uint8_t* rgb,
+                         uint32_t* count, cudaStream_t s);
+// ascending index list from a visibility bitmask; returns through d_total the number of set bits
+void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,
+                         uint32_t* d_total, cudaStream_t s);
+size_t compact_scratch_words(uint32_t n);
+
+}  // namespace pcp

@@ -1,0 +1,333 @@
+// pcp_nid.cu — (d) the NID joint-histogram cost of vlcal::NIDCost (include/vlcal/costs/nid_cost.hpp:42-116) for a batch of
+// candidate poses: per-CTA shared-memory bins (one private copy per warp), per-thread aggregation of the 4x4 B-spline
+// taps that fall in the same bin, one flush of each CTA's bins to the per-pose global histogram, then a tiny entropy
+// kernel.  Everything is FP64; no tensor cores (nothing here is a contraction).
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "../../include/pcp/pcp.h"
+#include "pcp_ctx.hpp"
+
+using namespace pcp;
+
+struct pcp_nid {
+  pcp_ctx* ctx = nullptr;
+  size_t m = 0;
+  int W = 0, H = 0, bins = 16;
+  float4* d_pts = nullptr;
+  uint8_t* d_binimg = nullptr;  // per-pixel image bin: min(int(pix*bins), bins-1)  (nid_cost.hpp:88)
+  double* d_se3 = nullptr;      // B x 7
+  double* d_hist = nullptr;     // B x (bins*bins + bins): joint histogram then point-bin counts
+  double* d_out = nullptr;      // B x 2: NID, ok flag
+  int cap_B = 0;
+};
+
+namespace {
+
+constexpr int kNidThreads = 256;
+constexpr int kNidSmemDoubles = 2048;  // 16 KB: 8 private copies of a 16x16 histogram
+
+__global__ void nid_bin_image_kernel(const double* __restrict__ img, size_t npix, int bins, uint8_t* __restrict__ out) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+    const double pb = __dmul_rn(img[i], (double)bins);
+    int b = __double2int_rz(pb);
+    if (!(pb == pb)) b = 0;
+    b = b < bins - 1 ? b : bins - 1;
+    out[i] = (uint8_t)(b < 0 ? 0 : b);
+  }
+}
+
+struct NidArgs {
+  const float4* __restrict__ pts;
+  const uint8_t* __restrict__ binimg;
+  const double* __restrict__ se3;
+  double* hist;
+  uint32_t m;
+  int W, H, bins, copies;
+  CamD cam;
+};
+
+__device__ __forceinline__ void bspline(double s, double b[4]) {
+  // beta = (1/6) * [[1,-3,3,-1],[4,0,-6,3],[1,3,3,-3],[0,0,0,1]] * [1,s,s^2,s^3]^T   (nid_cost.hpp:35-39, :71-77)
+  const double s2 = s * s, s3 = s2 * s;
+  const double k = 1.0 / 6.0;
+  b[0] = ((k + (-3.0 * k) * s) + (3.0 * k) * s2) + (-k) * s3;
+  b[1] = ((4.0 * k) + (-6.0 * k) * s2) + (3.0 * k) * s3;
+  b[2] = ((k + (3.0 * k) * s) + (3.0 * k) * s2) + (-3.0 * k) * s3;
+  b[3] = k * s3;
+}
+
+__global__ void __launch_bounds__(kNidThreads) nid_hist_kernel(const NidArgs a) {
+  __shared__ double sh[kNidSmemDoubles];
+  __shared__ unsigned int sh_pts[8 * 32];
+  const int bins = a.bins, nb2 = bins * bins;
+  const int pose = blockIdx.y;
+  for (int i = threadIdx.x; i < a.copies * nb2; i += blockDim.x) sh[i] = 0.0;
+  for (int i = threadIdx.x; i < 8 * 32; i += blockDim.x) sh_pts[i] = 0u;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5;
+  double* myh = sh + (warp % a.copies) * nb2;
+  unsigned int* myp = sh_pts + warp * 32;
+
+  const double* q = a.se3 + (size_t)pose * 7;
+  const double qx = q[0], qy = q[1], qz = q[2], qw = q[3], tx = q[4], ty = q[5], tz = q[6];
+
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.m; i += gridDim.x * blockDim.x) {
+    const float4 p4 = __ldg(a.pts + i);
+    const double px = p4.x, py = p4.y, pz = p4.z;
+    // Sophus SE3 * p : p + w*uv + qv x uv, uv = 2*(qv x p)   (nid_cost.hpp:55)
+    double ux = qy * pz - qz * py, uy = qz * px - qx * pz, uz = qx * py - qy * px;
+    ux += ux; uy += uy; uz += uz;
+    const double X = (px + qw * ux + (qy * uz - qz * uy)) + tx;
+    const double Y = (py + qw * uy + (qz * ux - qx * uz)) + ty;
+    const double Z = (pz + qw * uz + (qx * uy - qy * ux)) + tz;
+    const double ib = (double)p4.w * (double)bins;                 // :57-58
+    int bin_p;
+    if (!(ib == ib)) bin_p = 0; else if (ib >= (double)(bins - 1)) bin_p = bins - 1; else if (ib <= 0.0) bin_p = 0; else bin_p = (int)ib;
+    double u, v;
+    project(a.cam, X, Y, Z, u, v);                                 // :60 (no z > 0 gate)
+    if (!finite_d(u) || !finite_d(v)) continue;
+    const double fu = floor(u), fv = floor(v);                     // :61
+    if (fu < 0.0 || fv < 0.0 || fu >= (double)a.W || fv >= (double)a.H) continue;  // :64-67
+    const int kx = (int)fu, ky = (int)fv;
+    atomicAdd(&myp[bin_p], 1u);                                    // :69
+    double bx[4], by[4];
+    bspline(u - fu, bx);
+    bspline(v - fv, by);
+    int cur = -1;
+    double acc = 0.0;
+    #pragma unroll
+    for (int ia = 0; ia < 4; ia++) {
+      const int x = min(max(kx - 1 + ia, 0), a.W - 1);             // :79-82
+      #pragma unroll
+      for (int jb = 0; jb < 4; jb++) {
+        const int y = min(max(ky - 1 + jb, 0), a.H - 1);
+        const int bi = __ldg(a.binimg + (size_t)y * a.W + x);      // :87-88
+        const double w = bx[ia] * by[jb];                          // :86
+        if (bi != cur) {
+          if (cur >= 0) atomicAdd(&myh[cur * bins + bin_p], acc);  // :89
+          cur = bi;
+          acc = 0.0;
+        }
+        acc += w;
+      }
+    }
+    if (cur >= 0) atomicAdd(&myh[cur * bins + bin_p], acc);
+  }
+  __syncthreads();
+  double* gh = a.hist + (size_t)pose * (nb2 + bins);
+  for (int i = threadIdx.x; i < nb2; i += blockDim.x) {
+    double s = 0.0;
+    for (int c = 0; c < a.copies; c++) s += sh[c * nb2 + i];
+    if (s != 0.0) atomicAdd(&gh[i], s);
+  }
+  for (int i = threadIdx.x; i < bins; i += blockDim.x) {
+    unsigned int s = 0;
+    for (int w = 0; w < 8; w++) s += sh_pts[w * 32 + i];
+    if (s) atomicAdd(&gh[nb2 + i], (double)s);
+  }
+}
+
+// Entropies and NID (nid_cost.hpp:95-111); one warp per pose.
+__global__ void nid_entropy_kernel(const double* __restrict__ hist, int bins, int B, double* __restrict__ out) {
+  const int pose = blockIdx.x;
+  if (pose >= B) return;
+  const int nb2 = bins * bins;
+  const double* h = hist + (size_t)pose * (nb2 + bins);
+  const int lane = threadIdx.x;
+  double sum = 0.0;
+  for (int i = lane; i < bins; i += 32) sum += h[nb2 + i];
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  double Hi = 0.0, Hp = 0.0, Hj = 0.0;
+  for (int i = lane; i < bins; i += 32) {
+    double hi = 0.0;
+    for (int j = 0; j < bins; j++) hi += h[i * bins + j];        // hist_image[bin_i] = row sum (:90)
+    const double p = hi / sum;
+    Hi += p * log(p + 1e-6);
+    const double pp = h[nb2 + i] / sum;
+    Hp += pp * log(pp + 1e-6);
+  }
+  for (int i = lane; i < nb2; i += 32) {
+    const double p = h[i] / sum;
+    Hj += p * log(p + 1e-6);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    Hi += __shfl_xor_sync(0xffffffffu, Hi, o);
+    Hp += __shfl_xor_sync(0xffffffffu, Hp, o);
+    Hj += __shfl_xor_sync(0xffffffffu, Hj, o);
+  }
+  if (lane == 0) {
+    Hi = -Hi; Hp = -Hp; Hj = -Hj;
+    const double MI = Hi + Hp - Hj;
+    const double nid = (Hj - MI) / Hj;
+    out[2 * pose] = nid;
+    out[2 * pose + 1] = finite_d(nid) ? 1.0 : 0.0;
+  }
+}
+
+#define CUN(call)                                                                                 \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess) {                                                                      \
+      nid->ctx->fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return PCP_ECUDA;                                                                           \
+    }                                                                                             \
+  } while (0)
+
+int ensure_batch(pcp_nid* nid, int B) {
+  if (B <= nid->cap_B) return PCP_OK;
+  if (nid->d_se3) cudaFree(nid->d_se3);
+  if (nid->d_hist) cudaFree(nid->d_hist);
+  if (nid->d_out) cudaFree(nid->d_out);
+  nid->d_se3 = nullptr; nid->d_hist = nullptr; nid->d_out = nullptr; nid->cap_B = 0;
+  const int nb = nid->bins * nid->bins + nid->bins;
+  CUN(cudaMalloc(&nid->d_se3, sizeof(double) * 7 * B));
+  CUN(cudaMalloc(&nid->d_hist, sizeof(double) * nb * B));
+  CUN(cudaMalloc(&nid->d_out, sizeof(double) * 2 * B));
+  nid->cap_B = B;
+  return PCP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pcp_nid_create(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const double* image,
+                   int width, int height, int bins, pcp_nid** out) {
+  if (!ctx || !out) return PCP_EINVAL;
+  *out = nullptr;
+  if ((!points && m) || !image || width <= 0 || height <= 0 || bins < 2 || bins > 32 || stride_bytes < 12 || (stride_bytes & 3) ||
+      (intensity_offset & 3) || intensity_offset + 4 > stride_bytes || m >= 0xfffffff0ull) {
+    ctx->fail("pcp_nid_create: invalid argument");
+    return PCP_EINVAL;
+  }
+  if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->fail("cudaSetDevice failed"); return PCP_ECUDA; }
+  pcp_nid* nid = new pcp_nid();
+  nid->ctx = ctx; nid->m = m; nid->W = width; nid->H = height; nid->bins = bins;
+  cudaStream_t s = ctx->stream;
+  const size_t npix = (size_t)width * height;
+  double* d_img = nullptr;
+  uint8_t* d_aos = nullptr;
+  auto cleanup = [&]() { if (d_img) cudaFree(d_img); if (d_aos) cudaFree(d_aos); };
+  cudaError_t e;
+  if ((e = cudaMalloc(&nid->d_pts, sizeof(float4) * (m ? m : 1))) != cudaSuccess) goto fail;
+  if ((e = cudaMalloc(&nid->d_binimg, npix)) != cudaSuccess) goto fail;
+  if ((e = cudaMalloc(&d_img, npix * sizeof(double))) != cudaSuccess) goto fail;
+  if ((e = cudaMemcpyAsync(d_img, image, npix * sizeof(double), cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
+  nid_bin_image_kernel<<<ctx->sm_count * 8, 256, 0, s>>>(d_img, npix, bins, nid->d_binimg);
+  ctx->launches++;
+  if (m) {
+    if (stride_bytes == 16 && intensity_offset == 12) {
+      if ((e = cudaMemcpyAsync(nid->d_pts, points, sizeof(float4) * m, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
+    } else {
+      if ((e = cudaMalloc(&d_aos, m * stride_bytes)) != cudaSuccess) goto fail;
+      if ((e = cudaMemcpyAsync(d_aos, points, m * stride_bytes, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
+      launch_aos_to_soa(d_aos, m, stride_bytes, intensity_offset, nid->d_pts, s);
+      ctx->launches++;
+    }
+  }
+  if ((e = cudaStreamSynchronize(s)) != cudaSuccess) goto fail;
+  cleanup();
+  *out = nid;
+  return PCP_OK;
+fail:
+  ctx->fail("pcp_nid_create: %s", cudaGetErrorString(e));
+  cleanup();
+  pcp_nid_destroy(nid);
+  return PCP_ECUDA;
+}
+
+void pcp_nid_destroy(pcp_nid* nid) {
+  if (!nid) return;
+  if (nid->ctx) cudaSetDevice(nid->ctx->device);
+  if (nid->d_pts) cudaFree(nid->d_pts);
+  if (nid->d_binimg) cudaFree(nid->d_binimg);
+  if (nid->d_se3) cudaFree(nid->d_se3);
+  if (nid->d_hist) cudaFree(nid->d_hist);
+  if (nid->d_out) cudaFree(nid->d_out);
+  delete nid;
+}
+
+int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_t* ok_out) {
+  if (!nid || !se3 || B <= 0 || !nid_out) return PCP_EINVAL;
+  pcp_ctx* ctx = nid->ctx;
+  CUN(cudaSetDevice(ctx->device));
+  int rc = ensure_batch(nid, B);
+  if (rc != PCP_OK) return rc;
+  cudaStream_t s = ctx->stream;
+  const int nb = nid->bins * nid->bins + nid->bins;
+  CUN(cudaMemcpyAsync(nid->d_se3, se3, sizeof(double) * 7 * B, cudaMemcpyHostToDevice, s));
+  CUN(cudaMemsetAsync(nid->d_hist, 0, sizeof(double) * nb * B, s));
+  NidArgs a;
+  a.pts = nid->d_pts; a.binimg = nid->d_binimg; a.se3 = nid->d_se3; a.hist = nid->d_hist;
+  a.m = (uint32_t)nid->m; a.W = nid->W; a.H = nid->H; a.bins = nid->bins;
+  const int nb2 = nid->bins * nid->bins;
+  a.copies = kNidSmemDoubles / nb2 >= 8 ? 8 : (kNidSmemDoubles / nb2 >= 2 ? 2 : 1);
+  const pcp_camera& c = ctx->cam;
+  a.cam = CamD{c.fx, c.fy, c.cx, c.cy, c.dist[0], c.dist[1], c.dist[2], c.dist[3], c.dist[4]};
+  // enough CTAs per pose to fill the GPU, at least ~2048 points per CTA
+  int per_pose = (int)((nid->m + 2047) / 2048);
+  const int want = (ctx->sm_count * 4 + B - 1) / B;
+  if (per_pose > want) per_pose = want;
+  if (per_pose < 1) per_pose = 1;
+  for (int b0 = 0; b0 < B; b0 += 65535) {
+    const int bn = B - b0 < 65535 ? B - b0 : 65535;
+    NidArgs ab = a;
+    ab.se3 = a.se3 + (size_t)b0 * 7;
+    ab.hist = a.hist + (size_t)b0 * nb;
+    nid_hist_kernel<<<dim3(per_pose, bn), kNidThreads, 0, s>>>(ab);
+    ctx->launches++;
+  }
+  nid_entropy_kernel<<<B, 32, 0, s>>>(nid->d_hist, nid->bins, B, nid->d_out);
+  ctx->launches++;
+  std::vector<double> h(2 * (size_t)B);
+  CUN(cudaMemcpyAsync(h.data(), nid->d_out, sizeof(double) * 2 * B, cudaMemcpyDeviceToHost, s));
+  CUN(cudaStreamSynchronize(s));
+  CUN(cudaGetLastError());
+  for (int b = 0; b < B; b++) {
+    nid_out[b] = h[2 * b];
+    if (ok_out) ok_out[b] = h[2 * b + 1] != 0.0 ? 1 : 0;
+  }
+  return PCP_OK;
+}
+
+// Pose gate of MultiNIDCost (visual_camera_calibration.cpp:99-105): delta = init^-1 * T.
+static bool nid_pose_gate(const double* i7, const double* t7) {
+  const double ax = -i7[0], ay = -i7[1], az = -i7[2], aw = i7[3];  // conjugate of the (unit) init quaternion
+  const double bx = t7[0], by = t7[1], bz = t7[2], bw = t7[3];
+  const double dw = aw * bw - ax * bx - ay * by - az * bz;
+  const double dx = aw * bx + ax * bw + ay * bz - az * by;
+  const double dy = aw * by + ay * bw + az * bx - ax * bz;
+  const double dz = aw * bz + az * bw + ax * by - ay * bx;
+  const double p[3] = {t7[4] - i7[4], t7[5] - i7[5], t7[6] - i7[6]};
+  double uv[3] = {ay * p[2] - az * p[1], az * p[0] - ax * p[2], ax * p[1] - ay * p[0]};
+  for (double& u : uv) u += u;
+  const double rx = p[0] + aw * uv[0] + (ay * uv[2] - az * uv[1]);
+  const double ry = p[1] + aw * uv[1] + (az * uv[0] - ax * uv[2]);
+  const double rz = p[2] + aw * uv[2] + (ax * uv[1] - ay * uv[0]);
+  const double tn = std::sqrt((rx * rx + ry * ry) + rz * rz);
+  const double vn = std::sqrt((dx * dx + dy * dy) + dz * dz);
+  const double angle = 2.0 * std::atan2(vn, std::fabs(dw));
+  return !(tn > 0.2 || angle > 2.0 * M_PI / 180.0);
+}
+
+int pcp_nid_eval_multi(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
+                       uint8_t* ok_out) {
+  if (!costs || n_costs <= 0 || !init_se3 || !se3 || B <= 0 || !sum_out || !ok_out) return PCP_EINVAL;
+  std::vector<double> vals(B);
+  std::vector<uint8_t> oks(B);
+  std::vector<uint8_t> gate(B);
+  for (int b = 0; b < B; b++) { gate[b] = nid_pose_gate(init_se3, se3 + 7 * (size_t)b) ? 1 : 0; sum_out[b] = 0.0; ok_out[b] = gate[b]; }
+  for (int k = 0; k < n_costs; k++) {
+    const int rc = pcp_nid_eval(costs[k], se3, B, vals.data(), oks.data());
+    if (rc != PCP_OK) return rc;
+    for (int b = 0; b < B; b++) {
+      sum_out[b] += vals[b];                       // visual_camera_calibration.cpp:116-119
+      if (!oks[b]) ok_out[b] = 0;                  // :123
+    }
+  }
+  return PCP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,77 @@
+"""CPU-side checks of the boundary: the library loads, exports every symbol include/pcp/pcp.h declares, refuses to run
+without a GPU (no CPU fallback) and its host pose algebra equals the oracle's."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "pcp", "pcp.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(pcp_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported(built_lib):
+    from pointcloudprocessor_b200 import _capi
+    L = C.CDLL(built_lib)
+    decl = _declared_symbols()
+    assert len(decl) >= 25
+    for s in decl:
+        assert hasattr(L, s), f"{s} declared in pcp.h but not exported"
+    assert sorted(_capi.SYMBOLS) == decl
+    assert L.pcp_abi_version() == 1
+
+
+def test_default_params_match_reference(built_lib):
+    from pointcloudprocessor_b200 import api
+    p = api.default_params()
+    assert (p.cull_width, p.cull_height) == (4096, 3000)      # src/PointCloudProcessor.cpp:525
+    assert p.downsample == 14 and p.depth_tolerance == 0.05   # view_culling.cpp:63, :157
+    assert p.top_m == 5 and p.enable_depth_buffer_culling == 1
+
+
+def test_no_cpu_fallback(built_lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from pointcloudprocessor_b200 import api
+    cam = api.create_camera("pinhole", (100, 100, 50, 50), (0, 0, 0, 0, 0))
+    with pytest.raises(api.PcpError, match="no CUDA device"):
+        api.Colorizer(cam, api.default_params(image_size=(64, 48)))
+
+
+def test_create_camera_errors(built_lib):
+    from pointcloudprocessor_b200 import api
+    with pytest.raises(api.PcpError):
+        api.create_camera("fisheye", (1, 1, 0, 0), ())
+    with pytest.raises(api.PcpError):
+        api.create_camera("pinhole", (1, 1, 0), ())
+    cam = api.create_camera("pinhole", (1, 2, 3, 4), (0.1, 0.2))
+    assert list(cam.dist) == [0.1, 0.2, 0.0, 0.0, 0.0]
+
+
+def test_pose_matrices_equal_oracle(built_lib, oracle):
+    from pointcloudprocessor_b200 import api, synth
+    poses, _ = synth.make_poses(50)
+    rng = np.random.default_rng(3)
+    for i, p in enumerate(poses):
+        q = p.copy()
+        if i % 3 == 0:
+            q[3:] *= 1.0 + 1e-3 * rng.normal()  # Eigen does not normalise the quaternion
+        w_g, c_g = api.pose_matrices(q)
+        w_o, c_o = oracle.pose_matrices(q)
+        assert np.array_equal(w_g, w_o) and np.array_equal(c_g, c_o)
+        T = np.eye(4)
+        T[:3, 3] = rng.normal(size=3) * 0.05
+        a = rng.normal() * 0.01
+        T[:3, :3] = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
+        w_g, c_g = api.pose_matrices(q, T)
+        w_o, c_o = oracle.pose_matrices(q, T)
+        assert np.array_equal(w_g, w_o) and np.array_equal(c_g, c_o)
+        # sanity: w2c is the inverse of c2w
+        assert np.abs(w_g.astype(np.float64) @ c_g.astype(np.float64) - np.eye(4)).max() < 1e-4

@@ -1,0 +1,200 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bar: bit-exact visibility masks, pixel indices and integer accumulators; colours equal in SUM mode, <=1/255 in TOP5."""
+import numpy as np
+import pytest
+
+from conftest import make_scene
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_pair(oracle, sc, accum="sum", cull_size=None, T_opt=None, ds=14, tol=0.05, masks=False):
+    from pointcloudprocessor_b200 import api
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    W, H = sc["W"], sc["H"]
+    p = api.default_params(image_size=(W, H), cull_size=cull_size, downsample=ds, depth_tolerance=tol,
+                           accum_mode=api.ACCUM_TOP5 if accum == "top5" else api.ACCUM_SUM)
+    oc = oracle.Colorizer(cam_o, W, H, sc["cloud"], cull_size=cull_size, ds=ds, tol=tol, keep_obs=(accum == "top5"))
+    with api.Colorizer(cam_g, p) as gc:
+        gc.set_cloud(sc["cloud"])
+        for i, pose in enumerate(sc["poses"]):
+            mk = sc["masks"][i] if masks else None
+            ro = oc.frame(pose, sc["images"][i], mask=mk, T_opt=T_opt, want_vis=True, want_pix=True)
+            rg = gc.submit_frame(pose, sc["images"][i], mask=mk, T_opt=T_opt, want_vis=True, want_pix=True)
+            assert rg["n_candidates"] == ro["n_candidates"], f"frame {i} candidates"
+            assert rg["n_visible"] == ro["n_visible"], f"frame {i} visible count"
+            assert rg["n_colored"] == ro["n_colored"], f"frame {i} coloured count"
+            assert np.array_equal(rg["vis"], ro["vis"]), f"frame {i} visibility mask"
+            assert np.array_equal(rg["pix"], ro["pix"]), f"frame {i} pixel indices"
+        acc_g, mh_g, mm_g = gc.accumulators()
+        acc_o, mh_o, mm_o = oc.accumulators()
+        assert np.array_equal(acc_g, acc_o)
+        if masks:
+            assert np.array_equal(mh_g, mh_o) and np.array_equal(mm_g, mm_o)
+        rgb_g, cnt_g = gc.finalize()
+        if accum == "sum":
+            assert np.array_equal(rgb_g, oc.finalize_sum())
+            assert np.array_equal(cnt_g, acc_o[:, 3])
+        else:
+            rgb_o = oc.finalize_top5()
+            assert np.abs(rgb_g.astype(int) - rgb_o.astype(int)).max() <= 1  # tolerance 1/255 per channel
+        assert acc_o[:, 3].sum() > 0
+    return acc_o
+
+
+def test_tiny_sum(oracle, built_lib):
+    _run_pair(oracle, make_scene(20_000, 3, 320, 240))
+
+
+def test_tiny_masks(oracle, built_lib):
+    _run_pair(oracle, make_scene(20_000, 3, 320, 240, masks=True), masks=True)
+
+
+def test_tiny_top5(oracle, built_lib):
+    _run_pair(oracle, make_scene(30_000, 6, 320, 240), accum="top5")
+
+
+def test_c1_shape(oracle, built_lib):
+    _run_pair(oracle, make_scene(1_000_000, 4, 1280, 720))
+
+
+def test_reference_cull_size(oracle, built_lib):
+    # the reference passes a hard-coded 4096x3000 to ViewCulling whatever the image (cpp:525)
+    _run_pair(oracle, make_scene(100_000, 2, 640, 480), cull_size=(4096, 3000))
+
+
+def test_extrinsic_branch(oracle, built_lib):
+    # enableNIDOptimize / manual guess: general float affine inverse (cpp:504-519)
+    T = np.eye(4)
+    a = np.deg2rad(0.7)
+    T[:3, :3] = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
+    T[:3, 3] = (0.03, -0.02, 0.05)
+    _run_pair(oracle, make_scene(50_000, 3, 320, 240), T_opt=T)
+
+
+def test_ragged_and_empty(oracle, built_lib):
+    from pointcloudprocessor_b200 import api
+    for n in (0, 1, 31, 33, 257):
+        sc = make_scene(max(n, 1), 2, 320, 240)
+        sc["cloud"] = sc["cloud"][:n]
+        cam_o = oracle.camera(sc["intr"], sc["dist"])
+        cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+        oc = oracle.Colorizer(cam_o, 320, 240, sc["cloud"].reshape(-1, 4))
+        with api.Colorizer(cam_g, api.default_params(image_size=(320, 240))) as gc:
+            gc.set_cloud(sc["cloud"].reshape(-1, 4))
+            for i in range(2):
+                ro = oc.frame(sc["poses"][i], sc["images"][i], want_vis=True, want_pix=True)
+                rg = gc.submit_frame(sc["poses"][i], sc["images"][i], want_vis=True, want_pix=True)
+                assert np.array_equal(rg["vis"], ro["vis"]) and np.array_equal(rg["pix"], ro["pix"])
+            assert np.array_equal(gc.accumulators()[0], oc.accumulators()[0])
+
+
+def test_edge_points(oracle, built_lib):
+    """z == 0, points behind the camera, coincident points, exact depth ties, non-finite coordinates, negative-u
+    truncation into cell 0, border cells."""
+    from pointcloudprocessor_b200 import api
+    W, H = 320, 240
+    sc = make_scene(5000, 1, W, H)
+    rng = np.random.default_rng(7)
+    pose = np.array([0, 0, 0, 1, 0, 0, 0], np.float64)  # identity: cloud coordinates are camera coordinates
+    intr = sc["intr"]
+    pts = []
+    # dense fan in front of the camera, including just outside each image border
+    u = rng.uniform(-30, W + 30, 4000)
+    v = rng.uniform(-30, H + 30, 4000)
+    z = rng.uniform(0.5, 6.0, 4000)
+    pts.append(np.stack([(u - intr[2]) / intr[0] * z, (v - intr[3]) / intr[1] * z, z], 1))
+    pts.append(np.array([[0, 0, 0], [1, 1, 0], [0.1, 0.1, -1], [0, 0, 1], [0, 0, 1], [0, 0, 1.00000012], [np.nan, 0, 1], [0, np.inf, 1],
+                         [0, 0, np.inf], [1e30, 1e30, 1e-30], [-1e-3, 0, 1e-38], [3e38, 3e38, 3e38]], np.float64))
+    # exact ties: same direction and distance, different indices
+    pts.append(np.tile(np.array([[0.2, 0.1, 2.0]]), (5, 1)))
+    xyz = np.concatenate(pts).astype(np.float32)
+    cloud = np.concatenate([xyz, rng.random((xyz.shape[0], 1), dtype=np.float32)], 1)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    oc = oracle.Colorizer(cam_o, W, H, cloud)
+    with api.Colorizer(cam_g, api.default_params(image_size=(W, H))) as gc:
+        gc.set_cloud(cloud)
+        ro = oc.frame(pose, sc["images"][0], want_vis=True, want_pix=True)
+        rg = gc.submit_frame(pose, sc["images"][0], want_vis=True, want_pix=True)
+        assert ro["n_visible"] > 100
+        assert rg["n_candidates"] == ro["n_candidates"]
+        assert np.array_equal(rg["vis"], ro["vis"]) and np.array_equal(rg["pix"], ro["pix"])
+        assert np.array_equal(gc.accumulators()[0], oc.accumulators()[0])
+
+
+def test_cull_dropin(oracle, built_lib):
+    """vlcal::ViewCulling::cull: ascending index list, with a double T_camera_lidar and without depth culling."""
+    from pointcloudprocessor_b200 import api
+    sc = make_scene(60_000, 2, 640, 480)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    w2c, _ = oracle.pose_matrices(sc["poses"][1])
+    pts_cam = oracle.transform(sc["cloud"], w2c)
+    cloud_cam = np.concatenate([pts_cam, sc["cloud"][:, 3:]], 1)
+    T = np.eye(4)
+    T[:3, 3] = (0.01, 0.02, -0.03)
+    b = np.deg2rad(1.0)
+    T[:3, :3] = np.array([[1, 0, 0], [0, np.cos(b), -np.sin(b)], [0, np.sin(b), np.cos(b)]])
+    for depth in (True, False):
+        for Tm in (None, T):
+            ref = oracle.view_culling(cam_o, 640, 480, pts_cam, T=Tm, depth_culling=depth)
+            vc = api.ViewCulling(cam_g, (640, 480), enable_depth_buffer_culling=depth)
+            got = vc.cull(cloud_cam, Tm, return_indices=True)
+            vc.close()
+            assert np.array_equal(got, ref), (depth, Tm is not None)
+    # pose variant (loop body of viewCullingAndSaveFilteredPcds)
+    with api.Colorizer(cam_g, api.default_params(image_size=(640, 480))) as gc:
+        gc.set_cloud(sc["cloud"])
+        got = gc.cull_pose(sc["poses"][1])
+        assert np.array_equal(got, oracle.view_culling(cam_o, 640, 480, pts_cam))
+
+
+def test_pcl_record_layout(oracle, built_lib):
+    """pcl::PointXYZI records: 32 bytes, intensity at byte 16."""
+    from pointcloudprocessor_b200 import api
+    sc = make_scene(10_000, 1, 320, 240)
+    rec = np.zeros((10_000, 8), np.float32)
+    rec[:, :3] = sc["cloud"][:, :3]
+    rec[:, 3] = 1.0
+    rec[:, 4] = sc["cloud"][:, 3]
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    oc = oracle.Colorizer(cam_o, 320, 240, sc["cloud"])
+    with api.Colorizer(cam_g, api.default_params(image_size=(320, 240))) as gc:
+        gc.set_cloud(rec)
+        ro = oc.frame(sc["poses"][0], sc["images"][0], want_vis=True)
+        rg = gc.submit_frame(sc["poses"][0], sc["images"][0], want_vis=True)
+        assert np.array_equal(rg["vis"], ro["vis"])
+
+
+def test_nid(oracle, built_lib):
+    """NID within 1e-5 relative of the oracle's doubles (north_star tolerance)."""
+    from pointcloudprocessor_b200 import api, synth
+    W, H = 640, 480
+    sc = make_scene(200_000, 1, W, H)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    w2c, _ = oracle.pose_matrices(sc["poses"][0])
+    pts_cam = oracle.transform(sc["cloud"], w2c)
+    keep = oracle.view_culling(cam_o, W, H, pts_cam)
+    culled = np.concatenate([pts_cam[keep], sc["cloud"][keep, 3:]], 1)
+    grey = synth.grey_plane(sc["images"][0])
+    cands = synth.make_nid_candidates(16)
+    with api.Colorizer(cam_g, api.default_params(image_size=(W, H))) as gc:
+        cost = api.NIDCost(gc, grey, culled, 16)
+        got, ok = cost(cands)
+        for b in range(cands.shape[0]):
+            ref, rok = oracle.nid(cam_o, grey, culled, cands[b])
+            assert ok[b] == rok
+            assert abs(got[b] - ref) <= 1e-5 * abs(ref), (b, got[b], ref)
+        # MultiNIDCost: gate + sum
+        far = cands[1].copy()
+        far[4] += 0.5
+        s, okm = api.multi_nid([cost, cost], cands[0], np.stack([cands[2], far]))
+        r2, _ = oracle.nid(cam_o, grey, culled, cands[2])
+        assert okm[0] and not okm[1]
+        assert abs(s[0] - 2 * r2) <= 2e-5 * abs(r2)
+        assert oracle.nid_gate(cands[0], cands[2]) and not oracle.nid_gate(cands[0], far)
+        cost.close()
