@@ -125,6 +125,15 @@ int pcp_allreduce(pcp_ctx* ctx);
  * weighted mean. */
 int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out);
 
+/* Same as pcp_finalize with device-resident outputs (no host copy; asynchronous on the context's stream). */
+int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out);
+
+/* Per-kernel device timing (CUDA events on the context's stream around the scan and resolve kernels of every frame
+ * submitted while enabled).  pcp_profile_read synchronises and returns the accumulated milliseconds
+ * {zgrid init, scan, resolve} and the number of frames, then resets the accumulation. */
+int pcp_profile_enable(pcp_ctx* ctx, int on);
+int pcp_profile_read(pcp_ctx* ctx, double ms3[3], uint64_t* frames);
+
 /* vlcal::NIDCost (include/vlcal/costs/nid_cost.hpp:24-126).  points: m x {x,y,z,intensity} floats with
  * `stride_bytes` per record; image: W x H doubles in [0,1] (the CV_64F plane of
  * visual_camera_calibration.cpp:173), row-major. */

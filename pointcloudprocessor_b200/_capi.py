@@ -38,7 +38,7 @@ SYMBOLS = [
     "pcp_default_params", "pcp_abi_version", "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_set_stream", "pcp_get_stream",
     "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_device", "pcp_num_points",
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
-    "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize",
+    "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count",
 ]
 
@@ -85,6 +85,9 @@ def load():
     L.pcp_nccl_init.argtypes = [vp, vp, i32, i32]
     L.pcp_allreduce.argtypes = [vp]
     L.pcp_finalize.argtypes = [vp, vp, vp]
+    L.pcp_finalize_device.argtypes = [vp, vp, vp]
+    L.pcp_profile_enable.argtypes = [vp, i32]
+    L.pcp_profile_read.argtypes = [vp, vp, vp]
     L.pcp_nid_create.argtypes = [vp, vp, sz, sz, sz, vp, i32, i32, i32, C.POINTER(vp)]
     L.pcp_nid_destroy.argtypes = [vp]
     L.pcp_nid_destroy.restype = None

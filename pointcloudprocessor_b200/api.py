@@ -162,12 +162,31 @@ class Colorizer:
             res["pix"] = pix
         return res
 
-    def submit_frame_device(self, pose7, d_bgr: int, pitch: int, d_mask: int = 0, mask_pitch: int = 0, T_opt=None):
+    def submit_frame_device(self, pose7, d_bgr: int, pitch: int, d_mask: int = 0, mask_pitch: int = 0, T_opt=None, want_counts=False):
         pose = np.ascontiguousarray(pose7, np.float64)
         T = self._mat16(T_opt)
+        out = FrameOut() if want_counts else None
         rc = self._L.pcp_submit_frame_device(self._h, _ptr(pose), _ptr(T), C.c_void_p(d_bgr), pitch, C.c_void_p(d_mask or 0), mask_pitch,
-                                             None)
+                                             C.byref(out) if out is not None else None)
         self._check(rc, "pcp_submit_frame_device")
+        if out is not None:
+            return {"n_candidates": int(out.n_candidates), "n_visible": int(out.n_visible), "n_colored": int(out.n_colored)}
+        return None
+
+    def set_cloud_ptr(self, host_ptr: int, n: int, stride: int = 16, intensity_offset: int = 12):
+        """set_cloud from a raw (e.g. pinned) host pointer."""
+        self._check(self._L.pcp_set_cloud(self._h, C.c_void_p(host_ptr), n, stride, intensity_offset), "pcp_set_cloud")
+        self.n = n
+
+    def submit_frame_ptr(self, pose7, bgr_ptr: int, pitch: int, mask_ptr: int = 0, mask_pitch: int = 0, T_opt=None):
+        """submit_frame from raw (e.g. pinned) host pointers; asynchronous."""
+        pose = np.ascontiguousarray(pose7, np.float64)
+        T = self._mat16(T_opt)
+        rc = self._L.pcp_submit_frame(self._h, _ptr(pose), _ptr(T), C.c_void_p(bgr_ptr), pitch, C.c_void_p(mask_ptr or 0), mask_pitch, None)
+        self._check(rc, "pcp_submit_frame")
+
+    def finalize_ptr(self, rgb_ptr: int, count_ptr: int = 0):
+        self._check(self._L.pcp_finalize(self._h, C.c_void_p(rgb_ptr or 0), C.c_void_p(count_ptr or 0)), "pcp_finalize")
 
     # -- ViewCulling -----------------------------------------------------------------------------------
     def cull(self, w2c=None, T=None) -> np.ndarray:
@@ -205,6 +224,18 @@ class Colorizer:
         cnt = np.empty(self.n, np.uint32) if want_count else None
         self._check(self._L.pcp_finalize(self._h, _ptr(rgb), _ptr(cnt)), "pcp_finalize")
         return (rgb, cnt) if want_count else rgb
+
+    def finalize_device(self, d_rgb: int, d_count: int = 0):
+        self._check(self._L.pcp_finalize_device(self._h, C.c_void_p(d_rgb or 0), C.c_void_p(d_count or 0)), "pcp_finalize_device")
+
+    def profile_enable(self, on: bool = True):
+        self._check(self._L.pcp_profile_enable(self._h, int(on)), "pcp_profile_enable")
+
+    def profile_read(self):
+        ms = (C.c_double * 3)()
+        fr = C.c_uint64(0)
+        self._check(self._L.pcp_profile_read(self._h, ms, C.byref(fr)), "pcp_profile_read")
+        return {"init_ms": ms[0], "scan_ms": ms[1], "resolve_ms": ms[2], "frames": int(fr.value)}
 
     # -- multi-GPU -------------------------------------------------------------------------------------
     def nccl_unique_id(self) -> bytes:
@@ -299,3 +330,22 @@ def multi_nid(costs, init_se3, se3_params):
     rc = L.pcp_nid_eval_multi(arr, len(costs), _ptr(init), _ptr(se3), B, _ptr(out), _ptr(ok))
     costs[0]._ctx._check(rc, "pcp_nid_eval_multi")
     return out, ok.astype(bool)
+
+
+def host_alloc(nbytes: int) -> int:
+    """Pinned host memory (pcp_host_alloc); returns the address."""
+    p = C.c_void_p()
+    if _capi.load().pcp_host_alloc(C.byref(p), nbytes) != _capi.PCP_OK:
+        raise PcpError("pcp_host_alloc failed")
+    return int(p.value)
+
+
+def host_free(ptr: int):
+    _capi.load().pcp_host_free(C.c_void_p(ptr))
+
+
+def host_array(ptr: int, shape, dtype):
+    """numpy view of a raw host allocation."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    buf = (C.c_uint8 * n).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype).reshape(shape)

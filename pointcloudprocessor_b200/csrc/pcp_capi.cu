@@ -121,6 +121,7 @@ void pcp_destroy(pcp_ctx* ctx) {
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   if (ctx->d_total) cudaFree(ctx->d_total);
+  for (cudaEvent_t e : ctx->prof_events) if (e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   delete ctx;
@@ -211,10 +212,13 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
     return PCP_EINVAL;
   }
   CU(cudaSetDevice(ctx->device));
-  CU(cudaStreamSynchronize(ctx->stream));
-  ctx->free_cloud();
+  const bool reuse = ctx->d_cloud && ctx->n == n && n > 0;  // same-size cloud: keep every allocation, only re-upload
   const size_t n1 = n ? n : 1;
-  CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * n1));
+  if (!reuse) {
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->free_cloud();
+    CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * n1));
+  }
   if (n) {
     if (stride_bytes == 16 && intensity_offset == 12) {
       CU(cudaMemcpyAsync(ctx->d_cloud, points, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
@@ -231,6 +235,7 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
       if (e != cudaSuccess) { ctx->fail("pcp_set_cloud: upload failed: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
     }
   }
+  if (reuse) return pcp_reset_accumulators(ctx);
   return alloc_cloud_state(ctx, n);
 }
 

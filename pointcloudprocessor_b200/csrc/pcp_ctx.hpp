@@ -2,6 +2,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include <cuda_runtime.h>
 
@@ -49,6 +50,11 @@ struct pcp_ctx {
   int frame_index = 0;
   uint64_t launches = 0;
   std::string err;
+
+  // optional per-kernel timing
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_events;  // 4 per frame
+  size_t prof_used = 0;
 
   // NCCL (resolved with dlopen at first use; see pcp_nccl.cpp)
   void* nccl_comm = nullptr;

@@ -64,7 +64,19 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   if (want_vis) CU(cudaMemsetAsync(ctx->d_vis_bits, 0, sizeof(uint32_t) * ((ctx->n + 31) / 32), ctx->stream));
   if (want_pix) CU(cudaMemsetAsync(ctx->d_pix, 0xff, sizeof(int32_t) * ctx->n, ctx->stream));
 
+  cudaEvent_t* pe = nullptr;
+  if (ctx->profiling) {
+    if (ctx->prof_used + 4 > ctx->prof_events.size()) {
+      const size_t old_n = ctx->prof_events.size();
+      ctx->prof_events.resize(old_n + 1024, nullptr);
+      for (size_t i = old_n; i < ctx->prof_events.size(); i++) CU(cudaEventCreate(&ctx->prof_events[i]));
+    }
+    pe = &ctx->prof_events[ctx->prof_used];
+    ctx->prof_used += 4;
+    CU(cudaEventRecord(pe[0], ctx->stream));
+  }
   launch_zgrid_init(ctx->d_zgrid, ctx->Wc * ctx->Hc, ctx->d_counters, ctx->stream);
+  if (pe) CU(cudaEventRecord(pe[1], ctx->stream));
   ScanArgs sa;
   std::memset(&sa, 0, sizeof(sa));
   sa.cloud = ctx->d_cloud;
@@ -75,6 +87,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.counters = ctx->d_counters;
   sa.n = (uint32_t)ctx->n;
   launch_scan(sa, fp, ctx->scan_grid, ctx->stream);
+  if (pe) CU(cudaEventRecord(pe[2], ctx->stream));
 
   ResolveArgs ra;
   std::memset(&ra, 0, sizeof(ra));
@@ -97,6 +110,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ra.accum_mode = ctx->prm.accum_mode;
   ra.sample_mode = ctx->prm.sample_mode;
   launch_resolve(ra, fp, ctx->resolve_grid, ctx->stream);
+  if (pe) CU(cudaEventRecord(pe[3], ctx->stream));
   ctx->launches += 3;
   CU(cudaGetLastError());
   return PCP_OK;
@@ -225,6 +239,41 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
 }
 
 void* pcp_accumulators_device(pcp_ctx* ctx) { return ctx ? (void*)ctx->d_acc : nullptr; }
+
+int pcp_profile_enable(pcp_ctx* ctx, int on) {
+  if (!ctx) return PCP_EINVAL;
+  ctx->profiling = on != 0;
+  return PCP_OK;
+}
+
+int pcp_profile_read(pcp_ctx* ctx, double ms3[3], uint64_t* frames) {
+  if (!ctx || !ms3) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ms3[0] = ms3[1] = ms3[2] = 0.0;
+  for (size_t i = 0; i + 4 <= ctx->prof_used; i += 4) {
+    for (int k = 0; k < 3; k++) {
+      float ms = 0.f;
+      CU(cudaEventElapsedTime(&ms, ctx->prof_events[i + k], ctx->prof_events[i + k + 1]));
+      ms3[k] += ms;
+    }
+  }
+  if (frames) *frames = ctx->prof_used / 4;
+  ctx->prof_used = 0;
+  return PCP_OK;
+}
+
+int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  if (ctx->n == 0) return PCP_OK;
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->stream);
+  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
+  ctx->launches++;
+  CU(cudaGetLastError());
+  return PCP_OK;
+}
 
 int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
   if (!ctx) return PCP_EINVAL;
