@@ -9,7 +9,7 @@ The same bytes go to the CUDA path, the CPU oracle and the bench.  No file IO, n
            jitter, unit quaternions, pose = (x y z qw qx qy qz) as in the odometry file (cpp:973-978), seed 43
   camera : fx = fy = 1.1763 W, cx = 0.4962 W, cy = 0.5117 H (the reference's 4818/4096 FoV ratio) with the
            reference's plumb_bob coefficients (cpp:57-60)
-  images : u8 BGR band-limited noise (8 seeded sinusoids + U[0,8) noise), seed 44+i, passed once through the
+  images : u8 BGR, 8 seeded integer triangle waves per channel + U[0,8) noise, seed 44+i, passed once through the
            reference's 8-bit BGR->HSV->BGR round trip (cpp:723-741) with cv2 when available
   masks  : u8, ~2 % of pixels == 255 in blobs
 """
@@ -190,21 +190,43 @@ def hsv_round_trip(bgr: np.ndarray) -> np.ndarray:
     return cv2.cvtColor(hsv, cv2.COLOR_HSV2BGR)
 
 
-def make_image(i: int, W: int, H: int, out: np.ndarray | None = None, hsv: bool = True) -> np.ndarray:
-    """H x W x 3 u8 BGR."""
-    rng = np.random.default_rng(44 + i)
-    yy = np.arange(H, dtype=np.float32)[:, None]
-    xx = np.arange(W, dtype=np.float32)[None, :]
-    img = np.empty((H, W, 3), np.float32)
+_BASE_CACHE: dict = {}
+
+
+def _base_pattern(k: int, W: int, H: int) -> np.ndarray:
+    """H x W x 3 int16 pattern: 120 + sum of 8 integer triangle waves per channel along seeded directions.
+    Integer arithmetic only, so the bytes are identical on every machine (no libm / BLAS in the generator)."""
+    key = (k, W, H)
+    if key in _BASE_CACHE:
+        return _BASE_CACHE[key]
+    rng = np.random.default_rng(4400 + k)
+    yy = np.arange(H, dtype=np.int32)[:, None]
+    xx = np.arange(W, dtype=np.int32)[None, :]
+    img = np.empty((H, W, 3), np.int16)
     for c in range(3):
-        acc = np.full((H, W), 120.0, np.float32)
+        acc = np.full((H, W), 120, np.int32)
         for _ in range(8):
-            fx, fy = rng.uniform(-0.05, 0.05, 2)
-            ph = rng.uniform(0, 2 * np.pi)
-            amp = rng.uniform(4, 16)
-            acc += np.float32(amp) * np.sin(np.float32(fx) * xx + np.float32(fy) * yy + np.float32(ph))
+            a, b = (int(v) for v in rng.integers(-7, 8, 2))
+            period = int(rng.integers(64, 513)) * 2
+            ph = int(rng.integers(0, period))
+            amp = int(rng.integers(4, 17))
+            t = (a * xx + b * yy + ph) % period                # 0 .. period-1
+            tri = np.abs(t - period // 2)                      # 0 .. period/2
+            acc += (amp * (4 * tri - period)) // period        # -amp .. +amp
         img[:, :, c] = acc
-    img += rng.random((H, W, 3), dtype=np.float32) * 8.0
+    if len(_BASE_CACHE) > 16:
+        _BASE_CACHE.clear()
+    _BASE_CACHE[key] = img
+    return img
+
+
+def make_image(i: int, W: int, H: int, out: np.ndarray | None = None, hsv: bool = True) -> np.ndarray:
+    """H x W x 3 u8 BGR: one of 4 cached integer base patterns, rolled by a frame-dependent offset, plus U[0,8)
+    per-pixel noise (seed 44+i), then the reference's 8-bit HSV round trip."""
+    rng = np.random.default_rng(44 + i)
+    base = _base_pattern(i % 4, W, H)
+    img = np.roll(base, ((i * 13) % H, (i * 29) % W), axis=(0, 1))
+    img = img + rng.integers(0, 8, size=(H, W, 3), dtype=np.int16)
     u8 = np.clip(img, 0, 255).astype(np.uint8)
     if hsv:
         u8 = hsv_round_trip(u8)
