@@ -1,0 +1,309 @@
+"""CPU checks of the oracle itself (no GPU): committed golden fixtures, independent restatements (cv2.projectPoints, a
+literal numpy/python z-buffer, scipy rotations, a numpy NID) and the size-independent properties the domain offers."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import make_scene
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def load_colorize_inputs(g):
+    from pointcloudprocessor_b200 import synth
+    n, f, W, H = int(g["n"]), int(g["f"]), int(g["W"]), int(g["H"])
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(f)
+    assert sha(cloud) == str(g["sha_cloud"]), "synthetic cloud generator drifted from the golden fixture"
+    assert sha(poses) == str(g["sha_poses"]), "synthetic pose generator drifted from the golden fixture"
+    masks = bool(int(g["masks"]))
+    images, mks = [], []
+    for i in range(f):
+        img = synth.make_image(i, W, H)
+        mk = synth.make_mask(i, W, H) if masks else None
+        assert sha(img) + (sha(mk) if masks else "") == str(g["sha_images"][i]), "synthetic image generator drifted"
+        images.append(img)
+        mks.append(mk)
+    T = g["T_opt"] if g["T_opt"].size else None
+    return dict(n=n, f=f, W=W, H=H, intr=intr, dist=dist, cloud=cloud, poses=poses, images=images, masks=mks, T_opt=T,
+                cull_size=tuple(int(v) for v in g["cull_size"]), ds=int(g["ds"]), tol=float(g["tol"]))
+
+
+COLORIZE_CASES = ["tiny", "tiny_masks", "tiny_extrinsic", "refcull"]
+
+
+@pytest.mark.parametrize("name", COLORIZE_CASES)
+def test_oracle_matches_golden(oracle, name):
+    g = np.load(os.path.join(GOLD, f"colorize_{name}.npz"))
+    sc = load_colorize_inputs(g)
+    oc = oracle.Colorizer(oracle.camera(sc["intr"], sc["dist"]), sc["W"], sc["H"], sc["cloud"], cull_size=sc["cull_size"], ds=sc["ds"],
+                          tol=sc["tol"], keep_obs=True)
+    for i in range(sc["f"]):
+        r = oc.frame(sc["poses"][i], sc["images"][i], mask=sc["masks"][i], T_opt=sc["T_opt"], want_vis=True, want_pix=True, threads=1 + i % 3)
+        assert np.array_equal(np.packbits(r["vis"], bitorder="little"), g[f"vis_{i}"])
+        assert np.array_equal(r["pix"], g[f"pix_{i}"])
+        assert (r["n_candidates"], r["n_visible"], r["n_colored"]) == tuple(g["counts"][i])
+    acc, mh, mm = oc.accumulators()
+    assert np.array_equal(acc, g["acc"]) and np.array_equal(mh, g["mask_hits"]) and np.array_equal(mm, g["mask_max"])
+    assert np.array_equal(oc.finalize_sum(), g["rgb_sum"])
+    assert np.array_equal(oc.finalize_top5(), g["rgb_top5"])
+
+
+def test_oracle_edge_golden(oracle):
+    from pointcloudprocessor_b200 import synth
+    g = np.load(os.path.join(GOLD, "edge_points.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    intr, dist = synth.make_camera(W, H)
+    img = synth.make_image(0, W, H)
+    assert sha(img) == str(g["sha_image"])
+    oc = oracle.Colorizer(oracle.camera(intr, dist), W, H, g["cloud"])
+    r = oc.frame(g["pose"], img, want_vis=True, want_pix=True)
+    assert np.array_equal(np.packbits(r["vis"], bitorder="little"), g["vis"]) and np.array_equal(r["pix"], g["pix"])
+    assert [r["n_candidates"], r["n_visible"], r["n_colored"]] == list(g["counts"])
+    assert np.array_equal(oc.accumulators()[0], g["acc"])
+
+
+def test_oracle_nid_golden(oracle):
+    from pointcloudprocessor_b200 import synth
+    g = np.load(os.path.join(GOLD, "nid_tiny.npz"))
+    W, H, n = int(g["W"]), int(g["H"]), int(g["n"])
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(2)
+    assert sha(cloud) == str(g["sha_cloud"])
+    cam = oracle.camera(intr, dist)
+    w2c, _ = oracle.pose_matrices(poses[1])
+    pts_cam = oracle.transform(cloud, w2c)
+    keep = oracle.view_culling(cam, W, H, pts_cam)
+    assert np.array_equal(keep, g["keep"])
+    culled = np.concatenate([pts_cam[keep], cloud[keep, 3:]], 1)
+    img = synth.make_image(1, W, H)
+    assert sha(img) == str(g["sha_image"])
+    grey = synth.grey_plane(img)
+    for b, c in enumerate(g["cands"]):
+        v, ok, h, cnt = oracle.nid(cam, grey, culled, c, want_hist=True)
+        assert ok == bool(g["ok"][b])
+        assert np.array_equal(np.concatenate([h.reshape(-1), cnt]), g["hist"][b])
+        if ok:
+            assert v == g["nid"][b]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# independent restatements
+# ---------------------------------------------------------------------------------------------------------------------
+def test_projection_vs_cv2(oracle):
+    """include/camera/pinhole.hpp:12-51 is OpenCV's plumb_bob model with the same coefficient order."""
+    cv2 = pytest.importorskip("cv2")
+    from pointcloudprocessor_b200 import synth
+    rng = np.random.default_rng(0)
+    intr, dist = synth.REF_INTRINSICS, synth.REF_DISTORTION
+    xyz = np.stack([rng.uniform(-2, 2, 5000), rng.uniform(-1.5, 1.5, 5000), rng.uniform(0.5, 20, 5000)], 1)
+    uv = oracle.project(oracle.camera(intr, dist), xyz)
+    K = np.array([[intr[0], 0, intr[2]], [0, intr[1], intr[3]], [0, 0, 1]])
+    ref, _ = cv2.projectPoints(xyz.reshape(-1, 1, 3), np.zeros(3), np.zeros(3), K, np.array(dist))
+    assert np.abs(uv - ref.reshape(-1, 2)).max() < 1e-8
+
+
+def test_pose_matrices_vs_scipy(oracle):
+    from scipy.spatial.transform import Rotation
+    from pointcloudprocessor_b200 import synth
+    poses, _ = synth.make_poses(40)
+    for p in poses:
+        w2c, c2w = oracle.pose_matrices(p)
+        R = Rotation.from_quat([p[4], p[5], p[6], p[3]]).as_matrix()
+        T = np.eye(4)
+        T[:3, :3] = R
+        T[:3, 3] = p[:3]
+        assert np.abs(c2w - T.astype(np.float32)).max() <= 1e-6
+        assert np.abs(w2c - np.linalg.inv(T)).max() <= 5e-6
+
+
+def _literal_view_culling(cam_intr, dist, W, H, pts, ds=14, tol=0.05):
+    """view_culling.cpp:52-174 transcribed statement by statement with python floats (IEEE double) and numpy float32."""
+    fx, fy, cx, cy = cam_intr
+    k1, k2, p1, p2, k3 = dist
+    Wc, Hc = W // ds, H // ds
+    dist_map = np.full((Hc, Wc), np.finfo(np.float32).max, np.float32)
+    indices, projected = [], []
+    norms = {}
+    for i, (X, Y, Z) in enumerate(pts.astype(np.float64)):
+        n4 = np.sqrt(X * X + Y * Y + Z * Z + 1.0)
+        if Z / n4 < 0.0:
+            continue
+        with np.errstate(all="ignore"):
+            x, y = np.float64(X) / np.float64(Z), np.float64(Y) / np.float64(Z)
+            x2, y2 = x * x, y * y
+            r2 = x2 + y2
+            r4 = r2 * r2
+            r6 = r2 * r4
+            rc = 1.0 + k1 * r2 + k2 * r4 + k3 * r6
+            t1 = 2.0 * x * y
+            t2 = r2 + 2.0 * x2
+            t3 = r2 + 2.0 * y2
+            u = fx * (rc * x + p1 * t1 + p2 * t2) + cx
+            v = fy * (rc * y + p1 * t3 + p2 * t1) + cy
+            uf, vf = np.float32(u), np.float32(v)
+            qx, qy = uf / np.float32(ds), vf / np.float32(ds)
+        if not (np.isfinite(qx) and np.isfinite(qy)) or abs(qx) >= 2**31 or abs(qy) >= 2**31:
+            continue  # x86 cvttss2si -> INT_MIN -> "< 0" rejects
+        px, py = int(qx), int(qy)  # truncation toward zero
+        if px < 0 or py < 0 or px >= W or py >= H:
+            continue
+        indices.append(i)
+        projected.append((px, py))
+        d = float(np.sqrt(X * X + Y * Y + Z * Z))
+        norms[i] = d
+        if 0 <= px < Wc and 0 <= py < Hc:
+            if d > float(dist_map[py, px]):
+                continue
+            dist_map[py, px] = np.float32(d)
+    out = []
+    for i, (px, py) in zip(indices, projected):
+        if 0 <= px < Wc and 0 <= py < Hc:
+            if norms[i] > float(dist_map[py, px]) + tol:
+                continue
+        else:
+            continue
+        out.append(i)
+    return np.array(out, np.int32), dist_map, len(indices)
+
+
+def test_view_culling_vs_literal_python(oracle):
+    from pointcloudprocessor_b200 import synth
+    W, H = 320, 240
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(6000, seed=5)
+    poses, _ = synth.make_poses(3)
+    cam = oracle.camera(intr, dist)
+    for p in poses:
+        w2c, _ = oracle.pose_matrices(p)
+        pts = oracle.transform(cloud, w2c)
+        got, dm, im, ncand = oracle.view_culling(cam, W, H, pts, want_maps=True)
+        ref, dm_ref, ncand_ref = _literal_view_culling(intr, dist, W, H, pts)
+        assert np.array_equal(got, ref) and ncand == ncand_ref
+        assert np.array_equal(dm, dm_ref)
+        assert len(ref) > 50
+
+
+def test_view_culling_permutation_invariant(oracle):
+    """The kept SET does not depend on the order of the points (the z-grid ends at min fl32(dist) whatever the order)."""
+    from pointcloudprocessor_b200 import synth
+    W, H = 320, 240
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(20000, seed=9)
+    poses, _ = synth.make_poses(1)
+    cam = oracle.camera(intr, dist)
+    w2c, _ = oracle.pose_matrices(poses[0])
+    pts = oracle.transform(cloud, w2c)
+    keep = oracle.view_culling(cam, W, H, pts)
+    perm = np.random.default_rng(1).permutation(len(pts))
+    keep_p = oracle.view_culling(cam, W, H, pts[perm])
+    assert np.array_equal(np.sort(perm[keep_p]), keep)
+    # monotone in the tolerance
+    k2 = oracle.view_culling(cam, W, H, pts, tol=0.2)
+    assert set(keep).issubset(set(k2))
+
+
+def test_openmp_equals_single_thread(oracle):
+    sc = make_scene(50_000, 2, 320, 240)
+    cam = oracle.camera(sc["intr"], sc["dist"])
+    a = oracle.Colorizer(cam, 320, 240, sc["cloud"])
+    b = oracle.Colorizer(cam, 320, 240, sc["cloud"])
+    for i in range(2):
+        ra = a.frame(sc["poses"][i], sc["images"][i], want_vis=True, want_pix=True, threads=1)
+        rb = b.frame(sc["poses"][i], sc["images"][i], want_vis=True, want_pix=True, threads=5)
+        assert np.array_equal(ra["vis"], rb["vis"]) and np.array_equal(ra["pix"], rb["pix"])
+    assert np.array_equal(a.accumulators()[0], b.accumulators()[0])
+
+
+def test_color_pixels_are_truncated_projection(oracle):
+    from pointcloudprocessor_b200 import synth
+    W, H = 640, 480
+    intr, dist = synth.make_camera(W, H)
+    cam = oracle.camera(intr, dist)
+    rng = np.random.default_rng(2)
+    pts = np.stack([rng.uniform(-3, 3, 4000), rng.uniform(-2, 2, 4000), rng.uniform(-1, 8, 4000)], 1).astype(np.float32)
+    pix = oracle.color_pixels(cam, W, H, pts)
+    uv = oracle.project(cam, pts.astype(np.float64))
+    for i in range(len(pts)):
+        exp = -1
+        if pts[i, 2] > 0:
+            u, v = int(uv[i, 0]), int(uv[i, 1])
+            if 0 <= u < W and 0 <= v < H:
+                exp = v * W + u
+        assert pix[i] == exp
+
+
+def _numpy_nid(intr, dist, img, xyzi, se3, bins=16):
+    """nid_cost.hpp:42-116 with numpy, vectorised differently from the oracle (np.add.at histograms)."""
+    from scipy.spatial.transform import Rotation
+    fx, fy, cx, cy = intr
+    k1, k2, p1, p2, k3 = dist
+    H, W = img.shape
+    R = Rotation.from_quat(se3[:4]).as_matrix()
+    pc = xyzi[:, :3].astype(np.float64) @ R.T + se3[4:]
+    with np.errstate(all="ignore"):
+        x, y = pc[:, 0] / pc[:, 2], pc[:, 1] / pc[:, 2]
+        r2 = x * x + y * y
+        rc = 1 + k1 * r2 + k2 * r2**2 + k3 * r2**3
+        u = fx * (rc * x + 2 * p1 * x * y + p2 * (r2 + 2 * x * x)) + cx
+        v = fy * (rc * y + p1 * (r2 + 2 * y * y) + 2 * p2 * x * y) + cy
+    kx, ky = np.floor(u), np.floor(v)
+    ok = np.isfinite(u) & np.isfinite(v) & (kx >= 0) & (ky >= 0) & (kx < W) & (ky < H)
+    u, v, kx, ky = u[ok], v[ok], kx[ok].astype(int), ky[ok].astype(int)
+    bp = np.clip((xyzi[ok, 3].astype(np.float64) * bins).astype(int), 0, bins - 1)
+    C = np.array([[1, -3, 3, -1], [4, 0, -6, 3], [1, 3, 3, -3], [0, 0, 0, 1]], np.float64) / 6.0
+    sx, sy = u - kx, v - ky
+    bx = C @ np.stack([np.ones_like(sx), sx, sx**2, sx**3])
+    by = C @ np.stack([np.ones_like(sy), sy, sy**2, sy**3])
+    hist = np.zeros((bins, bins))
+    for i in range(4):
+        xs = np.clip(kx - 1 + i, 0, W - 1)
+        for j in range(4):
+            ys = np.clip(ky - 1 + j, 0, H - 1)
+            bi = np.minimum((img[ys, xs] * bins).astype(int), bins - 1)
+            np.add.at(hist, (bi, bp), bx[i] * by[j])
+    hp = np.bincount(bp, minlength=bins).astype(np.float64)
+    s = hp.sum()
+    ent = lambda p: -(p * np.log(p + 1e-6)).sum()  # noqa: E731
+    Hi, Hp, Hj = ent(hist.sum(1) / s), ent(hp / s), ent(hist / s)
+    return (Hj - (Hi + Hp - Hj)) / Hj
+
+
+def test_nid_vs_numpy(oracle):
+    from pointcloudprocessor_b200 import synth
+    W, H = 320, 240
+    sc = make_scene(20_000, 1, W, H)
+    cam = oracle.camera(sc["intr"], sc["dist"])
+    w2c, _ = oracle.pose_matrices(sc["poses"][0])
+    pts = oracle.transform(sc["cloud"], w2c)
+    keep = oracle.view_culling(cam, W, H, pts)
+    culled = np.concatenate([pts[keep], sc["cloud"][keep, 3:]], 1)
+    grey = synth.grey_plane(sc["images"][0])
+    for c in synth.make_nid_candidates(4):
+        v, ok = oracle.nid(cam, grey, culled, c)
+        ref = _numpy_nid(sc["intr"], sc["dist"], grey, culled, c)
+        assert ok and 0.0 <= v <= 1.0
+        assert abs(v - ref) <= 1e-9 * abs(ref)
+
+
+def test_scores_range_and_formula(oracle):
+    rng = np.random.default_rng(3)
+    pts = rng.normal(size=(2000, 3)).astype(np.float32) * 3
+    pose = np.array([0.3, -0.2, 0.1, 1, 0, 0, 0], np.float64)
+    s = oracle.scores(pts, pose)
+    assert (s >= 0.2 - 1e-6).all() and (s <= 1.0 + 1e-6).all()
+    d = np.linalg.norm(pts.astype(np.float64), axis=1)
+    exp_d = 0.2 + 0.8 * (1 - np.minimum(np.abs(d - 2) / 2, 1))
+    assert np.abs(s[:, 1] - exp_d).max() < 1e-5
+    v = pts.astype(np.float64) - pose[:3]
+    cz = v[:, 2] / np.linalg.norm(v, axis=1)
+    assert np.abs(s[:, 0] - (0.2 + 0.8 * (cz + 1) / 2)).max() < 1e-5
+    assert np.abs(s[:, 2] - (s[:, 0] + s[:, 1]) / 2).max() < 1e-6
