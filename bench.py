@@ -62,7 +62,7 @@ class ClockSampler:
         self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.proc = None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "50",
                                           "-i", str(index)], stdout=self.tmp, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -287,7 +287,7 @@ def run_native(args):
     value = n * f * world * args.steps / (ms * 1e-3)
 
     # ---- e2e: host buffers through the C ABI --------------------------------------------------------------------------
-    e2e_steps = max(1, min(args.steps, 5))
+    e2e_steps = max(1, min(args.steps, 10))
     step_e2e()
     barrier()
     torch.cuda.synchronize()
@@ -376,7 +376,7 @@ def run_native(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="C2")

@@ -56,10 +56,16 @@ typedef struct {
 typedef struct {
   uint32_t* visible_bits; /* ceil(N/32) words; bit i = point i survived ViewCulling::view_culling (view_culling.cpp:52-174) */
   int32_t* pixel_index;   /* N entries: v*W+u of the sampled pixel (cpp:752-754) or -1 */
-  int64_t n_candidates;   /* points recorded by pass 1 (view_culling.cpp:96) */
+  int64_t n_candidates;   /* points recorded by pass 1 (view_culling.cpp:96); -1 with PCP_OUT_SKIP_CANDIDATES */
   int64_t n_visible;      /* points kept by pass 2 (view_culling.cpp:167) */
   int64_t n_colored;      /* points pushed by generateColorMap (cpp:763) */
+  uint32_t flags;         /* in: PCP_OUT_* */
+  uint32_t reserved;
 } pcp_frame_out;
+/* n_candidates is an internal of the reference (indices.size() before its second pass) that nothing downstream reads;
+ * counting it exactly costs a wider FP32 classification per point.  Frames submitted without a pcp_frame_out, or with
+ * this flag, use the kernel variant that skips the count.  Every other output is identical. */
+enum { PCP_OUT_SKIP_CANDIDATES = 1 };
 
 void pcp_default_params(pcp_params* p);
 int pcp_abi_version(void);

@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpcp_b200.so")
+LIB_PATH = os.environ.get("PCP_LIB_PATH") or os.path.join(_HERE, "libpcp_b200.so")  # PCP_LIB_PATH: kernel-variant experiments
 
 PCP_OK, PCP_EINVAL, PCP_EIO, PCP_ECUDA, PCP_ENCCL, PCP_ENOMEM = range(6)
 ACCUM_SUM, ACCUM_TOP5 = 0, 1
@@ -30,7 +30,10 @@ class Params(C.Structure):
 
 class FrameOut(C.Structure):
     _fields_ = [("visible_bits", C.c_void_p), ("pixel_index", C.c_void_p), ("n_candidates", C.c_int64), ("n_visible", C.c_int64),
-                ("n_colored", C.c_int64)]
+                ("n_colored", C.c_int64), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+OUT_SKIP_CANDIDATES = 1
 
 
 # every symbol include/pcp/pcp.h declares

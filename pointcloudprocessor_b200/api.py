@@ -124,7 +124,7 @@ class Colorizer:
         return None if T is None else np.ascontiguousarray(np.asarray(T, np.float64).T.reshape(-1))
 
     def submit_frame(self, pose7, bgr: np.ndarray, mask: np.ndarray | None = None, T_opt=None, want_vis=False, want_pix=False,
-                     want_counts=False):
+                     want_counts=False, count_candidates=True):
         pose = np.ascontiguousarray(pose7, np.float64)
         T = self._mat16(T_opt)
         if bgr.dtype != np.uint8 or bgr.ndim != 3 or bgr.shape[2] != 3 or bgr.strides[2] != 1 or bgr.strides[1] != 3:
@@ -140,6 +140,7 @@ class Colorizer:
         vis = pix = None
         if want_vis or want_pix or want_counts:
             out = FrameOut()
+            out.flags = 0 if count_candidates else _capi.OUT_SKIP_CANDIDATES
             if want_vis:
                 vis = np.zeros((self.n + 31) // 32, np.uint32)
                 out.visible_bits = vis.ctypes.data

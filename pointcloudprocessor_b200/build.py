@@ -34,14 +34,17 @@ def _newer(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, defines=(), out: str | None = None) -> str:
     nvcc = _nvcc()
     srcs = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".hpp", ".h"))]
     headers.append(os.path.join(_HERE, "..", "include", "pcp", "pcp.h"))
-    objdir = os.path.join(_HERE, "build")
+    lib_path = out or LIB_PATH
+    tag = "" if not defines else "_" + "_".join(d.replace("=", "") for d in defines)
+    objdir = os.path.join(_HERE, "build" + tag)
     os.makedirs(objdir, exist_ok=True)
     common = ["-O3", "-std=c++17", "-lineinfo", "-fmad=false", "-ccbin", _host_cxx(), "-Xcompiler", "-fPIC,-ffp-contract=off"] + ARCH
+    common += [f"-D{d}" for d in defines]
     if verbose:
         common += ["-Xptxas", "-v"]
     objs = []
@@ -58,14 +61,16 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
                 raise RuntimeError(f"nvcc failed on {s}")
             rebuilt = True
         objs.append(obj)
-    if rebuilt or not os.path.exists(LIB_PATH):
-        cmd = [nvcc, "-shared", "-o", LIB_PATH] + objs + ARCH + ["-ccbin", _host_cxx(), "-ldl", "-Xlinker", "--no-undefined"]
+    if rebuilt or not os.path.exists(lib_path):
+        cmd = [nvcc, "-shared", "-o", lib_path] + objs + ARCH + ["-ccbin", _host_cxx(), "-ldl", "-Xlinker", "--no-undefined"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError("link failed")
-    return LIB_PATH
+    return lib_path
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    _defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    _out = next((a[6:] for a in sys.argv[1:] if a.startswith("--out=")), None)
+    print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv, defines=_defs, out=_out))

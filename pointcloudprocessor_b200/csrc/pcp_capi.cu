@@ -101,6 +101,10 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
   ctx->resolve_grid = ctx->sm_count * 4;
+  {
+    const char* e_np = std::getenv("PCP_NO_PREFILTER");
+    ctx->prefilter = !(e_np && e_np[0] == '1');
+  }
   *out = ctx;
   return PCP_OK;
 }

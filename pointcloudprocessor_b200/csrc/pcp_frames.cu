@@ -1,4 +1,5 @@
 // pcp_frames.cu — per-frame submission (the keyframe loop body), ViewCulling::cull drop-in, accumulators, finalize.
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -41,6 +42,27 @@ FrameParams base_params(const pcp_ctx* ctx) {
   fp.imgW = ctx->prm.image_width;
   fp.imgH = ctx->prm.image_height;
   fp.depth_culling = ctx->prm.enable_depth_buffer_culling;
+  // FP32 pre-filter constants: magnitudes are rounded away from zero so that the bound stays an upper bound
+  auto up = [](double v) { float f = (float)std::fabs(v); return (double)f < std::fabs(v) ? std::nextafterf(f, INFINITY) : f; };
+  PreF& q = fp.pre;
+  q.fx = (float)c.fx; q.fy = (float)c.fy; q.cx = (float)c.cx; q.cy = (float)c.cy;
+  q.k1 = (float)c.dist[0]; q.k2 = (float)c.dist[1]; q.p1 = (float)c.dist[2]; q.p2 = (float)c.dist[3]; q.k3 = (float)c.dist[4];
+  q.ak1 = up(c.dist[0]); q.ak2 = up(c.dist[1]); q.ak3 = up(c.dist[4]);
+  q.apt = up(3.0 * (std::fabs(c.dist[2]) + std::fabs(c.dist[3])) * (1.0 + 1e-6));
+  q.afmax = up(std::fmax(std::fabs(c.fx), std::fabs(c.fy))); q.acmax = up(std::fmax(std::fabs(c.cx), std::fabs(c.cy)));
+  const double ds = (double)ctx->prm.downsample;
+  q.inv_ds = (float)(1.0 / ds); q.wc = (float)ctx->Wc; q.hc = (float)ctx->Hc; q.Wc = ctx->Wc;
+  q.lo = -(float)ds;
+  q.u_hi_cand = (float)(ds * ctx->prm.cull_width); q.v_hi_cand = (float)(ds * ctx->prm.cull_height);
+  q.err = 64.0f * 5.9604644775390625e-08f;  // 64 * 2^-24
+  q.slack = 1.0f / 32.0f;                     // pixels; also covers the 1-ulp fuzz of the float division by ds
+  q.dscale = 1.0f - 8.0f * 5.9604644775390625e-08f;  // squared norm: 3 roundings + the final product < 5 eps
+  {
+    float t = (float)ctx->prm.depth_tolerance;
+    if ((double)t < ctx->prm.depth_tolerance) t = std::nextafterf(t, INFINITY);
+    q.tol_up = t >= 0.0f ? t : INFINITY;  // a negative tolerance disables the FP32 early-z (the squared compare needs lim >= 0)
+  }
+  fp.use_prefilter = ctx->prefilter ? 1 : 0;
   return fp;
 }
 
@@ -53,7 +75,7 @@ int ensure_outputs(pcp_ctx* ctx, bool vis, bool pix) {
 
 // Enqueue init + scan + resolve for one frame on ctx->stream.
 int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t pitch, const uint8_t* d_mask, size_t mask_pitch,
-              bool want_vis, bool want_pix, bool accumulate) {
+              bool want_vis, bool want_pix, bool accumulate, bool count_candidates) {
   if (!ctx->d_cloud) { ctx->fail("no cloud: call pcp_set_cloud first"); return PCP_EINVAL; }
   int rc = ensure_outputs(ctx, want_vis, want_pix);
   if (rc != PCP_OK) return rc;
@@ -86,7 +108,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.records = ctx->d_records;
   sa.counters = ctx->d_counters;
   sa.n = (uint32_t)ctx->n;
-  launch_scan(sa, fp, ctx->scan_grid, ctx->stream);
+  launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->stream);
   if (pe) CU(cudaEventRecord(pe[2], ctx->stream));
 
   ResolveArgs ra;
@@ -121,7 +143,7 @@ int fetch_outputs(pcp_ctx* ctx, pcp_frame_out* out) {
   if (out->visible_bits) CU(cudaMemcpyAsync(out->visible_bits, ctx->d_vis_bits, sizeof(uint32_t) * ((ctx->n + 31) / 32), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->pixel_index) CU(cudaMemcpyAsync(out->pixel_index, ctx->d_pix, sizeof(int32_t) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
-  out->n_candidates = ctx->h_counters->n_candidates;
+  out->n_candidates = (out->flags & PCP_OUT_SKIP_CANDIDATES) ? -1 : (int64_t)ctx->h_counters->n_candidates;
   out->n_visible = ctx->h_counters->n_visible;
   out->n_colored = ctx->h_counters->n_colored;
   return PCP_OK;
@@ -155,7 +177,8 @@ int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T
   FrameParams fp;
   int rc = frame_params_for_pose(ctx, pose7, T_opt16, fp);
   if (rc != PCP_OK) return rc;
-  rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true);
+  rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true,
+                 out && !(out->flags & PCP_OUT_SKIP_CANDIDATES));
   if (rc != PCP_OK) return rc;
   ctx->frame_index++;
   if (out) return fetch_outputs(ctx, out);
@@ -186,7 +209,7 @@ int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16,
 
 static int cull_common(pcp_ctx* ctx, const FrameParams& fp, int32_t* idx_out, size_t* m_out) {
   if (!idx_out || !m_out) { ctx->fail("pcp_cull: null output"); return PCP_EINVAL; }
-  int rc = run_frame(ctx, fp, nullptr, 0, nullptr, 0, true, false, false);
+  int rc = run_frame(ctx, fp, nullptr, 0, nullptr, 0, true, false, false, false);
   if (rc != PCP_OK) return rc;
   const size_t n1 = ctx->n ? ctx->n : 1;
   if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n1));
@@ -207,7 +230,7 @@ int pcp_cull(pcp_ctx* ctx, const float* w2c16, const double* T16, int32_t* idx_o
   CU(cudaSetDevice(ctx->device));
   FrameParams fp = base_params(ctx);
   if (w2c16) { fill_xf(fp.w2c, w2c16); fp.use_w2c = 1; }
-  if (T16) { fill_xd(fp.T, T16); fp.use_T = 1; }
+  if (T16) { fill_xd(fp.T, T16); fp.use_T = 1; fp.use_prefilter = 0; }  // the gate is taken after the double T: exact path only
   return cull_common(ctx, fp, idx_out, m_out);
 }
 

@@ -30,6 +30,20 @@ struct FrameCounters {
   unsigned int pad[11];
 };
 
+// FP32 pre-filter constants (pcp_kernels.cu: prefilter()): the camera in float, the same coefficients as magnitudes, the
+// decision boundaries in pixels and the error-bound factors.
+struct PreF {
+  float fx, fy, cx, cy, k1, k2, k3, p1, p2;
+  float ak1, ak2, ak3, apt;      // |k1|,|k2|,|k3| and 3(|p1|+|p2|), rounded up
+  float afmax, acmax;            // max(|fx|,|fy|), max(|cx|,|cy|), rounded up
+  float inv_ds, wc, hc;          // 1/ds, (float)Wc, (float)Hc: cells are trunc(u/ds), (-1,1) -> 0
+  int Wc;
+  float lo;                      // -ds
+  float u_hi_cand, v_hi_cand;    // ds * cullW, ds * cullH (pass-1 gate, candidate counting only)
+  float err, slack;              // 64 * 2^-24 and an absolute slack in pixels
+  float dscale, tol_up;          // (1 - 8 eps): lower bound of the float norm; tolerance rounded up to float
+};
+
 struct FrameParams {
   Xf34 w2c;          // float pre-transform (identity when absent)
   Xd34 T;            // double T_camera_lidar (view_culling.cpp:37)
@@ -43,6 +57,8 @@ struct FrameParams {
   int imgW, imgH;    // actual image size
   int depth_culling;
   int frame_index;
+  int use_prefilter;  // 0 when a double T is applied before the gate (pcp_cull with T16) or when disabled for testing
+  PreF pre;
 };
 
 struct ScanArgs {
@@ -76,7 +92,7 @@ struct ResolveArgs {
 };
 
 void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s);
-void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
+void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
 void launch_finalize_sum(const uint4* acc, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);

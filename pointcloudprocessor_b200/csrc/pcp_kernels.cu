@@ -13,9 +13,15 @@
 
 namespace pcp {
 
+#ifndef PCP_UNROLL
+#define PCP_UNROLL_CAP 4
+#else
+#define PCP_UNROLL_CAP PCP_UNROLL
+#endif
 static constexpr int kScanThreads = 256;
 static constexpr int kWarpsPerCta = kScanThreads / 32;
-static constexpr int kQueueCap = 64;  // per-warp staging queue (records), flushed 32 at a time
+static constexpr int kQueueCap = 64;  // per-warp record queue, flushed 32 at a time
+static constexpr int kCandCap = 32 * (PCP_UNROLL_CAP + 1); // per-warp candidate queue: < 32 left over + kUnroll x 32 new entries
 
 __global__ void zgrid_init_kernel(unsigned long long* zgrid, int cells, FrameCounters* counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -29,13 +35,91 @@ void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* coun
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Per-point body of pass 1.  Returns true when a record must be emitted.
+// Pass 1, stage A: conservative FP32 pre-filter (branch-free, so that the kUnroll points of a lane interleave).
+//
+// The reference's decisions (view_culling.cpp:76-168) are taken on the DOUBLE projection / norm of the float camera-frame
+// point.  Evaluating them in FP32 (with FMAs) costs a fraction of the FP64 path, and a running error bound tells when the
+// FP32 value is far enough from every decision boundary for the FP64 evaluation to be unnecessary:
+//   |u_f32 - u_exact| <= E = 64 eps * (max|f| * M + max|c|) + slack,
+//   M = (1 + |k1| r2 + |k2| r4 + |k3| r6) * max(|x|,|y|) + 3 (|p1| + |p2|) r2  >=  the polynomial on absolute values
+// (each term carries a relative error of at most ~31 eps: 3 eps from the reciprocal times the degree <= 7 of the term,
+// plus one eps per operation; the FP64 evaluation, its cast to float and the multiplication by 1/ds add < 4 eps; 64 eps
+// leaves a factor ~2; `slack` absorbs the 1-ulp fuzz of the reference's float division by ds).
+// A point is dropped here only when one of these is CERTAIN:
+//   * its cell lies outside the Wc x Hc z-grid (never kept by pass 2, :162-165), or
+//   * its cell is known and ||p|| (lower bound) exceeds the cell's current minimum + tol: the minimum only decreases, so
+//     pass 2 (:157) rejects it and it can never lower the minimum itself.
+// Anything non-finite makes the comparisons false, which sends the point to the exact path.
+// Returns: bit 0 = needs the exact FP64 path; bit 1 = certainly a pass-1 candidate (:96) that is dropped here (kCount only).
 // ---------------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool scan_point(const FrameParams& fp, unsigned long long* __restrict__ zgrid, float4 p, uint32_t idx,
-                                           Record& rec, bool& candidate) {
+struct PreA {
+  int cell;            // known cell, or 0
+  float dlo;           // lower bound of ||p||^2
+  unsigned int flags;  // 1 cell known, 2 certainly outside the z-grid, 4 certainly not a candidate, 8 certainly a candidate
+};
+
+template <bool kCount>
+__device__ __forceinline__ PreA prefilter_a(const PreF& c, float X, float Y, float Z) {
+  // rcp.approx.ftz: 1 ulp; Z == 0 / denormal -> inf -> NaN or inf below -> exact path; |Z| >= 2^126 would flush the
+  // reciprocal to 0 and give a finite but wrong x, so such Z are turned into NaN explicitly
+  float rz;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rz) : "f"(Z));
+  rz = (Z < 1.0e30f) ? rz : __int_as_float(0x7fc00000);
+  const float x = X * rz, y = Y * rz;
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float x2 = x * x, y2 = y * y;
+  const float r2 = x2 + y2;
+  const float rc = fmaf(r2, fmaf(r2, fmaf(r2, c.k3, c.k2), c.k1), 1.0f);
+  const float arc = fmaf(r2, fmaf(r2, fmaf(r2, c.ak3, c.ak2), c.ak1), 1.0f);
+  const float t1 = (x + x) * y;
+  const float t2 = fmaf(2.0f, x2, r2), t3 = fmaf(2.0f, y2, r2);
+  const float xd = fmaf(rc, x, fmaf(c.p1, t1, c.p2 * t2));
+  const float yd = fmaf(rc, y, fmaf(c.p1, t3, c.p2 * t1));
+  const float u = fmaf(c.fx, xd, c.cx), v = fmaf(c.fy, yd, c.cy);
+  const float m = fmaf(arc, fmaxf(ax, ay), c.apt * r2);
+  const float e = fmaf(fmaf(c.afmax, m, c.acmax), c.err, c.slack);
+  const float ulo = u - e, uhi = u + e, vlo = v - e, vhi = v + e;
+  const float qlo = ulo * c.inv_ds, qhi = uhi * c.inv_ds, rlo = vlo * c.inv_ds, rhi = vhi * c.inv_ds;
+  // certainly inside / certainly outside the z-grid (cells are trunc(u/ds): (-1,1) -> 0)
+  const bool in_grid = (qlo > -1.0f) && (qhi < c.wc) && (rlo > -1.0f) && (rhi < c.hc);
+  const bool out_grid = (qhi <= -1.0f) || (qlo >= c.wc) || (rhi <= -1.0f) || (rlo >= c.hc);
+  const int ix0 = __float2int_rz(qlo), ix1 = __float2int_rz(qhi), iy0 = __float2int_rz(rlo), iy1 = __float2int_rz(rhi);
+  const bool cell_known = in_grid && ix0 == ix1 && iy0 == iy1;
+  PreA o;
+  o.cell = cell_known ? iy0 * c.Wc + ix0 : 0;
+  o.dlo = fmaf(Z, Z, fmaf(Y, Y, X * X)) * c.dscale;  // <= the exact squared norm
+  o.flags = (cell_known ? 1u : 0u) | (out_grid ? 2u : 0u);
+  if (kCount) {
+    const bool not_cand = (uhi <= c.lo) || (vhi <= c.lo) || (ulo >= c.u_hi_cand) || (vlo >= c.v_hi_cand);
+    const bool is_cand = (ulo > c.lo) && (vlo > c.lo) && (uhi < c.u_hi_cand) && (vhi < c.v_hi_cand);
+    o.flags |= (not_cand ? 4u : 0u) | (is_cand ? 8u : 0u);
+  }
+  return o;
+}
+
+// Second half: `curbits` = high word of the cell's packed key (any value the cell held during this frame is an upper bound of
+// its final minimum).  Returns bit 0 = needs the exact path, bit 1 = dropped here but certainly a pass-1 candidate.
+template <bool kCount>
+__device__ __forceinline__ unsigned int prefilter_b(const PreF& c, const PreA& a, unsigned int curbits, bool depth_culling) {
+  const float lim = __fadd_ru(__uint_as_float(curbits), c.tol_up);  // >= current minimum + tol >= 0  (FLT_MAX -> inf)
+  const bool occluded = (a.flags & 1u) && (a.dlo > __fmul_ru(lim, lim));
+  const bool dropped = (a.flags & 2u) || occluded;
+  bool need;
+  if (!kCount) {
+    need = depth_culling ? !dropped : true;
+    return need ? 1u : 0u;
+  }
+  const bool cand_known = (a.flags & 12u) != 0u;
+  need = depth_culling ? !(cand_known && dropped) : !(a.flags & 4u);
+  return (need ? 1u : 0u) | ((!need && (a.flags & 8u)) ? 2u : 0u);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Pass 1, stage B: the exact FP64 body for one camera-frame float point.  Returns true when a record must be emitted.
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long long* __restrict__ zgrid, float x, float y, float z,
+                                            uint32_t idx, Record& rec, bool& candidate) {
   candidate = false;
-  float x = p.x, y = p.y, z = p.z;
-  if (fp.use_w2c) transform_point(fp.w2c, p.x, p.y, p.z, x, y, z);  // pcl::transformPointCloud (cpp:521)
   double X = (double)x, Y = (double)y, Z = (double)z;                // view_culling.cpp:33
   if (fp.use_T) transform_point_d(fp.T, (double)x, (double)y, (double)z, X, Y, Z);  // :37
   if (Z < 0.0) return false;                                          // :76
@@ -71,87 +155,173 @@ __device__ __forceinline__ bool scan_point(const FrameParams& fp, unsigned long 
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// scan_kernel: one point per lane per step; warp-private shared-memory queue, flushed 32 records (1 KB) at a time with a
-// single global atomicAdd, so record emission costs one global atomic per 32 records.
+// scan_kernel: per warp, kUnroll x 32 points are loaded (coalesced float4), transformed in float (exact, PCL order) and
+// pre-filtered; survivors are compacted into a warp-private shared-memory queue so that stage B runs with all 32 lanes
+// busy.  Records leave through a second warp-private queue, 32 records (1 KB) per global atomicAdd.
 // ---------------------------------------------------------------------------------------------------------------------
-template <bool kPrebin>
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
-  __shared__ Record queue[kWarpsPerCta][kQueueCap];
+#ifndef PCP_UNROLL
+#define PCP_UNROLL 4
+#endif
+#ifndef PCP_SCAN_CTAS
+#define PCP_SCAN_CTAS 4
+#endif
+// The early-z read of stage A goes through L1: a stale value is still an upper bound of the cell's final minimum (it only
+// decreases), and per-SM copies remove the L2 hot spot of the cells around the vanishing point (measured: 109 -> 77 us).
+#ifdef PCP_ZLOAD_L2
+#define PCP_ZLOAD(p) __ldcg(p)
+#else
+#define PCP_ZLOAD(p) __ldca(p)
+#endif
+static constexpr int kUnroll = PCP_UNROLL;
+
+template <bool kPrebin, bool kCount>
+__global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+  __shared__ float4 cand_queue[kWarpsPerCta][kCandCap];
+  __shared__ Record rec_queue[kWarpsPerCta][kQueueCap];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  Record* q = queue[warp];
-  int qn = 0;
+  const unsigned int lt_mask = (1u << lane) - 1u;
+  float4* cq = cand_queue[warp];
+  Record* rq = rec_queue[warp];
+  int cn = 0, rn = 0;
   unsigned int ncand = 0;
+  const bool prefilter_on = fp.use_prefilter != 0;
+  const bool depth_culling = fp.depth_culling != 0;
 
-  auto step = [&](bool valid, float4 p, uint32_t idx) {
+  // stage B on the last `cnt` (<= 32) entries of the candidate queue, then record compaction / flush
+  auto stage_b = [&](int cnt) {
     Record rec;
-    bool cand = false;
-    bool emit = false;
-    if (valid) emit = scan_point(fp, a.zgrid, p, idx, rec, cand);
-    ncand += cand ? 1u : 0u;
+    bool cand = false, emit = false;
+    cn -= cnt;
+    if (lane < cnt) {
+      const float4 c = cq[cn + lane];
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, __float_as_uint(c.w), rec, cand);
+    }
+    if (kCount) ncand += cand ? 1u : 0u;
     const unsigned int m = __ballot_sync(0xffffffffu, emit);
     if (m) {
-      if (emit) q[qn + __popc(m & ((1u << lane) - 1u))] = rec;
-      qn += __popc(m);
+      if (emit) rq[rn + __popc(m & lt_mask)] = rec;
+      rn += __popc(m);
       __syncwarp();
-      if (qn >= 32) {
+      if (rn >= 32) {
         unsigned int base = 0;
         if (lane == 0) base = atomicAdd(&a.counters->n_records, 32u);
         base = __shfl_sync(0xffffffffu, base, 0);
-        const uint4* src = reinterpret_cast<const uint4*>(q);
+        rn -= 32;
+        const uint4* src = reinterpret_cast<const uint4*>(rq + rn);
         uint4* dst = reinterpret_cast<uint4*>(a.records + base);
-        dst[lane] = src[lane];            // 64 x 16 B = the first 32 records, fully coalesced
+        dst[lane] = src[lane];            // 64 x 16 B = the last 32 records, fully coalesced
         dst[lane + 32] = src[lane + 32];
-        const int rem = qn - 32;
-        Record tmp;
-        if (lane < rem) tmp = q[32 + lane];
-        __syncwarp();
-        if (lane < rem) q[lane] = tmp;
-        qn = rem;
         __syncwarp();
       }
     }
   };
+  auto drain = [&]() {
+    __syncwarp();
+#pragma unroll 1
+    while (cn >= 32) stage_b(32);
+  };
+
+  // stage A for kUnroll points per lane: float transform (exact, PCL order), pre-filter, compaction into the queue
+  auto stage_a = [&](const bool (&valid)[kUnroll], const float4 (&p)[kUnroll], const uint32_t (&idx)[kUnroll]) {
+    float x[kUnroll], y[kUnroll], z[kUnroll];
+    bool push[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      x[k] = p[k].x; y[k] = p[k].y; z[k] = p[k].z;
+      if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x[k], y[k], z[k]);  // pcl::transformPointCloud (cpp:521)
+    }
+    if (prefilter_on) {
+      PreA pa[kUnroll];
+      unsigned int cur[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) pa[k] = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) {  // only lanes with a known cell touch the grid (no hot spot on cell 0)
+        cur[k] = 0x7f7fffffu;
+        if ((pa[k].flags & 1u) && !(z[k] < 0.0f)) cur[k] = PCP_ZLOAD(reinterpret_cast<const unsigned int*>(a.zgrid) + 2 * pa[k].cell + 1);
+      }
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) {
+        const unsigned int f = prefilter_b<kCount>(fp.pre, pa[k], cur[k], depth_culling);
+        const bool front = valid[k] && !(z[k] < 0.0f);  // view_culling.cpp:76 (exact: double(z) < 0 <=> z < 0)
+        push[k] = front && (f & 1u);
+        if (kCount) ncand += (front && (f & 2u)) ? 1u : 0u;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) push[k] = valid[k];
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      const unsigned int m = __ballot_sync(0xffffffffu, push[k]);
+      if (push[k]) cq[cn + __popc(m & lt_mask)] = make_float4(x[k], y[k], z[k], __uint_as_float(idx[k]));
+      cn += __popc(m);
+    }
+  };
 
   if (!kPrebin) {
-    const uint32_t stride = gridDim.x * kScanThreads;
-    for (uint32_t base = blockIdx.x * kScanThreads + warp * 32; base < a.n; base += stride) {
-      const uint32_t i = base + lane;
-      const bool valid = i < a.n;
-      float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (valid) p = __ldg(a.cloud + i);
-      step(valid, p, i);
+    const uint32_t chunk = 32u * kUnroll;
+    const unsigned long long stride = (unsigned long long)gridDim.x * kWarpsPerCta * chunk;
+    for (unsigned long long base64 = (unsigned long long)(blockIdx.x * kWarpsPerCta + warp) * chunk; base64 < a.n; base64 += stride) {
+      const uint32_t base = (uint32_t)base64;
+      float4 p[kUnroll];
+      bool valid[kUnroll];
+      uint32_t idx[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) {
+        idx[k] = base + k * 32 + lane;
+        valid[k] = idx[k] < a.n;
+        p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
+      }
+      stage_a(valid, p, idx);
+      drain();
     }
   } else {
     const uint32_t nact = a.counters->n_active_blocks;
-    const uint32_t warps_per_block = a.block_points / 32;
-    const uint32_t total = nact * warps_per_block;
+    const uint32_t chunks_per_block = a.block_points / (32 * kUnroll);
+    const uint32_t total = nact * chunks_per_block;
     for (uint32_t w = blockIdx.x * kWarpsPerCta + warp; w < total; w += gridDim.x * kWarpsPerCta) {
-      const uint32_t blk = a.active_blocks[w / warps_per_block];
-      const uint32_t i = blk * a.block_points + (w % warps_per_block) * 32 + lane;
-      const bool valid = i < a.n;
-      float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-      uint32_t idx = 0;
-      if (valid) { p = __ldg(a.cloud + i); idx = __ldg(a.perm + i); }
-      step(valid, p, idx);
+      const uint32_t blk = a.active_blocks[w / chunks_per_block];
+      const uint32_t base = blk * a.block_points + (w % chunks_per_block) * (32 * kUnroll);
+      float4 p[kUnroll];
+      bool valid[kUnroll];
+      uint32_t idx[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) {
+        const uint32_t i = base + k * 32 + lane;
+        valid[k] = i < a.n;
+        p[k] = valid[k] ? __ldcs(a.cloud + i) : make_float4(0.f, 0.f, -1.f, 0.f);
+        idx[k] = valid[k] ? __ldg(a.perm + i) : 0u;
+      }
+      stage_a(valid, p, idx);
+      drain();
     }
   }
 
-  // flush the tail of the queue
-  if (qn > 0) {
+  __syncwarp();
+  if (cn > 0) stage_b(cn);  // tail of the candidate queue
+  // flush the tail of the record queue
+  if (rn > 0) {
     unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)qn);
+    if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)rn);
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (lane < qn) a.records[base + lane] = q[lane];
+    if (lane < rn) a.records[base + lane] = rq[lane];
   }
-  // candidate count: warp reduce, one atomic per warp
-  for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
-  if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
+  if (kCount) {  // candidate count: warp reduce, one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
+    if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
+  }
 }
 
-void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, cudaStream_t s) {
-  if (a.active_blocks) scan_kernel<true><<<grid, kScanThreads, 0, s>>>(a, fp);
-  else scan_kernel<false><<<grid, kScanThreads, 0, s>>>(a, fp);
+void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s) {
+  if (a.active_blocks) {
+    if (count_candidates) scan_kernel<true, true><<<grid, kScanThreads, 0, s>>>(a, fp);
+    else scan_kernel<true, false><<<grid, kScanThreads, 0, s>>>(a, fp);
+  } else {
+    if (count_candidates) scan_kernel<false, true><<<grid, kScanThreads, 0, s>>>(a, fp);
+    else scan_kernel<false, false><<<grid, kScanThreads, 0, s>>>(a, fp);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -412,6 +582,6 @@ void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offset
 
 int scan_ctas_per_sm() {
   int occ = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcp::scan_kernel<false>, pcp::kScanThreads, 0) != cudaSuccess || occ < 1) occ = 2;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcp::scan_kernel<false, false>, pcp::kScanThreads, 0) != cudaSuccess || occ < 1) occ = 2;
   return occ;
 }

@@ -13,7 +13,8 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("name", COLORIZE_CASES)
 @pytest.mark.parametrize("accum", ["sum", "top5"])
-def test_colorize_golden(built_lib, name, accum):
+@pytest.mark.parametrize("count", [True, False])
+def test_colorize_golden(built_lib, name, accum, count):
     from pointcloudprocessor_b200 import api
     g = np.load(os.path.join(GOLD, f"colorize_{name}.npz"))
     sc = load_colorize_inputs(g)
@@ -22,10 +23,12 @@ def test_colorize_golden(built_lib, name, accum):
     with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), p) as gc:
         gc.set_cloud(sc["cloud"])
         for i in range(sc["f"]):
-            r = gc.submit_frame(sc["poses"][i], sc["images"][i], mask=sc["masks"][i], T_opt=sc["T_opt"], want_vis=True, want_pix=True)
+            r = gc.submit_frame(sc["poses"][i], sc["images"][i], mask=sc["masks"][i], T_opt=sc["T_opt"], want_vis=True, want_pix=True,
+                                count_candidates=count)
             assert np.array_equal(np.packbits(r["vis"], bitorder="little"), g[f"vis_{i}"]), f"frame {i} visibility"
             assert np.array_equal(r["pix"], g[f"pix_{i}"]), f"frame {i} pixel indices"
-            assert (r["n_candidates"], r["n_visible"], r["n_colored"]) == tuple(g["counts"][i])
+            assert (r["n_visible"], r["n_colored"]) == tuple(g["counts"][i][1:])
+            assert r["n_candidates"] == (g["counts"][i][0] if count else -1)
         acc, mh, mm = gc.accumulators()
         assert np.array_equal(acc, g["acc"])
         if sc["masks"][0] is not None:

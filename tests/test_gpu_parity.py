@@ -59,6 +59,21 @@ def test_c1_shape(oracle, built_lib):
     _run_pair(oracle, make_scene(1_000_000, 4, 1280, 720))
 
 
+def test_c1_shape_fast_variant(oracle, built_lib):
+    """The kernel variant that skips the n_candidates count (what the asynchronous path and the bench run)."""
+    from pointcloudprocessor_b200 import api
+    sc = make_scene(1_000_000, 4, 1280, 720)
+    oc = oracle.Colorizer(oracle.camera(sc["intr"], sc["dist"]), 1280, 720, sc["cloud"])
+    with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(1280, 720))) as gc:
+        gc.set_cloud(sc["cloud"])
+        for i, pose in enumerate(sc["poses"]):
+            ro = oc.frame(pose, sc["images"][i], want_vis=True, want_pix=True, threads=8)
+            rg = gc.submit_frame(pose, sc["images"][i], want_vis=True, want_pix=True, count_candidates=False)
+            assert rg["n_visible"] == ro["n_visible"] and rg["n_colored"] == ro["n_colored"]
+            assert np.array_equal(rg["vis"], ro["vis"]) and np.array_equal(rg["pix"], ro["pix"])
+        assert np.array_equal(gc.accumulators()[0], oc.accumulators()[0])
+
+
 def test_reference_cull_size(oracle, built_lib):
     # the reference passes a hard-coded 4096x3000 to ViewCulling whatever the image (cpp:525)
     _run_pair(oracle, make_scene(100_000, 2, 640, 480), cull_size=(4096, 3000))
