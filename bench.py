@@ -312,7 +312,7 @@ def run_native(args):
     # ---- roofline of the dominant kernel ------------------------------------------------------------------------------
     peak, peak_src = _peaks()
     frames_prof = max(prof["frames"], 1)
-    kern_ms = {"zgrid_init": prof["init_ms"] / frames_prof, "scan": prof["scan_ms"] / frames_prof, "resolve": prof["resolve_ms"] / frames_prof}
+    kern_ms = {"scan": prof["scan_ms"] / frames_prof, "resolve": prof["resolve_ms"] / frames_prof}
     dominant = max(kern_ms, key=kern_ms.get)
     Wc, Hc = W // prm.downsample, H // prm.downsample
     scan_bytes = 16.0 * n                                    # pass 1 reads every point once as float4

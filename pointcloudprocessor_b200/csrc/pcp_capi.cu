@@ -94,13 +94,14 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
     if ((e = cudaEventCreateWithFlags(&ctx->ev_free[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
   }
   const size_t cells = (size_t)ctx->Wc * ctx->Hc;
-  if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
-  if ((e = cudaMalloc(&ctx->d_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
-  if ((e = cudaMemset(ctx->d_counters, 0, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMemset", e);
+  if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * 2 * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
+  if ((e = cudaMalloc(&ctx->d_counters, 2 * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+  launch_zgrid_init(ctx->d_zgrid, 2 * (int)cells, ctx->d_counters, ctx->own_stream);  // both buffers start clean
+  if ((e = cudaStreamSynchronize(ctx->own_stream)) != cudaSuccess) return bail("zgrid init", e);
   if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
-  ctx->resolve_grid = ctx->sm_count * 4;
+  ctx->resolve_grid = ctx->sm_count * 8;
   {
     const char* e_np = std::getenv("PCP_NO_PREFILTER");
     ctx->prefilter = !(e_np && e_np[0] == '1');

@@ -41,8 +41,11 @@ struct pcp_ctx {
   int32_t* d_idx = nullptr;          // N, lazily allocated (pcp_cull)
   uint32_t* d_scratch = nullptr;     // compaction tile sums
 
-  unsigned long long* d_zgrid = nullptr;
-  pcp::FrameCounters* d_counters = nullptr;
+  // double-buffered per-frame scratch: frame f uses buffer f & 1; its resolve kernel re-initialises the other buffer for
+  // frame f+1, so a frame is two launches (scan, resolve) and no separate clear
+  unsigned long long* d_zgrid = nullptr;       // 2 x Wc*Hc packed (fl32 depth, point index) keys
+  pcp::FrameCounters* d_counters = nullptr;    // 2 entries
+  int buf = 0;
   pcp::FrameCounters* h_counters = nullptr;  // pinned
   uint32_t* d_total = nullptr;
 

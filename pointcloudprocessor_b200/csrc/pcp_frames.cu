@@ -95,18 +95,21 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
     }
     pe = &ctx->prof_events[ctx->prof_used];
     ctx->prof_used += 4;
-    CU(cudaEventRecord(pe[0], ctx->stream));
   }
-  launch_zgrid_init(ctx->d_zgrid, ctx->Wc * ctx->Hc, ctx->d_counters, ctx->stream);
+  const int cells = ctx->Wc * ctx->Hc;
+  const int b = ctx->buf;
+  ctx->buf ^= 1;
+  unsigned long long* zg = ctx->d_zgrid + (size_t)b * (cells ? cells : 1);
+  FrameCounters* ctr = ctx->d_counters + b;
   if (pe) CU(cudaEventRecord(pe[1], ctx->stream));
   ScanArgs sa;
   std::memset(&sa, 0, sizeof(sa));
   sa.cloud = ctx->d_cloud;
   sa.perm = nullptr;
   sa.active_blocks = nullptr;
-  sa.zgrid = ctx->d_zgrid;
+  sa.zgrid = zg;
   sa.records = ctx->d_records;
-  sa.counters = ctx->d_counters;
+  sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
   launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->stream);
   if (pe) CU(cudaEventRecord(pe[2], ctx->stream));
@@ -114,8 +117,11 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ResolveArgs ra;
   std::memset(&ra, 0, sizeof(ra));
   ra.records = ctx->d_records;
-  ra.zgrid = ctx->d_zgrid;
-  ra.counters = ctx->d_counters;
+  ra.zgrid = zg;
+  ra.counters = ctr;
+  ra.next_zgrid = ctx->d_zgrid + (size_t)(b ^ 1) * (cells ? cells : 1);
+  ra.next_counters = ctx->d_counters + (b ^ 1);
+  ra.cells = cells;
   ra.bgr = accumulate ? d_bgr : nullptr;
   ra.pitch = pitch;
   ra.mask = accumulate ? d_mask : nullptr;
@@ -133,13 +139,13 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ra.sample_mode = ctx->prm.sample_mode;
   launch_resolve(ra, fp, ctx->resolve_grid, ctx->stream);
   if (pe) CU(cudaEventRecord(pe[3], ctx->stream));
-  ctx->launches += 3;
+  ctx->launches += 2;
   CU(cudaGetLastError());
   return PCP_OK;
 }
 
 int fetch_outputs(pcp_ctx* ctx, pcp_frame_out* out) {
-  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters + (ctx->buf ^ 1), sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->visible_bits) CU(cudaMemcpyAsync(out->visible_bits, ctx->d_vis_bits, sizeof(uint32_t) * ((ctx->n + 31) / 32), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->pixel_index) CU(cudaMemcpyAsync(out->pixel_index, ctx->d_pix, sizeof(int32_t) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -275,7 +281,7 @@ int pcp_profile_read(pcp_ctx* ctx, double ms3[3], uint64_t* frames) {
   CU(cudaStreamSynchronize(ctx->stream));
   ms3[0] = ms3[1] = ms3[2] = 0.0;
   for (size_t i = 0; i + 4 <= ctx->prof_used; i += 4) {
-    for (int k = 0; k < 3; k++) {
+    for (int k = 1; k < 3; k++) {  // interval 0 (the separate z-grid clear) no longer exists: the resolve kernel clears
       float ms = 0.f;
       CU(cudaEventElapsedTime(&ms, ctx->prof_events[i + k], ctx->prof_events[i + k + 1]));
       ms3[k] += ms;

@@ -9,6 +9,7 @@ namespace pcp {
 
 // Initial z-grid key: fl32 FLT_MAX in the high word (view_culling.cpp:64), index 0xffffffff (= -1, :65).
 static constexpr unsigned long long kZInit = (0x7f7fffffull << 32) | 0xffffffffull;
+static constexpr unsigned int kZBoundInit = 0x7f7fffffu;  // FLT_MAX
 
 // One candidate that may still be visible after pass 1 (32 bytes, written/read as two 16-byte words).
 struct __align__(16) Record {
@@ -76,6 +77,9 @@ struct ResolveArgs {
   const Record* __restrict__ records;
   const unsigned long long* __restrict__ zgrid;
   FrameCounters* counters;
+  unsigned long long* next_zgrid;     // the other z-grid buffer, re-initialised here for the next frame
+  FrameCounters* next_counters;
+  int cells;
   const uint8_t* __restrict__ bgr; size_t pitch;
   const uint8_t* __restrict__ mask; size_t mask_pitch;
   uint4* acc;                 // N x {sum_r,sum_g,sum_b,count}

@@ -26,7 +26,7 @@ static constexpr int kCandCap = 32 * (PCP_UNROLL_CAP + 1); // per-warp candidate
 __global__ void zgrid_init_kernel(unsigned long long* zgrid, int cells, FrameCounters* counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < cells) zgrid[i] = kZInit;
-  if (i < (int)(sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(counters)[i] = 0u;
+  if (i < (int)(2 * sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(counters)[i] = 0u;
 }
 
 void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s) {
@@ -346,54 +346,82 @@ __device__ __forceinline__ void top_insert(const ResolveArgs& a, uint32_t idx, f
   }
 }
 
+// kRes records per thread, processed phase by phase so that the kRes independent chains of dependent loads (record ->
+// z-grid cell -> pixel -> accumulator) are in flight together: the kernel is latency-bound, not bandwidth-bound.
+static constexpr int kRes = 4;
+
 __global__ void __launch_bounds__(256) resolve_kernel(const ResolveArgs a, const __grid_constant__ FrameParams fp) {
   const unsigned int nrec = a.counters->n_records;
   unsigned int nvis = 0, ncol = 0;
-  for (unsigned int r = blockIdx.x * blockDim.x + threadIdx.x; r < nrec; r += gridDim.x * blockDim.x) {
-    const uint4* rp = reinterpret_cast<const uint4*>(a.records + r);
-    const uint4 w0 = __ldcs(rp), w1 = __ldcs(rp + 1);
-    Record rec;
-    *reinterpret_cast<uint4*>(&rec) = w0;
-    *(reinterpret_cast<uint4*>(&rec) + 1) = w1;
-    bool visible = true;
+  const unsigned int tile = blockDim.x * kRes;
+  for (unsigned int base = blockIdx.x * tile; base < nrec; base += gridDim.x * tile) {
+    Record rec[kRes];
+    bool live[kRes];
+#pragma unroll
+    for (int k = 0; k < kRes; k++) {
+      const unsigned int r = base + k * blockDim.x + threadIdx.x;
+      live[k] = r < nrec;
+      if (live[k]) {
+        const uint4* rp = reinterpret_cast<const uint4*>(a.records + r);
+        *reinterpret_cast<uint4*>(&rec[k]) = __ldcs(rp);
+        *(reinterpret_cast<uint4*>(&rec[k]) + 1) = __ldcs(rp + 1);
+      }
+    }
     if (fp.depth_culling) {
-      const float minf = __uint_as_float((unsigned int)(__ldg(a.zgrid + rec.cell) >> 32));
-      visible = !(rec.dist > __dadd_rn((double)minf, fp.tol));  // view_culling.cpp:157
+      unsigned int hi[kRes];
+#pragma unroll
+      for (int k = 0; k < kRes; k++) hi[k] = live[k] ? __ldg(reinterpret_cast<const unsigned int*>(a.zgrid) + 2 * rec[k].cell + 1) : 0u;
+#pragma unroll
+      for (int k = 0; k < kRes; k++)
+        live[k] = live[k] && !(rec[k].dist > __dadd_rn((double)__uint_as_float(hi[k]), fp.tol));  // view_culling.cpp:157
     }
-    if (!visible) continue;
-    nvis++;
-    if (a.vis_bits) atomicOr(a.vis_bits + (rec.idx >> 5), 1u << (rec.idx & 31));
-    int pix = rec.pix;
-    if (pix == -2) {  // a double T was applied for culling: generateColorMap projects the float point itself
-      double u, v;
-      project(fp.cam, (double)rec.x, (double)rec.y, (double)rec.z, u, v);
-      pix = color_pixel((double)rec.z, u, v, fp.imgW, fp.imgH);
+    int pv[kRes], pu[kRes];
+#pragma unroll
+    for (int k = 0; k < kRes; k++) {
+      if (!live[k]) continue;
+      nvis++;
+      if (a.vis_bits) atomicOr(a.vis_bits + (rec[k].idx >> 5), 1u << (rec[k].idx & 31));
+      int pix = rec[k].pix;
+      if (pix == -2) {  // a double T was applied for culling: generateColorMap projects the float point itself
+        double u, v;
+        project(fp.cam, (double)rec[k].x, (double)rec[k].y, (double)rec[k].z, u, v);
+        pix = color_pixel((double)rec[k].z, u, v, fp.imgW, fp.imgH);
+      }
+      live[k] = pix >= 0;
+      if (!live[k]) continue;
+      ncol++;
+      if (a.pix_out) a.pix_out[rec[k].idx] = pix;
+      pv[k] = pix / fp.imgW;
+      pu[k] = pix - pv[k] * fp.imgW;
     }
-    if (pix < 0) continue;
-    ncol++;
-    if (a.pix_out) a.pix_out[rec.idx] = pix;
     if (!a.bgr) continue;
-    const int pv = pix / fp.imgW, pu = pix - pv * fp.imgW;
-    const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
-    const uint32_t b = __ldg(px), g = __ldg(px + 1), rr = __ldg(px + 2);  // cpp:760-762
-    if (a.accum_mode == 0) {
-      uint4 s = a.acc[rec.idx];
-      s.x += rr; s.y += g; s.z += b; s.w += 1u;
-      a.acc[rec.idx] = s;
-    } else {
-      const float o = orientation_score(rec.x, rec.y, rec.z, fp.cam_pos[0], fp.cam_pos[1], fp.cam_pos[2]);
-      const float d = distance_score(rec.x, rec.y, rec.z);
-      top_insert(a, rec.idx, final_score(o, d), rr | (g << 8) | (b << 16), (uint32_t)fp.frame_index);
-      uint4 s = a.acc[rec.idx];
-      s.x += rr; s.y += g; s.z += b; s.w += 1u;
-      a.acc[rec.idx] = s;
+    uint32_t cb[kRes], cg[kRes], cr[kRes], mv[kRes];
+    uint4 s[kRes];
+#pragma unroll
+    for (int k = 0; k < kRes; k++) {
+      if (!live[k]) continue;
+      const uint8_t* px = a.bgr + (size_t)pv[k] * a.pitch + (size_t)pu[k] * 3;
+      cb[k] = __ldg(px); cg[k] = __ldg(px + 1); cr[k] = __ldg(px + 2);  // cpp:760-762
+      if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv[k] * a.mask_pitch + pu[k]);  // cpp:804
+      s[k] = a.acc[rec[k].idx];
     }
-    if (a.mask) {
-      const uint32_t mv = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);  // cpp:804
-      uint2 m = a.mask_acc[rec.idx];
-      m.x += (mv == 255u) ? 1u : 0u;                                       // cpp:806
-      m.y = mv > m.y ? mv : m.y;
-      a.mask_acc[rec.idx] = m;
+    // a point appears at most once per frame, so the accumulator update needs no atomics
+#pragma unroll
+    for (int k = 0; k < kRes; k++) {
+      if (!live[k]) continue;
+      s[k].x += cr[k]; s[k].y += cg[k]; s[k].z += cb[k]; s[k].w += 1u;
+      a.acc[rec[k].idx] = s[k];
+      if (a.accum_mode != 0) {
+        const float o = orientation_score(rec[k].x, rec[k].y, rec[k].z, fp.cam_pos[0], fp.cam_pos[1], fp.cam_pos[2]);
+        const float d = distance_score(rec[k].x, rec[k].y, rec[k].z);
+        top_insert(a, rec[k].idx, final_score(o, d), cr[k] | (cg[k] << 8) | (cb[k] << 16), (uint32_t)fp.frame_index);
+      }
+      if (a.mask) {
+        uint2 m = a.mask_acc[rec[k].idx];
+        m.x += (mv[k] == 255u) ? 1u : 0u;                                    // cpp:806
+        m.y = mv[k] > m.y ? mv[k] : m.y;
+        a.mask_acc[rec[k].idx] = m;
+      }
     }
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -404,6 +432,10 @@ __global__ void __launch_bounds__(256) resolve_kernel(const ResolveArgs a, const
     if (nvis) atomicAdd(&a.counters->n_visible, nvis);
     if (ncol) atomicAdd(&a.counters->n_colored, ncol);
   }
+  // clear the OTHER buffer for the next frame (nobody reads it during this kernel)
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.cells; i += gridDim.x * blockDim.x) a.next_zgrid[i] = kZInit;
+  if (blockIdx.x == 0 && threadIdx.x < sizeof(FrameCounters) / sizeof(unsigned int))
+    reinterpret_cast<unsigned int*>(a.next_counters)[threadIdx.x] = 0u;
 }
 
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s) {
