@@ -2,7 +2,7 @@
  *
  * The reference (ChunLI-666/PointCloudProcessor) has no FFI/plugin layer: its boundary is a C++ class API.
  * Each entry point below names the reference interface it replaces (paths relative to
- * /root/reference/PointCloudProcessor/).  The C++ facade in include/pcp/*.hpp re-creates those classes on
+ * /root/reference/PointCloudProcessor/).  The C++ facade in include/pcp/pcp.hpp re-creates those classes on
  * top of this ABI; INTEGRATION.md shows the binding a maintainer would add.
  *
  * Conventions: plain pointers and sizes only; every function returns a pcp_status (never throws);

@@ -1,0 +1,197 @@
+// pcp.hpp — header-only C++ facade over the C ABI of pcp.h with the reference's class and method names.
+//
+// PCL / OpenCV / Eigen are not available on this box, so their types are replaced by layout-compatible PODs:
+//   pcp::PointXYZI        == pcl::PointXYZI        (32 bytes: x y z pad | intensity pad pad pad)
+//   pcp::PointXYZRGB      == pcl::PointXYZRGB      (32 bytes: x y z pad | b g r a pad pad pad)
+//   pcp::PointXYZRGBMask  == PointXYZRGBMask       (include/FrameData.hpp:68-87)
+//   pcp::Isometry3d       == Eigen::Isometry3d     (double[16], column-major)
+//   pcp::Image            ~  cv::Mat               (8-bit, data/pitch/width/height/channels)
+// Errors: every failure of the C ABI is rethrown as std::runtime_error(pcp_last_error()), the convention main.cpp:64-68
+// already handles.  Citations are relative to /root/reference/PointCloudProcessor/.
+#ifndef PCP_PCP_HPP_
+#define PCP_PCP_HPP_
+
+#include <cstddef>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "pcp.h"
+
+namespace pcp {
+
+struct alignas(16) PointXYZI { float x, y, z, pad0; float intensity, pad1, pad2, pad3; };
+struct alignas(16) PointXYZRGB { float x, y, z, pad0; uint8_t b, g, r, a; float pad1, pad2, pad3; };
+struct alignas(16) PointXYZRGBMask { float x, y, z, pad0; uint8_t b, g, r, a; uint16_t segmentMask; uint16_t pad1; float pad2, pad3; };
+static_assert(sizeof(PointXYZI) == 32 && sizeof(PointXYZRGB) == 32 && sizeof(PointXYZRGBMask) == 32, "PCL point layouts");
+
+struct Isometry3d {
+  double m[16];  // column-major, Eigen's default
+  static Isometry3d Identity() { Isometry3d T{}; T.m[0] = T.m[5] = T.m[10] = T.m[15] = 1.0; return T; }
+  const double* data() const { return m; }
+};
+
+struct Image {
+  const uint8_t* data = nullptr;
+  int width = 0, height = 0, channels = 3;
+  size_t pitch = 0;  // bytes per row
+};
+
+// include/FrameData.hpp:9-12
+struct Pose { double x, y, z, qw, qx, qy, qz; };
+
+inline void check(int rc, pcp_ctx* ctx, const char* what) {
+  if (rc != PCP_OK) {
+    const char* msg = pcp_last_error(ctx);
+    throw std::runtime_error(std::string(what) + ": " + (msg ? msg : "error"));
+  }
+}
+
+}  // namespace pcp
+
+namespace camera {
+
+// camera::GenericCameraBase / create_camera (include/camera/create_camera.hpp:14, src/camera/create_camera.cpp:33-49)
+struct GenericCameraBase {
+  using ConstPtr = std::shared_ptr<const GenericCameraBase>;
+  pcp_camera cam{};
+};
+
+inline GenericCameraBase::ConstPtr create_camera(const std::string& camera_model, const std::vector<double>& intrinsics,
+                                                 const std::vector<double>& distortion_coeffs) {
+  if (camera_model != "pinhole") throw std::runtime_error("error: unknown camera model " + camera_model);
+  if (intrinsics.size() != 4) throw std::runtime_error("error: num of intrinsic parameters mismatch!!");
+  auto c = std::make_shared<GenericCameraBase>();
+  c->cam.fx = intrinsics[0]; c->cam.fy = intrinsics[1]; c->cam.cx = intrinsics[2]; c->cam.cy = intrinsics[3];
+  for (size_t i = 0; i < 5; i++) c->cam.dist[i] = i < distortion_coeffs.size() ? distortion_coeffs[i] : 0.0;  // create_camera.cpp:23-26
+  return c;
+}
+
+}  // namespace camera
+
+namespace pcp {
+
+// Device-resident state of pcdColorizationAndSmooth (src/PointCloudProcessor.cpp:474-602) on one GPU.
+class Colorizer {
+ public:
+  Colorizer(const camera::GenericCameraBase::ConstPtr& proj, const pcp_params& params, int device = 0) : params_(params) {
+    if (pcp_create(&ctx_, device, &proj->cam, &params) != PCP_OK) throw std::runtime_error(pcp_last_error(nullptr));
+  }
+  ~Colorizer() { pcp_destroy(ctx_); }
+  Colorizer(const Colorizer&) = delete;
+  Colorizer& operator=(const Colorizer&) = delete;
+
+  static pcp_params default_params(int image_width, int image_height) {
+    pcp_params p;
+    pcp_default_params(&p);
+    p.image_width = image_width; p.image_height = image_height;
+    return p;  // cull size stays the reference's hard-coded 4096x3000 (cpp:525) unless the caller changes it
+  }
+
+  pcp_ctx* handle() const { return ctx_; }
+  size_t size() const { return pcp_num_points(ctx_); }
+
+  // loadPointCloud (cpp:92-154)
+  void setCloud(const std::vector<PointXYZI>& cloud) {
+    check(pcp_set_cloud(ctx_, cloud.data(), cloud.size(), sizeof(PointXYZI), offsetof(PointXYZI, intensity)), ctx_, "pcp_set_cloud");
+  }
+  // one keyframe of the loop at cpp:488-595
+  void addFrame(const Pose& pose, const Image& bgr, const Image* mask = nullptr, const Isometry3d* T_opt = nullptr,
+                pcp_frame_out* out = nullptr) {
+    const double p7[7] = {pose.x, pose.y, pose.z, pose.qw, pose.qx, pose.qy, pose.qz};
+    check(pcp_submit_frame(ctx_, p7, T_opt ? T_opt->data() : nullptr, bgr.data, bgr.pitch, mask ? mask->data : nullptr,
+                           mask ? mask->pitch : 0, out), ctx_, "pcp_submit_frame");
+  }
+  // loop body of viewCullingAndSaveFilteredPcds (cpp:186-207): indices kept by the z-buffer culler, ascending
+  std::vector<int32_t> cullPose(const Pose& pose, const Isometry3d* T_opt = nullptr) {
+    const double p7[7] = {pose.x, pose.y, pose.z, pose.qw, pose.qx, pose.qy, pose.qz};
+    std::vector<int32_t> idx(size() ? size() : 1);
+    size_t m = 0;
+    check(pcp_cull_pose(ctx_, p7, T_opt ? T_opt->data() : nullptr, idx.data(), &m), ctx_, "pcp_cull_pose");
+    idx.resize(m);
+    return idx;
+  }
+  // smoothColors (cpp:604-631) + the information removePointsWithNoColor needs (hpp:238-252)
+  void smoothColors(std::vector<uint8_t>& rgb, std::vector<uint32_t>& count) {
+    rgb.resize(3 * size()); count.resize(size());
+    check(pcp_finalize(ctx_, rgb.data(), count.data()), ctx_, "pcp_finalize");
+  }
+  void allreduce() { check(pcp_allreduce(ctx_), ctx_, "pcp_allreduce"); }
+
+ private:
+  pcp_ctx* ctx_ = nullptr;
+  pcp_params params_;
+};
+
+}  // namespace pcp
+
+namespace vlcal {
+
+// include/vlcal/calib/view_culling.hpp:10-19
+struct ViewCullingParams {
+  bool enable_depth_buffer_culling = true;
+  double hidden_points_removal_max_z = 200.0;  // Katz HPR parameters: unused, the z-buffer culler replaces HPR (north_star b)
+};
+
+// vlcal::ViewCulling(proj, image_size, params).cull(points, T_camera_lidar) — include/vlcal/calib/view_culling.hpp:23-34,
+// z-buffer variant src/vlcal/calib/view_culling.cpp:52-174.
+class ViewCulling {
+ public:
+  ViewCulling(const camera::GenericCameraBase::ConstPtr& proj, int image_width, int image_height, const ViewCullingParams& params,
+              int device = 0) {
+    pcp_params p;
+    pcp_default_params(&p);
+    p.image_width = p.cull_width = image_width;
+    p.image_height = p.cull_height = image_height;
+    p.enable_depth_buffer_culling = params.enable_depth_buffer_culling ? 1 : 0;
+    c_.reset(new pcp::Colorizer(proj, p, device));
+  }
+  std::vector<pcp::PointXYZI> cull(const std::vector<pcp::PointXYZI>& points, const pcp::Isometry3d& T_camera_lidar) const {
+    c_->setCloud(points);
+    std::vector<int32_t> idx(points.size() ? points.size() : 1);
+    size_t m = 0;
+    pcp::check(pcp_cull(c_->handle(), nullptr, T_camera_lidar.data(), idx.data(), &m), c_->handle(), "pcp_cull");
+    std::vector<pcp::PointXYZI> out;
+    out.reserve(m);
+    for (size_t k = 0; k < m; k++) out.push_back(points[idx[k]]);  // ViewCulling::sample (view_culling.cpp:176-185)
+    return out;
+  }
+
+ private:
+  std::unique_ptr<pcp::Colorizer> c_;
+};
+
+// vlcal::NIDCost(proj, normalized_image, points, bins) — include/vlcal/costs/nid_cost.hpp:26-43 (value path, T = double).
+class NIDCost {
+ public:
+  NIDCost(pcp::Colorizer& ctx, const double* normalized_image, int width, int height, const std::vector<pcp::PointXYZI>& points,
+          int bins = 16) : ctx_(ctx.handle()) {
+    pcp::check(pcp_nid_create(ctx_, points.data(), points.size(), sizeof(pcp::PointXYZI), offsetof(pcp::PointXYZI, intensity),
+                              normalized_image, width, height, bins, &nid_), ctx_, "pcp_nid_create");
+  }
+  ~NIDCost() { pcp_nid_destroy(nid_); }
+  NIDCost(const NIDCost&) = delete;
+  NIDCost& operator=(const NIDCost&) = delete;
+  // bool operator()(const T* T_camera_lidar_params, T* residual) with Sophus parameter order {qx,qy,qz,qw,tx,ty,tz}
+  bool operator()(const double* T_camera_lidar_params, double* residual) const {
+    uint8_t ok = 0;
+    pcp::check(pcp_nid_eval(nid_, T_camera_lidar_params, 1, residual, &ok), ctx_, "pcp_nid_eval");
+    return ok != 0;
+  }
+  // B candidate poses per launch (what a batched line search or derivative-free search should call)
+  void evaluate(const double* params_Bx7, int B, double* nid_out, uint8_t* ok_out) const {
+    pcp::check(pcp_nid_eval(nid_, params_Bx7, B, nid_out, ok_out), ctx_, "pcp_nid_eval");
+  }
+  pcp_nid* handle() const { return nid_; }
+
+ private:
+  pcp_ctx* ctx_;
+  pcp_nid* nid_ = nullptr;
+};
+
+}  // namespace vlcal
+
+#endif  // PCP_PCP_HPP_

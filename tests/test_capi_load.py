@@ -75,3 +75,33 @@ def test_pose_matrices_equal_oracle(built_lib, oracle):
         assert np.array_equal(w_g, w_o) and np.array_equal(c_g, c_o)
         # sanity: w2c is the inverse of c2w
         assert np.abs(w_g.astype(np.float64) @ c_g.astype(np.float64) - np.eye(4)).max() < 1e-4
+
+
+def _build_facade(tmp_path, built_lib):
+    import subprocess
+    exe = str(tmp_path / "facade_smoke")
+    libdir = os.path.dirname(built_lib)
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "facade_smoke.cpp"),
+                           "-o", exe, "-L" + libdir, "-lpcp_b200", "-Wl,-rpath," + libdir])
+    return exe
+
+
+def test_cpp_facade_compiles_and_fails_loudly_without_gpu(tmp_path, built_lib):
+    """include/pcp/pcp.hpp (reference class names over the C ABI) compiles with -Wall -Werror, links, and without a CUDA
+    device rethrows the library's error (no CPU fallback)."""
+    import subprocess
+    import torch
+    exe = _build_facade(tmp_path, built_lib)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert "facade ok" in r.stdout
+    else:
+        assert r.returncode == 3 and "no CUDA device" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cpp_facade_on_gpu(tmp_path, built_lib):
+    import subprocess
+    r = subprocess.run([_build_facade(tmp_path, built_lib)], capture_output=True, text=True)
+    assert r.returncode == 0 and "facade ok" in r.stdout, r.stdout + r.stderr
