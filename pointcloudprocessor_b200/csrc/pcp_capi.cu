@@ -101,10 +101,12 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
-  ctx->resolve_grid = ctx->sm_count * 8;
+  ctx->resolve_grid = ctx->sm_count * 6;
   {
     const char* e_np = std::getenv("PCP_NO_PREFILTER");
     ctx->prefilter = !(e_np && e_np[0] == '1');
+    const char* e_ns = std::getenv("PCP_SMZ");  // opt-in: measured 75-81 us vs 74.5 us for scan_kernel at C2
+    ctx->use_smz = (e_ns && e_ns[0] == '1');
   }
   *out = ctx;
   return PCP_OK;

@@ -51,6 +51,7 @@ struct pcp_ctx {
 
   int scan_grid = 148 * 4, resolve_grid = 148 * 4;
   int frame_index = 0;
+  bool use_smz = false;   // shared-memory early-z scan kernel (PCP_SMZ=1 enables it when the grid fits)
   bool prefilter = true;  // FP32 pre-filter of the scan kernel (PCP_NO_PREFILTER=1 disables it: exact path for every point)
   uint64_t launches = 0;
   std::string err;

@@ -111,7 +111,13 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.records = ctx->d_records;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
-  launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->stream);
+  // shared-memory early-z variant when the z-grid's high words fit beside the queues (see scan_smz_kernel)
+  const bool smz = ctx->use_smz && fp.use_prefilter && fp.depth_culling && !fp.use_T && scan_smz_smem_bytes(cells) <= 232448;
+  if (smz) {
+    if (launch_scan_smz(sa, fp, ctx->sm_count, count_candidates, ctx->stream) != 0) { ctx->fail("scan_smz_kernel: cannot reserve shared memory"); return PCP_ECUDA; }
+  } else {
+    launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->stream);
+  }
   if (pe) CU(cudaEventRecord(pe[2], ctx->stream));
 
   ResolveArgs ra;

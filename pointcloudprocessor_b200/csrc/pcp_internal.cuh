@@ -97,6 +97,8 @@ struct ResolveArgs {
 
 void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s);
 void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s);
+size_t scan_smz_smem_bytes(int cells);
+int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
 void launch_finalize_sum(const uint4* acc, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);

@@ -11,6 +11,8 @@
 // Compiled with -fmad=false; every decision-making operation additionally uses explicit _rn intrinsics (pcp_math.cuh).
 #include "pcp_internal.cuh"
 
+#define PCP_SMZ_LOCALB 1  // scan_smz_kernel: stage B consults the shared-memory bound before talking to L2
+
 namespace pcp {
 
 #ifndef PCP_UNROLL
@@ -118,7 +120,7 @@ __device__ __forceinline__ unsigned int prefilter_b(const PreF& c, const PreA& a
 // Pass 1, stage B: the exact FP64 body for one camera-frame float point.  Returns true when a record must be emitted.
 // ---------------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long long* __restrict__ zgrid, float x, float y, float z,
-                                            uint32_t idx, Record& rec, bool& candidate) {
+                                            uint32_t idx, Record& rec, bool& candidate, unsigned int* zs = nullptr) {
   candidate = false;
   double X = (double)x, Y = (double)y, Z = (double)z;                // view_culling.cpp:33
   if (fp.use_T) transform_point_d(fp.T, (double)x, (double)y, (double)z, X, Y, Z);  // :37
@@ -142,10 +144,26 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
   const int cell = py * fp.Wc + px;
   const float df = __double2float_rn(dist);                           // :123
   const unsigned long long key = ((unsigned long long)__float_as_uint(df) << 32) | (unsigned long long)idx;
-  unsigned long long cur = __ldcg(zgrid + cell);                      // L2-coherent read: an upper bound of the final minimum
-  if (key < cur && dist <= 3.4028234663852886e+38) {                  // :118 (dist > FLT_MAX never enters the map)
-    const unsigned long long old = atomicMin(zgrid + cell, key);
-    cur = old < key ? old : key;
+  unsigned long long cur;
+#ifdef PCP_SMZ_LOCALB
+  if (zs) {
+    // shared-memory copy first: only a point that can lower (or tie) the SM's bound talks to L2 at all
+    const unsigned int local = zs[cell];
+    cur = ((unsigned long long)local << 32) | 0xffffffffull;
+    if (__float_as_uint(df) <= local && dist <= 3.4028234663852886e+38) {
+      const unsigned long long old = atomicMin(zgrid + cell, key);
+      cur = old < key ? old : key;
+      atomicMin(zs + cell, (unsigned int)(cur >> 32));
+    }
+  } else
+#endif
+  {
+    cur = __ldcg(zgrid + cell);                                       // L2-coherent read: an upper bound of the final minimum
+    if (key < cur && dist <= 3.4028234663852886e+38) {                // :118 (dist > FLT_MAX never enters the map)
+      const unsigned long long old = atomicMin(zgrid + cell, key);
+      cur = old < key ? old : key;
+    }
+    if (zs) atomicMin(zs + cell, (unsigned int)(cur >> 32));         // the SM's shared-memory copy learns what L2 knows
   }
   const float minf = __uint_as_float((unsigned int)(cur >> 32));
   if (dist > __dadd_rn((double)minf, fp.tol)) return false;           // :157 can only get stricter as the minimum decreases
@@ -314,6 +332,159 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// scan_smz_kernel: the same two stages with the early-z reads served from SHARED MEMORY.  One CTA of 32 warps per SM keeps
+// a private copy zs[cell] of the z-grid's high words (FP32 bit patterns, upper bounds of the final minima):
+//   * stage A reads it with LDS instead of a scattered global load (the L1/L2 latency of those reads was the top stall);
+//   * stage B, which talks to the authoritative 64-bit grid in L2 anyway, lowers zs[cell] to what it saw there;
+//   * after iterations 1, 2, 4, 8, ... the whole CTA re-reads the global grid (coalesced, ~8 B x cells) so that every SM
+//     learns the minima found by the others.  All warps run the same number of iterations, so the barriers are uniform.
+// Used when 144 KB of queues + 4 B x cells fit in the 227 KB of shared memory (<= ~21 k cells: every BASELINE config; the
+// reference's hard-coded 4096x3000 cull size has 62 k cells and takes scan_kernel).
+// ---------------------------------------------------------------------------------------------------------------------
+#ifndef PCP_SMZ_THREADS
+#define PCP_SMZ_THREADS 1024
+#endif
+static constexpr int kSmzThreads = PCP_SMZ_THREADS;
+static constexpr int kSmzWarps = kSmzThreads / 32;
+static constexpr size_t kSmzQueueBytes = (size_t)kSmzWarps * kCandCap * sizeof(float4) + (size_t)kSmzWarps * kQueueCap * sizeof(Record);
+
+template <bool kCount>
+__global__ void __launch_bounds__(kSmzThreads, 1) scan_smz_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+  extern __shared__ __align__(16) unsigned char smz_smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const unsigned int lt_mask = (1u << lane) - 1u;
+  float4* cq = reinterpret_cast<float4*>(smz_smem) + (size_t)warp * kCandCap;
+  Record* rq = reinterpret_cast<Record*>(smz_smem + (size_t)kSmzWarps * kCandCap * sizeof(float4)) + (size_t)warp * kQueueCap;
+  unsigned int* zs = reinterpret_cast<unsigned int*>(smz_smem + kSmzQueueBytes);
+  const int cells = fp.Wc * fp.Hc;
+  for (int i = threadIdx.x; i < cells; i += kSmzThreads) zs[i] = kZBoundInit;
+  __syncthreads();
+  int cn = 0, rn = 0;
+  unsigned int ncand = 0;
+
+  auto stage_b = [&](int cnt) {
+    Record rec;
+    bool cand = false, emit = false;
+    cn -= cnt;
+    if (lane < cnt) {
+      const float4 c = cq[cn + lane];
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, __float_as_uint(c.w), rec, cand, zs);
+    }
+    if (kCount) ncand += cand ? 1u : 0u;
+    const unsigned int m = __ballot_sync(0xffffffffu, emit);
+    if (m) {
+      if (emit) rq[rn + __popc(m & lt_mask)] = rec;
+      rn += __popc(m);
+      __syncwarp();
+      if (rn >= 32) {
+        unsigned int base = 0;
+        if (lane == 0) base = atomicAdd(&a.counters->n_records, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        rn -= 32;
+        const uint4* src = reinterpret_cast<const uint4*>(rq + rn);
+        uint4* dst = reinterpret_cast<uint4*>(a.records + base);
+        dst[lane] = src[lane];
+        dst[lane + 32] = src[lane + 32];
+        __syncwarp();
+      }
+    }
+  };
+
+  const unsigned long long per_iter = (unsigned long long)gridDim.x * kSmzThreads * kUnroll;
+  const uint32_t iters = (uint32_t)(((unsigned long long)a.n + per_iter - 1) / per_iter);
+  float4 p[kUnroll];
+  auto load_chunk = [&](uint32_t it) {
+    const unsigned long long b = ((unsigned long long)it * gridDim.x + blockIdx.x) * (kSmzThreads * kUnroll) + (unsigned long long)warp * (32 * kUnroll);
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      const unsigned long long i = b + k * 32 + lane;
+      p[k] = i < a.n ? __ldcs(a.cloud + i) : make_float4(0.f, 0.f, -1.f, 0.f);
+    }
+  };
+#ifdef PCP_SMZ_PIPE
+  load_chunk(0);
+#endif
+  for (uint32_t it = 0; it < iters; it++) {
+    const unsigned long long base64 = ((unsigned long long)it * gridDim.x + blockIdx.x) * (kSmzThreads * kUnroll) + (unsigned long long)warp * (32 * kUnroll);
+    bool valid[kUnroll];
+    uint32_t idx[kUnroll];
+#ifndef PCP_SMZ_PIPE
+    load_chunk(it);
+#endif
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      const unsigned long long i = base64 + k * 32 + lane;
+      valid[k] = i < a.n;
+      idx[k] = (uint32_t)i;
+    }
+    float x[kUnroll], y[kUnroll], z[kUnroll];
+    bool push[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      x[k] = p[k].x; y[k] = p[k].y; z[k] = p[k].z;
+      if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x[k], y[k], z[k]);  // pcl::transformPointCloud (cpp:521)
+    }
+#ifdef PCP_SMZ_PIPE
+    // the registers of p are free again: the next chunk's loads fly during the pre-filter and stage B of this one
+    if (it + 1 < iters) load_chunk(it + 1);
+#endif
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      const PreA pa = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
+      const unsigned int cur = (pa.flags & 1u) ? zs[pa.cell] : kZBoundInit;
+      const unsigned int f = prefilter_b<kCount>(fp.pre, pa, cur, true);
+      const bool front = valid[k] && !(z[k] < 0.0f);  // view_culling.cpp:76
+      push[k] = front && (f & 1u);
+      if (kCount) ncand += (front && (f & 2u)) ? 1u : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; k++) {
+      const unsigned int m = __ballot_sync(0xffffffffu, push[k]);
+      if (push[k]) cq[cn + __popc(m & lt_mask)] = make_float4(x[k], y[k], z[k], __uint_as_float(idx[k]));
+      cn += __popc(m);
+    }
+    __syncwarp();
+#pragma unroll 1
+    while (cn >= 32) stage_b(32);
+    if (((it + 1) & it) == 0 && it + 1 < iters) {  // after iterations 1, 2, 4, 8, ...: pull the other SMs' minima
+      __syncthreads();
+      const unsigned int* zhi = reinterpret_cast<const unsigned int*>(a.zgrid) + 1;
+      for (int i = threadIdx.x; i < cells; i += kSmzThreads) atomicMin(zs + i, __ldcg(zhi + 2 * i));
+      __syncthreads();
+    }
+  }
+
+  __syncwarp();
+  if (cn > 0) stage_b(cn);
+  if (rn > 0) {
+    unsigned int base = 0;
+    if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)rn);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (lane < rn) a.records[base + lane] = rq[lane];
+  }
+  if (kCount) {
+    for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
+    if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
+  }
+}
+
+size_t scan_smz_smem_bytes(int cells) { return kSmzQueueBytes + sizeof(unsigned int) * (size_t)(cells > 0 ? cells : 1); }
+
+int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s) {
+  static bool configured = false;
+  const size_t bytes = scan_smz_smem_bytes(fp.Wc * fp.Hc);
+  if (!configured) {
+    if (cudaFuncSetAttribute(scan_smz_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448) != cudaSuccess) return 1;
+    if (cudaFuncSetAttribute(scan_smz_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448) != cudaSuccess) return 1;
+    configured = true;
+  }
+  if (count_candidates) scan_smz_kernel<true><<<sm_count, kSmzThreads, bytes, s>>>(a, fp);
+  else scan_smz_kernel<false><<<sm_count, kSmzThreads, bytes, s>>>(a, fp);
+  return 0;
+}
+
 void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s) {
   if (a.active_blocks) {
     if (count_candidates) scan_kernel<true, true><<<grid, kScanThreads, 0, s>>>(a, fp);
@@ -347,80 +518,95 @@ __device__ __forceinline__ void top_insert(const ResolveArgs& a, uint32_t idx, f
 }
 
 // kRes records per thread, processed phase by phase so that the kRes independent chains of dependent loads (record ->
-// z-grid cell -> pixel -> accumulator) are in flight together: the kernel is latency-bound, not bandwidth-bound.
-static constexpr int kRes = 4;
+// z-grid cell -> pixel -> accumulator) are in flight together: the kernel is latency-bound, not bandwidth-bound.  Only the
+// fields every record needs (index, dist, cell, pixel) stay in registers; x,y,z are re-read for the rare paths that use
+// them (TOP5 scores, re-projection after a double T), which keeps the kernel at 3 CTAs per SM.
+#ifndef PCP_RES
+#define PCP_RES 4
+#endif
+#ifndef PCP_RES_CTAS
+#define PCP_RES_CTAS 3
+#endif
+static constexpr int kRes = PCP_RES;
 
-__global__ void __launch_bounds__(256) resolve_kernel(const ResolveArgs a, const __grid_constant__ FrameParams fp) {
+__global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const ResolveArgs a, const __grid_constant__ FrameParams fp) {
   const unsigned int nrec = a.counters->n_records;
   unsigned int nvis = 0, ncol = 0;
   const unsigned int tile = blockDim.x * kRes;
   for (unsigned int base = blockIdx.x * tile; base < nrec; base += gridDim.x * tile) {
-    Record rec[kRes];
+    uint32_t idx[kRes];
+    int cell[kRes], pix[kRes];
+    double dist[kRes];
     bool live[kRes];
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       const unsigned int r = base + k * blockDim.x + threadIdx.x;
       live[k] = r < nrec;
+      idx[k] = 0; cell[k] = 0; pix[k] = -1; dist[k] = 0.0;
       if (live[k]) {
         const uint4* rp = reinterpret_cast<const uint4*>(a.records + r);
-        *reinterpret_cast<uint4*>(&rec[k]) = __ldcs(rp);
-        *(reinterpret_cast<uint4*>(&rec[k]) + 1) = __ldcs(rp + 1);
+        const uint4 w0 = __ldcs(rp), w1 = __ldcs(rp + 1);
+        idx[k] = w0.w;
+        dist[k] = __hiloint2double((int)w1.y, (int)w1.x);
+        cell[k] = (int)w1.z;
+        pix[k] = (int)w1.w;
       }
     }
     if (fp.depth_culling) {
       unsigned int hi[kRes];
 #pragma unroll
-      for (int k = 0; k < kRes; k++) hi[k] = live[k] ? __ldg(reinterpret_cast<const unsigned int*>(a.zgrid) + 2 * rec[k].cell + 1) : 0u;
+      for (int k = 0; k < kRes; k++) hi[k] = live[k] ? __ldg(reinterpret_cast<const unsigned int*>(a.zgrid) + 2 * cell[k] + 1) : 0u;
 #pragma unroll
       for (int k = 0; k < kRes; k++)
-        live[k] = live[k] && !(rec[k].dist > __dadd_rn((double)__uint_as_float(hi[k]), fp.tol));  // view_culling.cpp:157
+        live[k] = live[k] && !(dist[k] > __dadd_rn((double)__uint_as_float(hi[k]), fp.tol));  // view_culling.cpp:157
     }
-    int pv[kRes], pu[kRes];
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       if (!live[k]) continue;
       nvis++;
-      if (a.vis_bits) atomicOr(a.vis_bits + (rec[k].idx >> 5), 1u << (rec[k].idx & 31));
-      int pix = rec[k].pix;
-      if (pix == -2) {  // a double T was applied for culling: generateColorMap projects the float point itself
+      if (a.vis_bits) atomicOr(a.vis_bits + (idx[k] >> 5), 1u << (idx[k] & 31));
+      if (pix[k] == -2) {  // a double T was applied for culling: generateColorMap projects the float point itself
+        const Record* rp = a.records + (base + k * blockDim.x + threadIdx.x);
+        const float rx = rp->x, ry = rp->y, rz = rp->z;
         double u, v;
-        project(fp.cam, (double)rec[k].x, (double)rec[k].y, (double)rec[k].z, u, v);
-        pix = color_pixel((double)rec[k].z, u, v, fp.imgW, fp.imgH);
+        project(fp.cam, (double)rx, (double)ry, (double)rz, u, v);
+        pix[k] = color_pixel((double)rz, u, v, fp.imgW, fp.imgH);
       }
-      live[k] = pix >= 0;
+      live[k] = pix[k] >= 0;
       if (!live[k]) continue;
       ncol++;
-      if (a.pix_out) a.pix_out[rec[k].idx] = pix;
-      pv[k] = pix / fp.imgW;
-      pu[k] = pix - pv[k] * fp.imgW;
+      if (a.pix_out) a.pix_out[idx[k]] = pix[k];
     }
     if (!a.bgr) continue;
-    uint32_t cb[kRes], cg[kRes], cr[kRes], mv[kRes];
+    uint32_t rgb[kRes], mv[kRes];
     uint4 s[kRes];
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       if (!live[k]) continue;
-      const uint8_t* px = a.bgr + (size_t)pv[k] * a.pitch + (size_t)pu[k] * 3;
-      cb[k] = __ldg(px); cg[k] = __ldg(px + 1); cr[k] = __ldg(px + 2);  // cpp:760-762
-      if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv[k] * a.mask_pitch + pu[k]);  // cpp:804
-      s[k] = a.acc[rec[k].idx];
+      const int pv = pix[k] / fp.imgW, pu = pix[k] - pv * fp.imgW;
+      const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
+      rgb[k] = (uint32_t)__ldg(px + 2) | ((uint32_t)__ldg(px + 1) << 8) | ((uint32_t)__ldg(px) << 16);  // r | g<<8 | b<<16 (cpp:760-762)
+      if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);  // cpp:804
+      s[k] = a.acc[idx[k]];
     }
     // a point appears at most once per frame, so the accumulator update needs no atomics
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       if (!live[k]) continue;
-      s[k].x += cr[k]; s[k].y += cg[k]; s[k].z += cb[k]; s[k].w += 1u;
-      a.acc[rec[k].idx] = s[k];
+      s[k].x += rgb[k] & 255u; s[k].y += (rgb[k] >> 8) & 255u; s[k].z += rgb[k] >> 16; s[k].w += 1u;
+      a.acc[idx[k]] = s[k];
       if (a.accum_mode != 0) {
-        const float o = orientation_score(rec[k].x, rec[k].y, rec[k].z, fp.cam_pos[0], fp.cam_pos[1], fp.cam_pos[2]);
-        const float d = distance_score(rec[k].x, rec[k].y, rec[k].z);
-        top_insert(a, rec[k].idx, final_score(o, d), cr[k] | (cg[k] << 8) | (cb[k] << 16), (uint32_t)fp.frame_index);
+        const Record* rp = a.records + (base + k * blockDim.x + threadIdx.x);
+        const float rx = rp->x, ry = rp->y, rz = rp->z;
+        const float o = orientation_score(rx, ry, rz, fp.cam_pos[0], fp.cam_pos[1], fp.cam_pos[2]);
+        const float d = distance_score(rx, ry, rz);
+        top_insert(a, idx[k], final_score(o, d), rgb[k], (uint32_t)fp.frame_index);
       }
       if (a.mask) {
-        uint2 m = a.mask_acc[rec[k].idx];
+        uint2 m = a.mask_acc[idx[k]];
         m.x += (mv[k] == 255u) ? 1u : 0u;                                    // cpp:806
         m.y = mv[k] > m.y ? mv[k] : m.y;
-        a.mask_acc[rec[k].idx] = m;
+        a.mask_acc[idx[k]] = m;
       }
     }
   }
