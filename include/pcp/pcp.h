@@ -48,7 +48,9 @@ typedef struct {
   int accum_mode;                  /* PCP_ACCUM_SUM (u32 sums+count, all-reducible) | PCP_ACCUM_TOP5 (cpp:604-631) */
   int sample_mode;                 /* PCP_SAMPLE_NEAREST (reference, cpp:752-762) | PCP_SAMPLE_BILINEAR (extension) */
   int top_m;                       /* 5 (cpp:615) */
-  int prebin;                      /* 1: sort the cloud into spatial blocks at set_cloud and cull blocks per frame */
+  int prebin;                      /* 1 (default): Morton-sort the device copy of the cloud into 128-point chunks with bounding
+                                    * boxes at set_cloud; chunks certainly behind the camera / outside the z-grid are skipped per
+                                    * frame.  Every output stays in the caller's point order.  0: keep the caller's order. */
   int reserved[7];
 } pcp_params;
 
@@ -116,7 +118,8 @@ int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[
 
 /* Raw accumulators: acc4 = N x {sum_r, sum_g, sum_b, count} u32; mask_hits/mask_max = N u32 (may be NULL). */
 int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint32_t* mask_max);
-/* Device pointer of the N x 4 u32 accumulator array (original point order), e.g. for an external all-reduce. */
+/* Device pointer of the N x 4 u32 accumulator array, e.g. for an external all-reduce.  With prebin = 1 the array is in the
+ * library's sorted order (identical on every rank that holds the same cloud); pcp_get_accumulators un-permutes. */
 void* pcp_accumulators_device(pcp_ctx* ctx);
 int pcp_reset_accumulators(pcp_ctx* ctx);
 

@@ -47,7 +47,7 @@ void pcp_default_params(pcp_params* p) {
   p->accum_mode = PCP_ACCUM_SUM;
   p->sample_mode = PCP_SAMPLE_NEAREST;
   p->top_m = 5;
-  p->prebin = 0;
+  p->prebin = 1;  // Morton-sorted chunks with AABBs; PCP_NO_PREBIN=1 or prebin = 0 keeps the caller's order on the device
 }
 
 int pcp_abi_version(void) { return PCP_ABI_VERSION; }
@@ -176,9 +176,34 @@ int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[
 // ---------------------------------------------------------------------------------------------------------------------
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
-  F(d_cloud); F(d_perm); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
+  F(d_cloud); F(d_perm); F(d_aabb); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
   F(d_pix); F(d_idx); F(d_scratch);
   n = 0;
+}
+
+// Sort the uploaded cloud into Morton chunks (pcp_prebin.cu).  Called after every upload, before the accumulators are reset.
+static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
+  const char* e_np = std::getenv("PCP_NO_PREBIN");
+  const bool on = ctx->prm.prebin != 0 && !(e_np && e_np[0] == '1') && n > 0;
+  if (!on) {
+    if (ctx->d_perm) { cudaFree(ctx->d_perm); ctx->d_perm = nullptr; }
+    if (ctx->d_aabb) { cudaFree(ctx->d_aabb); ctx->d_aabb = nullptr; }
+    ctx->n_chunks = 0;
+    return PCP_OK;
+  }
+  const uint32_t n_chunks = (uint32_t)((n + kChunk - 1) / kChunk);
+  if (!ctx->d_perm) CU(cudaMalloc(&ctx->d_perm, sizeof(uint32_t) * n));
+  if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
+  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->sm_count, ctx->stream));
+  ctx->n_chunks = n_chunks;
+  // odd multiplier coprime with n_chunks: the visiting order (slot * mul) % n_chunks is a permutation of the chunks
+  auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };
+  uint32_t mul = 1;
+  for (uint32_t cand : {40503u, 7919u, 7907u, 6007u, 5003u, 4001u, 3001u, 2003u, 1009u, 509u, 251u, 127u, 61u, 31u, 13u, 7u, 3u})
+    if (cand < n_chunks && gcd(cand, n_chunks) == 1) { mul = cand; break; }
+  ctx->chunk_mul = mul;
+  ctx->launches += 5;
+  return PCP_OK;
 }
 
 static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
@@ -242,6 +267,10 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
       if (e != cudaSuccess) { ctx->fail("pcp_set_cloud: upload failed: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
     }
   }
+  {
+    const int rc = prebin_if_enabled(ctx, n);
+    if (rc != PCP_OK) return rc;
+  }
   if (reuse) return pcp_reset_accumulators(ctx);
   return alloc_cloud_state(ctx, n);
 }
@@ -253,6 +282,10 @@ int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n) {
   ctx->free_cloud();
   CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * (n ? n : 1)));
   if (n) CU(cudaMemcpyAsync(ctx->d_cloud, d_xyzi, sizeof(float4) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+  {
+    const int rc = prebin_if_enabled(ctx, n);
+    if (rc != PCP_OK) return rc;
+  }
   return alloc_cloud_state(ctx, n);
 }
 

@@ -105,14 +105,16 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ScanArgs sa;
   std::memset(&sa, 0, sizeof(sa));
   sa.cloud = ctx->d_cloud;
-  sa.perm = nullptr;
-  sa.active_blocks = nullptr;
+  sa.perm = ctx->d_perm;
+  sa.aabb = ctx->d_perm ? ctx->d_aabb : nullptr;
+  sa.n_chunks = ctx->n_chunks;
+  sa.chunk_mul = ctx->chunk_mul;
   sa.zgrid = zg;
   sa.records = ctx->d_records;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
   // shared-memory early-z variant when the z-grid's high words fit beside the queues (see scan_smz_kernel)
-  const bool smz = ctx->use_smz && fp.use_prefilter && fp.depth_culling && !fp.use_T && scan_smz_smem_bytes(cells) <= 232448;
+  const bool smz = ctx->use_smz && !ctx->d_perm && fp.use_prefilter && fp.depth_culling && !fp.use_T && scan_smz_smem_bytes(cells) <= 232448;
   if (smz) {
     if (launch_scan_smz(sa, fp, ctx->sm_count, count_candidates, ctx->stream) != 0) { ctx->fail("scan_smz_kernel: cannot reserve shared memory"); return PCP_ECUDA; }
   } else {
@@ -125,6 +127,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ra.records = ctx->d_records;
   ra.zgrid = zg;
   ra.counters = ctr;
+  ra.perm = ctx->d_perm;
   ra.next_zgrid = ctx->d_zgrid + (size_t)(b ^ 1) * (cells ? cells : 1);
   ra.next_counters = ctx->d_counters + (b ^ 1);
   ra.cells = cells;
@@ -259,17 +262,30 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
-  if (acc4) CU(cudaMemcpyAsync(acc4, ctx->d_acc, sizeof(uint4) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (ctx->n == 0) return PCP_OK;
+  // per-point state lives in sorted order when the cloud is pre-binned: hand it back in the caller's order
+  uint32_t* d_tmp = nullptr;
+  if (ctx->d_perm) CU(cudaMalloc(&d_tmp, sizeof(uint4) * ctx->n));
+  if (acc4) {
+    const void* src = ctx->d_acc;
+    if (ctx->d_perm) { launch_unpermute(reinterpret_cast<const uint32_t*>(ctx->d_acc), ctx->d_perm, (uint32_t)ctx->n, 4, d_tmp, ctx->stream); src = d_tmp; }
+    CU(cudaMemcpyAsync(acc4, src, sizeof(uint4) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+  }
   CU(cudaStreamSynchronize(ctx->stream));
   if (mask_hits || mask_max) {
     std::vector<uint2> tmp(ctx->n);
-    if (ctx->d_mask_acc) CU(cudaMemcpy(tmp.data(), ctx->d_mask_acc, sizeof(uint2) * ctx->n, cudaMemcpyDeviceToHost));
-    else std::memset(tmp.data(), 0, sizeof(uint2) * ctx->n);
+    if (ctx->d_mask_acc) {
+      const void* src = ctx->d_mask_acc;
+      if (ctx->d_perm) { launch_unpermute(reinterpret_cast<const uint32_t*>(ctx->d_mask_acc), ctx->d_perm, (uint32_t)ctx->n, 2, d_tmp, ctx->stream); src = d_tmp; }
+      CU(cudaMemcpyAsync(tmp.data(), src, sizeof(uint2) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+      CU(cudaStreamSynchronize(ctx->stream));
+    } else std::memset(tmp.data(), 0, sizeof(uint2) * ctx->n);
     for (size_t i = 0; i < ctx->n; i++) {
       if (mask_hits) mask_hits[i] = tmp[i].x;
       if (mask_max) mask_max[i] = tmp[i].y;
     }
   }
+  if (d_tmp) cudaFree(d_tmp);
   return PCP_OK;
 }
 
@@ -303,8 +319,8 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
-  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->stream);
-  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->stream);
+  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
   ctx->launches++;
   CU(cudaGetLastError());
   return PCP_OK;
@@ -320,8 +336,8 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
   uint32_t* d_cnt = nullptr;
   if (rgb_out) CU(cudaMallocAsync(&d_rgb, n * 3, ctx->stream));
   if (count_out) CU(cudaMallocAsync(&d_cnt, n * sizeof(uint32_t), ctx->stream));
-  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, (uint32_t)n, d_rgb, d_cnt, ctx->stream);
-  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm, (uint32_t)n, d_rgb, d_cnt, ctx->stream);
+  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
   ctx->launches++;
   if (rgb_out) CU(cudaMemcpyAsync(rgb_out, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream));
   if (count_out) CU(cudaMemcpyAsync(count_out, d_cnt, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));

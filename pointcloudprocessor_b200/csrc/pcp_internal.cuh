@@ -10,6 +10,7 @@ namespace pcp {
 // Initial z-grid key: fl32 FLT_MAX in the high word (view_culling.cpp:64), index 0xffffffff (= -1, :65).
 static constexpr unsigned long long kZInit = (0x7f7fffffull << 32) | 0xffffffffull;
 static constexpr unsigned int kZBoundInit = 0x7f7fffffu;  // FLT_MAX
+static constexpr int kChunk = 128;  // points per pre-binned chunk = one warp iteration of the scan kernel (4 x 32)
 
 // One candidate that may still be visible after pass 1 (32 bytes, written/read as two 16-byte words).
 struct __align__(16) Record {
@@ -65,18 +66,20 @@ struct FrameParams {
 struct ScanArgs {
   const float4* __restrict__ cloud;   // N x {x,y,z,intensity}, possibly block-sorted
   const uint32_t* __restrict__ perm;  // sorted position -> original index (null when not pre-binned)
-  const uint32_t* __restrict__ active_blocks;  // list of block ids to scan (null = all points)
+  const float4* __restrict__ aabb;    // pre-binned: 2 float4 per chunk {lo.xyz, nonfinite}, {hi.xyz, count}; null otherwise
+  uint32_t n_chunks;                  // ceil(n / kChunk)
+  uint32_t chunk_mul;                 // odd multiplier coprime with n_chunks: chunk visited at slot s is (s * chunk_mul) % n_chunks
   unsigned long long* zgrid;          // Wc*Hc packed keys
   Record* records;
   FrameCounters* counters;
   uint32_t n;
-  uint32_t block_points;              // points per spatial block (pre-binned mode)
 };
 
 struct ResolveArgs {
   const Record* __restrict__ records;
   const unsigned long long* __restrict__ zgrid;
   FrameCounters* counters;
+  const uint32_t* __restrict__ perm;  // pre-binned: record.idx is a sorted position; outputs in caller order go through perm
   unsigned long long* next_zgrid;     // the other z-grid buffer, re-initialised here for the next frame
   FrameCounters* next_counters;
   int cells;
@@ -101,9 +104,12 @@ size_t scan_smz_smem_bytes(int cells);
 int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
-void launch_finalize_sum(const uint4* acc, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);
-void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, uint32_t n, int top_m, uint8_t* rgb,
-                         uint32_t* count, cudaStream_t s);
+void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);
+void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
+                         uint8_t* rgb, uint32_t* count, cudaStream_t s);
+// pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, int sm_count, cudaStream_t s);
+void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s);
 // ascending index list from a visibility bitmask; returns through d_total the number of set bits
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,
                          uint32_t* d_total, cudaStream_t s);

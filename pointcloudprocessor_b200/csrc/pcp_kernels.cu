@@ -10,6 +10,7 @@
 //
 // Compiled with -fmad=false; every decision-making operation additionally uses explicit _rn intrinsics (pcp_math.cuh).
 #include "pcp_internal.cuh"
+#include "pcp_chunk.cuh"
 
 #define PCP_SMZ_LOCALB 1  // scan_smz_kernel: stage B consults the shared-memory bound before talking to L2
 
@@ -119,8 +120,10 @@ __device__ __forceinline__ unsigned int prefilter_b(const PreF& c, const PreA& a
 // ---------------------------------------------------------------------------------------------------------------------
 // Pass 1, stage B: the exact FP64 body for one camera-frame float point.  Returns true when a record must be emitted.
 // ---------------------------------------------------------------------------------------------------------------------
+// `idx` goes into the record (the accumulator slot: original index, or sorted position when pre-binned); `key_idx` is the
+// ORIGINAL point index and goes into the packed z-grid key, so that ties resolve identically whatever the storage order.
 __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long long* __restrict__ zgrid, float x, float y, float z,
-                                            uint32_t idx, Record& rec, bool& candidate, unsigned int* zs = nullptr) {
+                                            uint32_t idx, uint32_t key_idx, Record& rec, bool& candidate, unsigned int* zs = nullptr) {
   candidate = false;
   double X = (double)x, Y = (double)y, Z = (double)z;                // view_culling.cpp:33
   if (fp.use_T) transform_point_d(fp.T, (double)x, (double)y, (double)z, X, Y, Z);  // :37
@@ -143,7 +146,7 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
   const double dist = norm3(X, Y, Z);                                 // :102
   const int cell = py * fp.Wc + px;
   const float df = __double2float_rn(dist);                           // :123
-  const unsigned long long key = ((unsigned long long)__float_as_uint(df) << 32) | (unsigned long long)idx;
+  const unsigned long long key = ((unsigned long long)__float_as_uint(df) << 32) | (unsigned long long)key_idx;
   unsigned long long cur;
 #ifdef PCP_SMZ_LOCALB
   if (zs) {
@@ -191,6 +194,7 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
 #define PCP_ZLOAD(p) __ldca(p)
 #endif
 static constexpr int kUnroll = PCP_UNROLL;
+static_assert(kUnroll * 32 == kChunk, "one pre-binned chunk = one warp iteration");
 
 template <bool kPrebin, bool kCount>
 __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
@@ -213,7 +217,8 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
     cn -= cnt;
     if (lane < cnt) {
       const float4 c = cq[cn + lane];
-      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, __float_as_uint(c.w), rec, cand);
+      const uint32_t slot = __float_as_uint(c.w);
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, kPrebin ? __ldg(a.perm + slot) : slot, rec, cand);
     }
     if (kCount) ncand += cand ? 1u : 0u;
     const unsigned int m = __ballot_sync(0xffffffffu, emit);
@@ -296,24 +301,43 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
       drain();
     }
   } else {
-    const uint32_t nact = a.counters->n_active_blocks;
-    const uint32_t chunks_per_block = a.block_points / (32 * kUnroll);
-    const uint32_t total = nact * chunks_per_block;
-    for (uint32_t w = blockIdx.x * kWarpsPerCta + warp; w < total; w += gridDim.x * kWarpsPerCta) {
-      const uint32_t blk = a.active_blocks[w / chunks_per_block];
-      const uint32_t base = blk * a.block_points + (w % chunks_per_block) * (32 * kUnroll);
-      float4 p[kUnroll];
-      bool valid[kUnroll];
-      uint32_t idx[kUnroll];
-#pragma unroll
-      for (int k = 0; k < kUnroll; k++) {
-        const uint32_t i = base + k * 32 + lane;
-        valid[k] = i < a.n;
-        p[k] = valid[k] ? __ldcs(a.cloud + i) : make_float4(0.f, 0.f, -1.f, 0.f);
-        idx[k] = valid[k] ? __ldg(a.perm + i) : 0u;
+    // Pre-binned cloud: slot s of the chunk sequence is chunk (s * chunk_mul) % n_chunks, so that the chunks in flight at
+    // any moment are spread over the whole map (the early-z statistics of a shuffled cloud, at chunk granularity) while
+    // the 128 points of one warp iteration are spatial neighbours.  Warp w owns slots w, w + W, w + 2W, ...; 32 of them
+    // are classified at once, one per lane, and only the chunks that are not certainly culled are read.
+    const uint32_t total_warps = gridDim.x * kWarpsPerCta;
+    const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
+    const bool prefilter_chunks = prefilter_on;  // with a double T (pcp_cull) the gate is taken after T: no chunk culling
+    for (unsigned long long s0 = gw; s0 < a.n_chunks; s0 += 32ull * total_warps) {
+      const unsigned long long slot = s0 + (unsigned long long)lane * total_warps;
+      uint32_t chunk = 0xffffffffu;
+      int cls = kChunkSkip;
+      if (slot < a.n_chunks) {
+        chunk = (uint32_t)((slot * a.chunk_mul) % a.n_chunks);
+        cls = kChunkProcess;
+        if (prefilter_chunks) {
+          const float4 a0 = __ldg(a.aabb + 2 * chunk), a1 = __ldg(a.aabb + 2 * chunk + 1);
+          cls = classify_chunk(fp, a0, a1, kCount);
+          if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
+        }
       }
-      stage_a(valid, p, idx);
-      drain();
+      unsigned int todo = __ballot_sync(0xffffffffu, cls == kChunkProcess);
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t base = __shfl_sync(0xffffffffu, chunk, src) * kChunk;
+        float4 p[kUnroll];
+        bool valid[kUnroll];
+        uint32_t idx[kUnroll];
+#pragma unroll
+        for (int k = 0; k < kUnroll; k++) {
+          idx[k] = base + k * 32 + lane;  // sorted position: the accumulator slot
+          valid[k] = idx[k] < a.n;
+          p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
+        }
+        stage_a(valid, p, idx);
+        drain();
+      }
     }
   }
 
@@ -370,7 +394,7 @@ __global__ void __launch_bounds__(kSmzThreads, 1) scan_smz_kernel(const ScanArgs
     cn -= cnt;
     if (lane < cnt) {
       const float4 c = cq[cn + lane];
-      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, __float_as_uint(c.w), rec, cand, zs);
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, __float_as_uint(c.w), __float_as_uint(c.w), rec, cand, zs);
     }
     if (kCount) ncand += cand ? 1u : 0u;
     const unsigned int m = __ballot_sync(0xffffffffu, emit);
@@ -486,7 +510,7 @@ int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool
 }
 
 void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s) {
-  if (a.active_blocks) {
+  if (a.aabb) {
     if (count_candidates) scan_kernel<true, true><<<grid, kScanThreads, 0, s>>>(a, fp);
     else scan_kernel<true, false><<<grid, kScanThreads, 0, s>>>(a, fp);
   } else {
@@ -564,7 +588,8 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
     for (int k = 0; k < kRes; k++) {
       if (!live[k]) continue;
       nvis++;
-      if (a.vis_bits) atomicOr(a.vis_bits + (idx[k] >> 5), 1u << (idx[k] & 31));
+      const uint32_t orig = (a.vis_bits || a.pix_out) ? (a.perm ? __ldg(a.perm + idx[k]) : idx[k]) : 0u;  // caller's index
+      if (a.vis_bits) atomicOr(a.vis_bits + (orig >> 5), 1u << (orig & 31));
       if (pix[k] == -2) {  // a double T was applied for culling: generateColorMap projects the float point itself
         const Record* rp = a.records + (base + k * blockDim.x + threadIdx.x);
         const float rx = rp->x, ry = rp->y, rz = rp->z;
@@ -575,7 +600,7 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
       live[k] = pix[k] >= 0;
       if (!live[k]) continue;
       ncol++;
-      if (a.pix_out) a.pix_out[idx[k]] = pix[k];
+      if (a.pix_out) a.pix_out[orig] = pix[k];
     }
     if (!a.bgr) continue;
     uint32_t rgb[kRes], mv[kRes];
@@ -647,29 +672,33 @@ void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t iof
 // ---------------------------------------------------------------------------------------------------------------------
 // Finalize.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void finalize_sum_kernel(const uint4* __restrict__ acc, uint32_t n, uint8_t* __restrict__ rgb, uint32_t* __restrict__ count) {
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint4 s = acc[i];
+__global__ void finalize_sum_kernel(const uint4* __restrict__ acc, const uint32_t* __restrict__ perm, uint32_t n, uint8_t* __restrict__ rgb,
+                                    uint32_t* __restrict__ count) {
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const uint4 s = acc[j];
+    const uint32_t i = perm ? perm[j] : j;  // outputs in the caller's point order
     uint32_t r = 0, g = 0, b = 0;
     if (s.w) { r = s.x / s.w; g = s.y / s.w; b = s.z / s.w; }
     if (rgb) { rgb[3 * (size_t)i] = (uint8_t)r; rgb[3 * (size_t)i + 1] = (uint8_t)g; rgb[3 * (size_t)i + 2] = (uint8_t)b; }
     if (count) count[i] = s.w;
   }
 }
-void launch_finalize_sum(const uint4* acc, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s) {
+void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s) {
   if (n == 0) return;
   const int grid = (n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16;
-  finalize_sum_kernel<<<grid, 256, 0, s>>>(acc, n, rgb, count);
+  finalize_sum_kernel<<<grid, 256, 0, s>>>(acc, perm, n, rgb, count);
 }
 
 // smoothColors (cpp:612-629): slots are already sorted by (score desc, frame asc); weighted mean in float, truncation.
 __global__ void finalize_top_kernel(const float* __restrict__ score, const uint32_t* __restrict__ rgbf, const uint32_t* __restrict__ frame,
-                                    uint32_t n, int top_m, uint8_t* __restrict__ rgb, uint32_t* __restrict__ count) {
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+                                    const uint32_t* __restrict__ perm, uint32_t n, int top_m, uint8_t* __restrict__ rgb,
+                                    uint32_t* __restrict__ count) {
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const uint32_t i = perm ? perm[j] : j;  // outputs in the caller's point order
     float total = 0.f, r = 0.f, g = 0.f, b = 0.f;
     uint32_t m = 0;
     for (int k = 0; k < top_m; k++) {
-      const size_t o = (size_t)k * n + i;
+      const size_t o = (size_t)k * n + j;
       if (frame[o] == 0xffffffffu) break;
       const float s = score[o];
       const uint32_t c = rgbf[o];
@@ -689,11 +718,24 @@ __global__ void finalize_top_kernel(const float* __restrict__ score, const uint3
     if (count) count[i] = m;
   }
 }
-void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, uint32_t n, int top_m, uint8_t* rgb,
-                         uint32_t* count, cudaStream_t s) {
+void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
+                         uint8_t* rgb, uint32_t* count, cudaStream_t s) {
   if (n == 0) return;
   const int grid = (n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16;
-  finalize_top_kernel<<<grid, 256, 0, s>>>(score, rgbf, frame, n, top_m, rgb, count);
+  finalize_top_kernel<<<grid, 256, 0, s>>>(score, rgbf, frame, perm, n, top_m, rgb, count);
+}
+
+// Per-point arrays kept in sorted order (pre-binned cloud) -> the caller's order: dst[perm[j]] = src[j], `w` words each.
+__global__ void unpermute_kernel(const uint32_t* __restrict__ src, const uint32_t* __restrict__ perm, uint32_t n, int w, uint32_t* __restrict__ dst) {
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const size_t o = (size_t)perm[j] * w, i = (size_t)j * w;
+    for (int k = 0; k < w; k++) dst[o + k] = src[i + k];
+  }
+}
+void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s) {
+  if (n == 0) return;
+  const int grid = (n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16;
+  unpermute_kernel<<<grid, 256, 0, s>>>(src, perm, n, elem_words, dst);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

@@ -58,6 +58,23 @@ def test_colorize_golden_async_path(built_lib, name):
         assert np.array_equal(gc.finalize(want_count=False), g["rgb_sum"])
 
 
+@pytest.mark.parametrize("name", COLORIZE_CASES)
+def test_colorize_golden_caller_order(built_lib, name):
+    """prebin = 0: the device copy keeps the caller's point order (no chunk culling); same bits."""
+    from pointcloudprocessor_b200 import api
+    g = np.load(os.path.join(GOLD, f"colorize_{name}.npz"))
+    sc = load_colorize_inputs(g)
+    p = api.default_params(image_size=(sc["W"], sc["H"]), cull_size=sc["cull_size"], downsample=sc["ds"], depth_tolerance=sc["tol"], prebin=0)
+    with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), p) as gc:
+        gc.set_cloud(sc["cloud"])
+        for i in range(sc["f"]):
+            r = gc.submit_frame(sc["poses"][i], sc["images"][i], mask=sc["masks"][i], T_opt=sc["T_opt"], want_vis=True, want_pix=True)
+            assert np.array_equal(np.packbits(r["vis"], bitorder="little"), g[f"vis_{i}"]) and np.array_equal(r["pix"], g[f"pix_{i}"])
+            assert (r["n_candidates"], r["n_visible"], r["n_colored"]) == tuple(g["counts"][i])
+        assert np.array_equal(gc.accumulators()[0], g["acc"])
+        assert np.array_equal(gc.finalize(want_count=False), g["rgb_sum"])
+
+
 def test_edge_golden(built_lib):
     from pointcloudprocessor_b200 import api, synth
     g = np.load(os.path.join(GOLD, "edge_points.npz"))
