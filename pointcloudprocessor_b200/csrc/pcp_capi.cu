@@ -176,7 +176,7 @@ int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[
 // ---------------------------------------------------------------------------------------------------------------------
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
-  F(d_cloud); F(d_perm); F(d_aabb); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
+  F(d_cloud); F(d_perm); F(d_aabb); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
   F(d_pix); F(d_idx); F(d_scratch);
   n = 0;
 }
@@ -188,12 +188,14 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   if (!on) {
     if (ctx->d_perm) { cudaFree(ctx->d_perm); ctx->d_perm = nullptr; }
     if (ctx->d_aabb) { cudaFree(ctx->d_aabb); ctx->d_aabb = nullptr; }
+    if (ctx->d_active) { cudaFree(ctx->d_active); ctx->d_active = nullptr; }
     ctx->n_chunks = 0;
     return PCP_OK;
   }
   const uint32_t n_chunks = (uint32_t)((n + kChunk - 1) / kChunk);
   if (!ctx->d_perm) CU(cudaMalloc(&ctx->d_perm, sizeof(uint32_t) * n));
   if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
+  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint32_t) * n_chunks));
   CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->sm_count, ctx->stream));
   ctx->n_chunks = n_chunks;
   // odd multiplier coprime with n_chunks: the visiting order (slot * mul) % n_chunks is a permutation of the chunks

@@ -107,6 +107,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.cloud = ctx->d_cloud;
   sa.perm = ctx->d_perm;
   sa.aabb = ctx->d_perm ? ctx->d_aabb : nullptr;
+  sa.active = ctx->d_active;
   sa.n_chunks = ctx->n_chunks;
   sa.chunk_mul = ctx->chunk_mul;
   sa.zgrid = zg;
@@ -148,7 +149,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ra.sample_mode = ctx->prm.sample_mode;
   launch_resolve(ra, fp, ctx->resolve_grid, ctx->stream);
   if (pe) CU(cudaEventRecord(pe[3], ctx->stream));
-  ctx->launches += 2;
+  ctx->launches += ctx->d_perm ? 3 : 2;
   CU(cudaGetLastError());
   return PCP_OK;
 }

@@ -67,6 +67,7 @@ struct ScanArgs {
   const float4* __restrict__ cloud;   // N x {x,y,z,intensity}, possibly block-sorted
   const uint32_t* __restrict__ perm;  // sorted position -> original index (null when not pre-binned)
   const float4* __restrict__ aabb;    // pre-binned: 2 float4 per chunk {lo.xyz, nonfinite}, {hi.xyz, count}; null otherwise
+  uint32_t* active;                   // pre-binned: chunk ids classify_kernel found worth processing this frame
   uint32_t n_chunks;                  // ceil(n / kChunk)
   uint32_t chunk_mul;                 // odd multiplier coprime with n_chunks: chunk visited at slot s is (s * chunk_mul) % n_chunks
   unsigned long long* zgrid;          // Wc*Hc packed keys

@@ -196,6 +196,45 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
 static constexpr int kUnroll = PCP_UNROLL;
 static_assert(kUnroll * 32 == kChunk, "one pre-binned chunk = one warp iteration");
 
+// ---------------------------------------------------------------------------------------------------------------------
+// classify_kernel (pre-binned cloud): one lane per chunk runs classify_chunk; chunks that must be processed are appended to
+// `active` (one atomicAdd per warp), chunks that are certainly "all candidates, none in the grid" only add their point
+// count to n_candidates.  Slot s of the sequence is chunk (s * chunk_mul) % n_chunks.
+// ---------------------------------------------------------------------------------------------------------------------
+template <bool kCount>
+__global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+  const int lane = threadIdx.x & 31;
+  unsigned int ncand = 0;
+  for (unsigned long long s0 = (unsigned long long)(blockIdx.x * blockDim.x + threadIdx.x - lane); s0 < a.n_chunks;
+       s0 += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long slot = s0 + lane;
+    uint32_t chunk = 0;
+    int cls = kChunkSkip;
+    if (slot < a.n_chunks) {
+      chunk = (uint32_t)((slot * a.chunk_mul) % a.n_chunks);
+      cls = kChunkProcess;
+      if (fp.use_prefilter) {  // with a double T (pcp_cull) the gate is taken after T: no chunk culling
+        const float4 a0 = __ldg(a.aabb + 2 * chunk), a1 = __ldg(a.aabb + 2 * chunk + 1);
+        cls = classify_chunk(fp, a0, a1, kCount);
+        if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
+      }
+    }
+    const unsigned int m = __ballot_sync(0xffffffffu, cls == kChunkProcess);
+    if (m) {
+      unsigned int base = 0;
+      if (lane == 0) base = atomicAdd(&a.counters->n_active_blocks, (unsigned int)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (cls == kChunkProcess) a.active[base + __popc(m & ((1u << lane) - 1u))] = chunk;
+    }
+  }
+  if (kCount) {
+    for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
+    if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
+  }
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 template <bool kPrebin, bool kCount>
 __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
   __shared__ float4 cand_queue[kWarpsPerCta][kCandCap];
@@ -301,43 +340,27 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
       drain();
     }
   } else {
-    // Pre-binned cloud: slot s of the chunk sequence is chunk (s * chunk_mul) % n_chunks, so that the chunks in flight at
-    // any moment are spread over the whole map (the early-z statistics of a shuffled cloud, at chunk granularity) while
-    // the 128 points of one warp iteration are spatial neighbours.  Warp w owns slots w, w + W, w + 2W, ...; 32 of them
-    // are classified at once, one per lane, and only the chunks that are not certainly culled are read.
+    // Pre-binned cloud: classify_kernel has written the list of chunks that are not certainly culled (in a pseudo-random
+    // order, so that the chunks in flight are spread over the whole map: the early-z statistics of a shuffled cloud at
+    // chunk granularity).  Warp w processes entries w, w + W, ...: the load is balanced to one chunk.
     const uint32_t total_warps = gridDim.x * kWarpsPerCta;
     const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
-    const bool prefilter_chunks = prefilter_on;  // with a double T (pcp_cull) the gate is taken after T: no chunk culling
-    for (unsigned long long s0 = gw; s0 < a.n_chunks; s0 += 32ull * total_warps) {
-      const unsigned long long slot = s0 + (unsigned long long)lane * total_warps;
-      uint32_t chunk = 0xffffffffu;
-      int cls = kChunkSkip;
-      if (slot < a.n_chunks) {
-        chunk = (uint32_t)((slot * a.chunk_mul) % a.n_chunks);
-        cls = kChunkProcess;
-        if (prefilter_chunks) {
-          const float4 a0 = __ldg(a.aabb + 2 * chunk), a1 = __ldg(a.aabb + 2 * chunk + 1);
-          cls = classify_chunk(fp, a0, a1, kCount);
-          if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
-        }
-      }
-      unsigned int todo = __ballot_sync(0xffffffffu, cls == kChunkProcess);
-      while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const uint32_t base = __shfl_sync(0xffffffffu, chunk, src) * kChunk;
-        float4 p[kUnroll];
-        bool valid[kUnroll];
-        uint32_t idx[kUnroll];
+    const uint32_t n_active = a.counters->n_active_blocks;
+    for (uint32_t e = gw; e < n_active; e += total_warps) {
+      const uint32_t base = __ldg(a.active + e) * kChunk;
+      if (e + total_warps < n_active && lane < 16)  // next chunk of this warp: 16 lines of 128 B into L2
+        prefetch_l2(a.cloud + (size_t)__ldg(a.active + e + total_warps) * kChunk + lane * 8);
+      float4 p[kUnroll];
+      bool valid[kUnroll];
+      uint32_t idx[kUnroll];
 #pragma unroll
-        for (int k = 0; k < kUnroll; k++) {
-          idx[k] = base + k * 32 + lane;  // sorted position: the accumulator slot
-          valid[k] = idx[k] < a.n;
-          p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
-        }
-        stage_a(valid, p, idx);
-        drain();
+      for (int k = 0; k < kUnroll; k++) {
+        idx[k] = base + k * 32 + lane;  // sorted position: the accumulator slot
+        valid[k] = idx[k] < a.n;
+        p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
       }
+      stage_a(valid, p, idx);
+      drain();
     }
   }
 
@@ -511,8 +534,14 @@ int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool
 
 void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s) {
   if (a.aabb) {
-    if (count_candidates) scan_kernel<true, true><<<grid, kScanThreads, 0, s>>>(a, fp);
-    else scan_kernel<true, false><<<grid, kScanThreads, 0, s>>>(a, fp);
+    const int cgrid = (int)((a.n_chunks + 255) / 256);
+    if (count_candidates) {
+      classify_kernel<true><<<cgrid, 256, 0, s>>>(a, fp);
+      scan_kernel<true, true><<<grid, kScanThreads, 0, s>>>(a, fp);
+    } else {
+      classify_kernel<false><<<cgrid, 256, 0, s>>>(a, fp);
+      scan_kernel<true, false><<<grid, kScanThreads, 0, s>>>(a, fp);
+    }
   } else {
     if (count_candidates) scan_kernel<false, true><<<grid, kScanThreads, 0, s>>>(a, fp);
     else scan_kernel<false, false><<<grid, kScanThreads, 0, s>>>(a, fp);
@@ -576,10 +605,26 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
         pix[k] = (int)w1.w;
       }
     }
-    if (fp.depth_culling) {
-      unsigned int hi[kRes];
+    // The z-grid word, the pixel and the accumulator are all addressed from the record alone, so their loads are issued
+    // together (speculatively for records that turn out to be occluded): two dependent latencies per record, not four.
+    unsigned int hi[kRes];
+    uint32_t rgb[kRes], mv[kRes];
+    uint4 s[kRes];
+    const bool gather = a.bgr != nullptr;
 #pragma unroll
-      for (int k = 0; k < kRes; k++) hi[k] = live[k] ? __ldg(reinterpret_cast<const unsigned int*>(a.zgrid) + 2 * cell[k] + 1) : 0u;
+    for (int k = 0; k < kRes; k++) {
+      hi[k] = 0u; rgb[k] = 0u; mv[k] = 0u; s[k] = make_uint4(0u, 0u, 0u, 0u);
+      if (!live[k]) continue;
+      if (fp.depth_culling) hi[k] = __ldg(reinterpret_cast<const unsigned int*>(a.zgrid) + 2 * cell[k] + 1);
+      if (gather && pix[k] >= 0) {
+        const int pv = pix[k] / fp.imgW, pu = pix[k] - pv * fp.imgW;
+        const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
+        rgb[k] = (uint32_t)__ldg(px + 2) | ((uint32_t)__ldg(px + 1) << 8) | ((uint32_t)__ldg(px) << 16);  // r | g<<8 | b<<16 (cpp:760-762)
+        if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);  // cpp:804
+        s[k] = a.acc[idx[k]];
+      }
+    }
+    if (fp.depth_culling) {
 #pragma unroll
       for (int k = 0; k < kRes; k++)
         live[k] = live[k] && !(dist[k] > __dadd_rn((double)__uint_as_float(hi[k]), fp.tol));  // view_culling.cpp:157
@@ -596,24 +641,20 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
         double u, v;
         project(fp.cam, (double)rx, (double)ry, (double)rz, u, v);
         pix[k] = color_pixel((double)rz, u, v, fp.imgW, fp.imgH);
+        if (gather && pix[k] >= 0) {  // rare path (pcp_cull with T never gathers; kept for completeness)
+          const int pv = pix[k] / fp.imgW, pu = pix[k] - pv * fp.imgW;
+          const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
+          rgb[k] = (uint32_t)__ldg(px + 2) | ((uint32_t)__ldg(px + 1) << 8) | ((uint32_t)__ldg(px) << 16);
+          if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);
+          s[k] = a.acc[idx[k]];
+        }
       }
       live[k] = pix[k] >= 0;
       if (!live[k]) continue;
       ncol++;
       if (a.pix_out) a.pix_out[orig] = pix[k];
     }
-    if (!a.bgr) continue;
-    uint32_t rgb[kRes], mv[kRes];
-    uint4 s[kRes];
-#pragma unroll
-    for (int k = 0; k < kRes; k++) {
-      if (!live[k]) continue;
-      const int pv = pix[k] / fp.imgW, pu = pix[k] - pv * fp.imgW;
-      const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
-      rgb[k] = (uint32_t)__ldg(px + 2) | ((uint32_t)__ldg(px + 1) << 8) | ((uint32_t)__ldg(px) << 16);  // r | g<<8 | b<<16 (cpp:760-762)
-      if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);  // cpp:804
-      s[k] = a.acc[idx[k]];
-    }
+    if (!gather) continue;
     // a point appears at most once per frame, so the accumulator update needs no atomics
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
@@ -635,13 +676,23 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
       }
     }
   }
+  // counts: warp shuffle, then shared memory, then ONE pair of global atomics per CTA (same-address atomics serialise in
+  // L2 at about one per cycle: one pair per warp was 50 k of them, i.e. most of this kernel's 20 us)
+  __shared__ unsigned int cta_counts[2];
+  if (threadIdx.x < 2) cta_counts[threadIdx.x] = 0u;
+  __syncthreads();
   for (int o = 16; o > 0; o >>= 1) {
     nvis += __shfl_down_sync(0xffffffffu, nvis, o);
     ncol += __shfl_down_sync(0xffffffffu, ncol, o);
   }
   if ((threadIdx.x & 31) == 0) {
-    if (nvis) atomicAdd(&a.counters->n_visible, nvis);
-    if (ncol) atomicAdd(&a.counters->n_colored, ncol);
+    if (nvis) atomicAdd(&cta_counts[0], nvis);
+    if (ncol) atomicAdd(&cta_counts[1], ncol);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (cta_counts[0]) atomicAdd(&a.counters->n_visible, cta_counts[0]);
+    if (cta_counts[1]) atomicAdd(&a.counters->n_colored, cta_counts[1]);
   }
   // clear the OTHER buffer for the next frame (nobody reads it during this kernel)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.cells; i += gridDim.x * blockDim.x) a.next_zgrid[i] = kZInit;
