@@ -158,6 +158,11 @@ int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_
 int pcp_nid_eval_multi(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
                        uint8_t* ok_out);
 
+/* Debug/bench: the 16 u32 device counters of the last submitted frame: {records emitted by the scan, candidates, visible,
+ * coloured, active chunks, then (library built with -DPCP_STATS only) chunks skipped whole, points kept by the chunk-level
+ * depth test, points kept by the FP32 projection pre-filter}.  No reference counterpart. */
+int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]);
+
 /* Counters for benches: kernels launched by this context since creation. */
 uint64_t pcp_launch_count(const pcp_ctx* ctx);
 

@@ -42,7 +42,7 @@ SYMBOLS = [
     "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_device", "pcp_num_points",
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
-    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count",
+    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count", "pcp_debug_counters",
 ]
 
 _lib = None
@@ -96,6 +96,7 @@ def load():
     L.pcp_nid_destroy.restype = None
     L.pcp_nid_eval.argtypes = [vp, vp, i32, vp, vp]
     L.pcp_nid_eval_multi.argtypes = [C.POINTER(vp), i32, vp, vp, i32, vp, vp]
+    L.pcp_debug_counters.argtypes = [vp, vp]
     L.pcp_launch_count.argtypes = [vp]
     L.pcp_launch_count.restype = C.c_uint64
     _lib = L

@@ -101,6 +101,13 @@ class Colorizer:
     def launch_count(self) -> int:
         return int(self._L.pcp_launch_count(self._h))
 
+    def debug_counters(self) -> dict:
+        """Device counters of the last submitted frame (see pcp_debug_counters)."""
+        out = np.zeros(16, np.uint32)
+        self._check(self._L.pcp_debug_counters(self._h, _ptr(out)), "pcp_debug_counters")
+        keys = ("records", "candidates", "visible", "colored", "active_chunks", "chunks_skipped", "kept_a0", "kept_a1")
+        return {k: int(out[i]) for i, k in enumerate(keys)}
+
     # -- cloud -----------------------------------------------------------------------------------------
     def set_cloud(self, points: np.ndarray, intensity_offset: int | None = None):
         """points: (N,4) float32 {x,y,z,intensity} or any (N,k) float32 record array (pcl::PointXYZI: k=8,

@@ -195,8 +195,8 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   const uint32_t n_chunks = (uint32_t)((n + kChunk - 1) / kChunk);
   if (!ctx->d_perm) CU(cudaMalloc(&ctx->d_perm, sizeof(uint32_t) * n));
   if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
-  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint32_t) * n_chunks));
-  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->sm_count, ctx->stream));
+  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks));
+  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->bbox, ctx->sm_count, ctx->stream));
   ctx->n_chunks = n_chunks;
   // odd multiplier coprime with n_chunks: the visiting order (slot * mul) % n_chunks is a permutation of the chunks
   auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };

@@ -28,8 +28,19 @@ __device__ __forceinline__ Ival iv_sq(Ival a) {
 }
 __device__ __forceinline__ float iv_absmax(Ival a) { return fmaxf(fabsf(a.lo), fabsf(a.hi)); }
 
+// What the scan kernel needs to test a whole chunk (and then its points one by one) against the z-grid BEFORE projecting
+// anything: the rectangle of z-grid cells the chunk can fall into and a lower bound of the squared distance of its points.
+// A point whose squared distance exceeds (min + tol)^2 of EVERY cell of the rectangle is rejected by the reference's second
+// pass whatever its own cell is (view_culling.cpp:157; cell minima only decrease), and it cannot lower a minimum itself.
+struct ChunkInfo {
+  uint32_t rect;   // 0: no test possible; else w | h << 6 | point count << 12   (w * h <= 32)
+  uint32_t org;    // cx0 | cy0 << 16
+  float d2lo;      // lower bound of ||p||^2 over the chunk
+};
+
 // a0 = {lo.xyz, nonfinite flag}, a1 = {hi.xyz, count}.  `count_candidates`: the caller needs n_candidates exact.
-__device__ __forceinline__ int classify_chunk(const FrameParams& fp, float4 a0, float4 a1, bool count_candidates) {
+__device__ __forceinline__ int classify_chunk(const FrameParams& fp, float4 a0, float4 a1, bool count_candidates, ChunkInfo& info) {
+  info.rect = 0u; info.org = 0u; info.d2lo = 0.0f;
   if (a0.w != 0.0f) return kChunkProcess;  // holds a non-finite coordinate
   const float eps = 5.9604644775390625e-08f;
   const float cx = 0.5f * (a0.x + a1.x), cy = 0.5f * (a0.y + a1.y), cz = 0.5f * (a0.z + a1.z);
@@ -81,7 +92,23 @@ __device__ __forceinline__ int classify_chunk(const FrameParams& fp, float4 a0, 
   const bool all_cand = (ulo > c.lo) && (vlo > c.lo) && (uhi < c.u_hi_cand) && (vhi < c.v_hi_cand);
   if (none_cand) return kChunkSkip;  // no point passes the gate of :90, whatever the mode
   if (!fp.depth_culling) return kChunkProcess;  // every candidate is kept (:135)
-  if (!out_grid) return kChunkProcess;
+  if (!out_grid) {
+    // Cell rectangle (clamped to the grid: points outside the grid are never kept, :162-165) and distance bound.  The 0.5 px
+    // of `e` dwarfs the rounding of the reference's float division by ds.  When n_candidates must stay exact the test is
+    // only offered for chunks whose points are all certain candidates (the scan kernel then counts the points it drops).
+    if (c.tol_up < 3.0e38f && (!count_candidates || all_cand)) {
+      const int x0 = max((int)floorf(ulo * c.inv_ds), 0), x1 = min((int)floorf(uhi * c.inv_ds), fp.Wc - 1);
+      const int y0 = max((int)floorf(vlo * c.inv_ds), 0), y1 = min((int)floorf(vhi * c.inv_ds), fp.Hc - 1);
+      const int w = x1 - x0 + 1, h = y1 - y0 + 1;
+      if (w >= 1 && h >= 1 && w * h <= 32) {
+        const float dx = fmaxf(fabsf(cc[0]) - rr[0], 0.0f), dy = fmaxf(fabsf(cc[1]) - rr[1], 0.0f), dz = fmaxf(fabsf(cc[2]) - rr[2], 0.0f);
+        info.rect = (uint32_t)w | ((uint32_t)h << 6) | ((uint32_t)a1.w << 12);
+        info.org = (uint32_t)x0 | ((uint32_t)y0 << 16);
+        info.d2lo = fmaf(dz, dz, fmaf(dy, dy, dx * dx)) * c.dscale;
+      }
+    }
+    return kChunkProcess;
+  }
   // certainly outside the z-grid: never kept by pass 2 (:162-165)
   if (!count_candidates) return kChunkSkip;
   return all_cand ? kChunkAllCandidates : kChunkProcess;

@@ -31,8 +31,9 @@ struct pcp_ctx {
   float4* d_cloud = nullptr;      // N x 16 B  {x,y,z,intensity}
   uint32_t* d_perm = nullptr;     // N x 4 B   sorted position -> original index (pre-binned mode; null otherwise)
   float4* d_aabb = nullptr;       // 2 float4 per chunk of 128 sorted points (pre-binned mode)
-  uint32_t* d_active = nullptr;   // per-frame list of chunks to scan (pre-binned mode)
+  uint4* d_active = nullptr;      // per-frame list of chunks to scan + their cell rectangle / distance bound (pre-binned mode)
   uint32_t n_chunks = 0, chunk_mul = 1;
+  float bbox[6] = {0, 0, 0, 0, 0, 0};  // finite bounding box of the cloud {lo.xyz, hi.xyz} (pre-binned mode)
   uint4* d_acc = nullptr;         // N x 16 B  {sum_r,sum_g,sum_b,count}
   uint2* d_mask_acc = nullptr;    // N x 8 B   {hits, max}; allocated at the first frame that carries a mask
   float* d_top_score = nullptr;   // top_m x N

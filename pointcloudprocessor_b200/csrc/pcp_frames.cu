@@ -290,6 +290,16 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
   return PCP_OK;
 }
 
+/* Debug: the 16 u32 device counters of the last submitted frame {records, candidates, visible, coloured, active chunks,
+ * [PCP_STATS builds: chunks skipped whole, points kept by stage A0, points kept by stage A1], ...}. */
+int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]) {
+  if (!ctx || !out16) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaMemcpy(out16, ctx->d_counters + (ctx->buf ^ 1), 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  return PCP_OK;
+}
+
 void* pcp_accumulators_device(pcp_ctx* ctx) { return ctx ? (void*)ctx->d_acc : nullptr; }
 
 int pcp_profile_enable(pcp_ctx* ctx, int on) {

@@ -29,8 +29,10 @@ struct FrameCounters {
   unsigned int n_visible;     // kept by pass 2 (view_culling.cpp:167)
   unsigned int n_colored;     // generateColorMap pushes (cpp:763)
   unsigned int n_active_blocks;
-  unsigned int pad[11];
+  unsigned int stats[3];      // PCP_STATS builds: chunks skipped whole, points kept by stage A0, points kept by stage A1
+  unsigned int pad[8];
 };
+static_assert(sizeof(FrameCounters) == 64, "FrameCounters layout");
 
 // FP32 pre-filter constants (pcp_kernels.cu: prefilter()): the camera in float, the same coefficients as magnitudes, the
 // decision boundaries in pixels and the error-bound factors.
@@ -67,7 +69,7 @@ struct ScanArgs {
   const float4* __restrict__ cloud;   // N x {x,y,z,intensity}, possibly block-sorted
   const uint32_t* __restrict__ perm;  // sorted position -> original index (null when not pre-binned)
   const float4* __restrict__ aabb;    // pre-binned: 2 float4 per chunk {lo.xyz, nonfinite}, {hi.xyz, count}; null otherwise
-  uint32_t* active;                   // pre-binned: chunk ids classify_kernel found worth processing this frame
+  uint4* active;                      // pre-binned: {chunk id, ChunkInfo rect, org, d2lo bits} of the chunks worth processing this frame
   uint32_t n_chunks;                  // ceil(n / kChunk)
   uint32_t chunk_mul;                 // odd multiplier coprime with n_chunks: chunk visited at slot s is (s * chunk_mul) % n_chunks
   unsigned long long* zgrid;          // Wc*Hc packed keys
@@ -109,7 +111,7 @@ void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uin
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
 // pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)
-cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, int sm_count, cudaStream_t s);
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, float bbox6[6], int sm_count, cudaStream_t s);
 void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s);
 // ascending index list from a visibility bitmask; returns through d_total the number of set bits
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,

@@ -193,6 +193,13 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
 #else
 #define PCP_ZLOAD(p) __ldca(p)
 #endif
+// The per-chunk read of the pre-binned scan (one load per chunk and cell) goes to L2: it is rare enough not to create a
+// hot spot, and a fresh minimum is what lets whole chunks be skipped.
+#ifdef PCP_ZLOAD0_L1
+#define PCP_ZLOAD0(p) __ldca(p)
+#else
+#define PCP_ZLOAD0(p) __ldcg(p)
+#endif
 static constexpr int kUnroll = PCP_UNROLL;
 static_assert(kUnroll * 32 == kChunk, "one pre-binned chunk = one warp iteration");
 
@@ -210,12 +217,13 @@ __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const _
     const unsigned long long slot = s0 + lane;
     uint32_t chunk = 0;
     int cls = kChunkSkip;
+    ChunkInfo info{0u, 0u, 0.0f};
     if (slot < a.n_chunks) {
       chunk = (uint32_t)((slot * a.chunk_mul) % a.n_chunks);
       cls = kChunkProcess;
       if (fp.use_prefilter) {  // with a double T (pcp_cull) the gate is taken after T: no chunk culling
         const float4 a0 = __ldg(a.aabb + 2 * chunk), a1 = __ldg(a.aabb + 2 * chunk + 1);
-        cls = classify_chunk(fp, a0, a1, kCount);
+        cls = classify_chunk(fp, a0, a1, kCount, info);
         if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
       }
     }
@@ -224,7 +232,8 @@ __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const _
       unsigned int base = 0;
       if (lane == 0) base = atomicAdd(&a.counters->n_active_blocks, (unsigned int)__popc(m));
       base = __shfl_sync(0xffffffffu, base, 0);
-      if (cls == kChunkProcess) a.active[base + __popc(m & ((1u << lane) - 1u))] = chunk;
+      if (cls == kChunkProcess)
+        a.active[base + __popc(m & ((1u << lane) - 1u))] = make_uint4(chunk, info.rect, info.org, __float_as_uint(info.d2lo));
     }
   }
   if (kCount) {
@@ -235,7 +244,7 @@ __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const _
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
-template <bool kPrebin, bool kCount>
+template <bool kCount>
 __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
   __shared__ float4 cand_queue[kWarpsPerCta][kCandCap];
   __shared__ Record rec_queue[kWarpsPerCta][kQueueCap];
@@ -257,7 +266,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
     if (lane < cnt) {
       const float4 c = cq[cn + lane];
       const uint32_t slot = __float_as_uint(c.w);
-      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, kPrebin ? __ldg(a.perm + slot) : slot, rec, cand);
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, slot, rec, cand);
     }
     if (kCount) ncand += cand ? 1u : 0u;
     const unsigned int m = __ballot_sync(0xffffffffu, emit);
@@ -322,46 +331,21 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
     }
   };
 
-  if (!kPrebin) {
-    const uint32_t chunk = 32u * kUnroll;
-    const unsigned long long stride = (unsigned long long)gridDim.x * kWarpsPerCta * chunk;
-    for (unsigned long long base64 = (unsigned long long)(blockIdx.x * kWarpsPerCta + warp) * chunk; base64 < a.n; base64 += stride) {
-      const uint32_t base = (uint32_t)base64;
-      float4 p[kUnroll];
-      bool valid[kUnroll];
-      uint32_t idx[kUnroll];
+  const uint32_t chunk = 32u * kUnroll;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kWarpsPerCta * chunk;
+  for (unsigned long long base64 = (unsigned long long)(blockIdx.x * kWarpsPerCta + warp) * chunk; base64 < a.n; base64 += stride) {
+    const uint32_t base = (uint32_t)base64;
+    float4 p[kUnroll];
+    bool valid[kUnroll];
+    uint32_t idx[kUnroll];
 #pragma unroll
-      for (int k = 0; k < kUnroll; k++) {
-        idx[k] = base + k * 32 + lane;
-        valid[k] = idx[k] < a.n;
-        p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
-      }
-      stage_a(valid, p, idx);
-      drain();
+    for (int k = 0; k < kUnroll; k++) {
+      idx[k] = base + k * 32 + lane;
+      valid[k] = idx[k] < a.n;
+      p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
     }
-  } else {
-    // Pre-binned cloud: classify_kernel has written the list of chunks that are not certainly culled (in a pseudo-random
-    // order, so that the chunks in flight are spread over the whole map: the early-z statistics of a shuffled cloud at
-    // chunk granularity).  Warp w processes entries w, w + W, ...: the load is balanced to one chunk.
-    const uint32_t total_warps = gridDim.x * kWarpsPerCta;
-    const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
-    const uint32_t n_active = a.counters->n_active_blocks;
-    for (uint32_t e = gw; e < n_active; e += total_warps) {
-      const uint32_t base = __ldg(a.active + e) * kChunk;
-      if (e + total_warps < n_active && lane < 16)  // next chunk of this warp: 16 lines of 128 B into L2
-        prefetch_l2(a.cloud + (size_t)__ldg(a.active + e + total_warps) * kChunk + lane * 8);
-      float4 p[kUnroll];
-      bool valid[kUnroll];
-      uint32_t idx[kUnroll];
-#pragma unroll
-      for (int k = 0; k < kUnroll; k++) {
-        idx[k] = base + k * 32 + lane;  // sorted position: the accumulator slot
-        valid[k] = idx[k] < a.n;
-        p[k] = valid[k] ? __ldcs(a.cloud + idx[k]) : make_float4(0.f, 0.f, -1.f, 0.f);
-      }
-      stage_a(valid, p, idx);
-      drain();
-    }
+    stage_a(valid, p, idx);
+    drain();
   }
 
   __syncwarp();
@@ -374,6 +358,225 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
     if (lane < rn) a.records[base + lane] = rq[lane];
   }
   if (kCount) {  // candidate count: warp reduce, one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
+    if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// scan_binned_kernel (pre-binned cloud): three compaction stages per warp, each running with all 32 lanes busy.
+//   A0  per chunk: the chunk's cell rectangle (ChunkInfo, from classify_kernel) gives lim2 = max over its cells of
+//       (current minimum + tol)^2, read once by the warp (one lane per cell).  A chunk whose distance bound exceeds lim2 is
+//       skipped without loading a point.  Otherwise its 128 points are loaded, transformed in float (exact, PCL order) and
+//       tested with one compare each (z < 0, ||p||^2 > lim2): ~30 instructions per 32 points instead of the ~110 of the
+//       projection pre-filter, for the bulk of the occluded points.
+//   A1  the survivors run the FP32 projection pre-filter of prefilter_a/b against their own cell, kA1 x 32 at a time.
+//   B   the exact FP64 body (exact_point) and the record queue, as in scan_kernel.
+// ---------------------------------------------------------------------------------------------------------------------
+#ifndef PCP_A1W
+#define PCP_A1W 2
+#endif
+static constexpr int kA1 = PCP_A1W;
+static constexpr int kQ0Cap = 32 * (kUnroll + 1);  // < 32 left over + one chunk
+static constexpr int kQ1Cap = 32 * (kA1 + 1);      // < 32 left over + one A1 batch
+static constexpr size_t kBinnedSmem = (size_t)kWarpsPerCta * ((kQ0Cap + kQ1Cap) * sizeof(float4) + kQueueCap * sizeof(Record));
+
+template <bool kCount>
+__global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+  extern __shared__ __align__(16) unsigned char binned_smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const unsigned int lt_mask = (1u << lane) - 1u;
+  float4* q0 = reinterpret_cast<float4*>(binned_smem) + (size_t)warp * kQ0Cap;
+  float4* q1 = reinterpret_cast<float4*>(binned_smem) + (size_t)kWarpsPerCta * kQ0Cap + (size_t)warp * kQ1Cap;
+  Record* rq = reinterpret_cast<Record*>(binned_smem + (size_t)kWarpsPerCta * (kQ0Cap + kQ1Cap) * sizeof(float4)) + (size_t)warp * kQueueCap;
+  int n0 = 0, n1 = 0, rn = 0;
+  unsigned int ncand = 0;
+#ifdef PCP_STATS
+  unsigned int st_skipped = 0, st_a0 = 0, st_a1 = 0;  // chunks skipped whole, points kept by A0, points kept by A1 (per warp)
+#endif
+  const bool prefilter_on = fp.use_prefilter != 0;
+  const bool depth_culling = fp.depth_culling != 0;
+  const unsigned int* zhi = reinterpret_cast<const unsigned int*>(a.zgrid) + 1;
+
+  auto stage_b = [&](int cnt) {
+    Record rec;
+    bool cand = false, emit = false;
+    n1 -= cnt;
+    if (lane < cnt) {
+      const float4 c = q1[n1 + lane];
+      const uint32_t slot = __float_as_uint(c.w);
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, __ldg(a.perm + slot), rec, cand);
+    }
+    if (kCount) ncand += cand ? 1u : 0u;
+    const unsigned int m = __ballot_sync(0xffffffffu, emit);
+    if (m) {
+      if (emit) rq[rn + __popc(m & lt_mask)] = rec;
+      rn += __popc(m);
+      __syncwarp();
+      if (rn >= 32) {
+        unsigned int base = 0;
+        if (lane == 0) base = atomicAdd(&a.counters->n_records, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        rn -= 32;
+        const uint4* src = reinterpret_cast<const uint4*>(rq + rn);
+        uint4* dst = reinterpret_cast<uint4*>(a.records + base);
+        dst[lane] = src[lane];
+        dst[lane + 32] = src[lane + 32];
+        __syncwarp();
+      }
+    }
+  };
+
+  // A1 on the last min(n0, 32 kA1) entries of q0
+  auto stage_a1 = [&]() {
+    const int cnt = n0 < 32 * kA1 ? n0 : 32 * kA1;
+    n0 -= cnt;
+    float x[kA1], y[kA1], z[kA1], w[kA1];
+    bool ok[kA1], push[kA1];
+    unsigned int cur[kA1];
+#pragma unroll
+    for (int k = 0; k < kA1; k++) {
+      const int i = k * 32 + lane;
+      ok[k] = i < cnt;
+      const float4 c = q0[n0 + (ok[k] ? i : 0)];
+      x[k] = c.x; y[k] = c.y; z[k] = c.z; w[k] = c.w;
+      cur[k] = kZBoundInit;  // FLT_MAX: always an upper bound (cell unknown, or pre-filter off)
+    }
+    if (prefilter_on) {
+      PreA pa[kA1];
+#pragma unroll
+      for (int k = 0; k < kA1; k++) pa[k] = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
+#pragma unroll
+      for (int k = 0; k < kA1; k++)
+        if (ok[k] && (pa[k].flags & 1u)) cur[k] = PCP_ZLOAD(zhi + 2 * pa[k].cell);
+#pragma unroll
+      for (int k = 0; k < kA1; k++) {
+        const unsigned int f = prefilter_b<kCount>(fp.pre, pa[k], cur[k], depth_culling);
+        push[k] = ok[k] && (f & 1u);
+        if (kCount) ncand += (ok[k] && (f & 2u)) ? 1u : 0u;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < kA1; k++) push[k] = ok[k];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < kA1; k++) {
+      const unsigned int m = __ballot_sync(0xffffffffu, push[k]);
+      if (push[k]) q1[n1 + __popc(m & lt_mask)] = make_float4(x[k], y[k], z[k], w[k]);
+      n1 += __popc(m);
+#ifdef PCP_STATS
+      st_a1 += __popc(m);
+#endif
+    }
+    __syncwarp();
+#pragma unroll 1
+    while (n1 >= 32) stage_b(32);
+  };
+
+  // Work distribution.  classify_kernel lists the active chunks in a pseudo-random order (chunks in flight are spread over
+  // the whole map, like a shuffled cloud at chunk granularity).  CTA c owns items c, c + G, c + 2G, ...; its warps take them
+  // one at a time from a shared-memory ticket (chunk costs differ by orders of magnitude: skipped whole vs full of FP64
+  // work).  The next item's list entry is loaded and its points are pulled into L2 while the current one is processed.
+  __shared__ unsigned int s_ticket;
+  if (threadIdx.x == 0) s_ticket = 0u;
+  __syncthreads();
+  const uint32_t n_active = a.counters->n_active_blocks;
+  auto take = [&]() -> uint32_t {
+    uint32_t j = 0;
+    if (lane == 0) j = atomicAdd(&s_ticket, 1u);
+    j = __shfl_sync(0xffffffffu, j, 0);
+    return blockIdx.x + gridDim.x * j;
+  };
+  const uint4 kNoEnt = make_uint4(0u, 0u, 0u, 0u);
+  // one lane per cell of the entry's rectangle: (minimum + tol)^2 rounded up, as bits (0 for the other lanes / no rectangle)
+  auto rect_bits = [&](const uint4& e) -> unsigned int {
+    const int w = (int)(e.y & 63u), h = (int)((e.y >> 6) & 63u);
+    unsigned int bits = 0u;
+    if (lane < w * h) {
+      const int cy = lane / w, cx = lane - cy * w;
+      const int cell = ((int)(e.z >> 16) + cy) * fp.Wc + (int)(e.z & 0xffffu) + cx;
+      const float lim = __fadd_ru(__uint_as_float(PCP_ZLOAD0(zhi + 2 * cell)), fp.pre.tol_up);  // >= minimum + tol >= 0
+      bits = __float_as_uint(__fmul_ru(lim, lim));
+    }
+    return bits;
+  };
+  // The next item's list entry is loaded (and its points pulled into L2) while the current one is processed.  Deeper
+  // pipelining (z-grid cells of the next item, record blocks reserved ahead, stage A1's z word reused by stage B) was
+  // measured slower: the kernel sits at its 64-register budget and every extra live value costs more than the latency it hides.
+  uint32_t item = take();
+  uint4 ent = item < n_active ? __ldg(a.active + item) : kNoEnt;
+  while (item < n_active) {
+    const uint32_t nitem = take();
+    uint4 nent = kNoEnt;
+    if (nitem < n_active) {
+      nent = __ldg(a.active + nitem);
+      if (lane < 16) prefetch_l2(a.cloud + (size_t)nent.x * kChunk + lane * 8);  // 16 lines of 128 B
+    }
+    const unsigned int zb = rect_bits(ent);
+    const uint32_t base = ent.x * kChunk;
+    float lim2 = __int_as_float(0x7f800000);  // +inf: nothing is dropped by the distance test
+    bool skip = false;
+    if (ent.y != 0u) {
+      lim2 = __uint_as_float(__reduce_max_sync(0xffffffffu, zb));  // non-negative floats order like their bit patterns
+      skip = __uint_as_float(ent.w) > lim2;  // the whole chunk is farther than every cell it can fall into
+    }
+    if (skip) {
+      if (kCount && lane == 0) ncand += ent.y >> 12;  // offered only for all-candidate chunks (classify_chunk)
+#ifdef PCP_STATS
+      st_skipped++;
+#endif
+    } else {
+      float4 p[kUnroll];
+      bool valid[kUnroll];
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) {
+        const uint32_t i = base + k * 32 + lane;  // sorted position: the accumulator slot
+        valid[k] = i < a.n;
+        p[k] = valid[k] ? __ldcs(a.cloud + i) : make_float4(0.f, 0.f, -1.f, 0.f);
+      }
+#pragma unroll
+      for (int k = 0; k < kUnroll; k++) {
+        float x = p[k].x, y = p[k].y, z = p[k].z;
+        if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x, y, z);  // pcl::transformPointCloud (cpp:521)
+        const bool front = valid[k] && !(z < 0.0f);  // view_culling.cpp:76 (exact: double(z) < 0 <=> z < 0)
+        const float dlo = fmaf(z, z, fmaf(y, y, x * x)) * fp.pre.dscale;  // <= the exact squared norm; NaN compares false
+        const bool far = dlo > lim2;
+        if (kCount) ncand += (front && far) ? 1u : 0u;
+        const bool keep = front && !far;
+        const unsigned int m = __ballot_sync(0xffffffffu, keep);
+        if (keep) q0[n0 + __popc(m & lt_mask)] = make_float4(x, y, z, __uint_as_float(base + k * 32 + lane));
+        n0 += __popc(m);
+#ifdef PCP_STATS
+        st_a0 += __popc(m);
+#endif
+      }
+      __syncwarp();
+#pragma unroll 1
+      while (n0 >= 32) stage_a1();
+    }
+    item = nitem;
+    ent = nent;
+  }
+
+  __syncwarp();
+  if (n0 > 0) stage_a1();
+  if (n1 > 0) stage_b(n1);
+#ifdef PCP_STATS
+  if (lane == 0) {
+    atomicAdd(&a.counters->stats[0], st_skipped);
+    atomicAdd(&a.counters->stats[1], st_a0);
+    atomicAdd(&a.counters->stats[2], st_a1);
+  }
+#endif
+  if (rn > 0) {
+    unsigned int base = 0;
+    if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)rn);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (lane < rn) a.records[base + lane] = rq[lane];
+  }
+  if (kCount) {
     for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
     if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
   }
@@ -535,16 +738,22 @@ int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool
 void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s) {
   if (a.aabb) {
     const int cgrid = (int)((a.n_chunks + 255) / 256);
+    static bool configured = false;
+    if (!configured) {
+      cudaFuncSetAttribute(scan_binned_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem);
+      cudaFuncSetAttribute(scan_binned_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem);
+      configured = true;
+    }
     if (count_candidates) {
       classify_kernel<true><<<cgrid, 256, 0, s>>>(a, fp);
-      scan_kernel<true, true><<<grid, kScanThreads, 0, s>>>(a, fp);
+      scan_binned_kernel<true><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
     } else {
       classify_kernel<false><<<cgrid, 256, 0, s>>>(a, fp);
-      scan_kernel<true, false><<<grid, kScanThreads, 0, s>>>(a, fp);
+      scan_binned_kernel<false><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
     }
   } else {
-    if (count_candidates) scan_kernel<false, true><<<grid, kScanThreads, 0, s>>>(a, fp);
-    else scan_kernel<false, false><<<grid, kScanThreads, 0, s>>>(a, fp);
+    if (count_candidates) scan_kernel<true><<<grid, kScanThreads, 0, s>>>(a, fp);
+    else scan_kernel<false><<<grid, kScanThreads, 0, s>>>(a, fp);
   }
 }
 
@@ -893,6 +1102,6 @@ void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offset
 
 int scan_ctas_per_sm() {
   int occ = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcp::scan_kernel<false, false>, pcp::kScanThreads, 0) != cudaSuccess || occ < 1) occ = 2;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcp::scan_kernel<false>, pcp::kScanThreads, 0) != cudaSuccess || occ < 1) occ = 2;
   return occ;
 }

@@ -1,6 +1,6 @@
 // pcp_prebin.cu — one-time spatial pre-binning of the map cloud (pcp_params.prebin, SURVEY.md §8d "pre-binned").
 //
-// At pcp_set_cloud the points are sorted by a 30-bit Morton key of their position inside the cloud's bounding box and cut
+// At pcp_set_cloud the points are sorted by a 63-bit Morton key of their position on an isotropic grid over the cloud's bounding box and cut
 // into chunks of kChunk = 128 consecutive points (one warp iteration of the scan kernel); every chunk gets an axis-aligned
 // bounding box.  Per frame the scan kernel (a) skips, after reading 32 bytes, every chunk that is certainly behind the
 // camera or certainly outside the z-grid, (b) runs with coherent warps on the rest, and (c) addresses the per-point
@@ -13,6 +13,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <cfloat>
+#include <cstring>
 
 #include "pcp_ctx.hpp"
 
@@ -47,29 +48,33 @@ __global__ void bbox_kernel(const float4* __restrict__ pts, uint32_t n, float* _
   }
 }
 
-__device__ __forceinline__ uint32_t spread10(uint32_t v) {  // 10 bits -> every third bit
-  v &= 0x3ffu;
-  v = (v | (v << 16)) & 0x030000ffu;
-  v = (v | (v << 8)) & 0x0300f00fu;
-  v = (v | (v << 4)) & 0x030c30c3u;
-  v = (v | (v << 2)) & 0x09249249u;
+__device__ __forceinline__ unsigned long long spread21(unsigned long long v) {  // 21 bits -> every third bit
+  v &= 0x1fffffull;
+  v = (v | (v << 32)) & 0x001f00000000ffffull;
+  v = (v | (v << 16)) & 0x001f0000ff0000ffull;
+  v = (v | (v << 8)) & 0x100f00f00f00f00full;
+  v = (v | (v << 4)) & 0x10c30c30c30c30c3ull;
+  v = (v | (v << 2)) & 0x1249249249249249ull;
   return v;
 }
 
-__global__ void morton_kernel(const float4* __restrict__ pts, uint32_t n, const int* __restrict__ box6, uint32_t* __restrict__ keys,
+// 63-bit Morton key on an ISOTROPIC grid (one cell size for the three axes = largest extent / 2^21): the scale of an axis must
+// not depend on the extent of the cloud along it, or chunks of a long thin map (a corridor) become long thin boxes whose
+// bounding boxes cull poorly.  With one cell size, 128 consecutive points of a surface are a compact patch.
+__global__ void morton_kernel(const float4* __restrict__ pts, uint32_t n, const int* __restrict__ box6, unsigned long long* __restrict__ keys,
                               uint32_t* __restrict__ idx) {
   auto dec = [](int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); };
   const float lx = dec(box6[0]), ly = dec(box6[1]), lz = dec(box6[2]);
-  const float sx = 1023.0f / fmaxf(dec(box6[3]) - lx, 1e-20f), sy = 1023.0f / fmaxf(dec(box6[4]) - ly, 1e-20f),
-              sz = 1023.0f / fmaxf(dec(box6[5]) - lz, 1e-20f);
+  const float ext = fmaxf(fmaxf(dec(box6[3]) - lx, dec(box6[4]) - ly), fmaxf(dec(box6[5]) - lz, 1e-20f));
+  const float sc = 2097151.0f / ext;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float4 p = pts[i];
-    uint32_t key = 0x3fffffffu;  // non-finite points sort to the end
+    unsigned long long key = 0x7fffffffffffffffull;  // non-finite points sort to the end
     if (finite3(p)) {
-      const uint32_t qx = (uint32_t)fminf(fmaxf((p.x - lx) * sx, 0.0f), 1023.0f);
-      const uint32_t qy = (uint32_t)fminf(fmaxf((p.y - ly) * sy, 0.0f), 1023.0f);
-      const uint32_t qz = (uint32_t)fminf(fmaxf((p.z - lz) * sz, 0.0f), 1023.0f);
-      key = spread10(qx) | (spread10(qy) << 1) | (spread10(qz) << 2);
+      const unsigned long long qx = (unsigned long long)fminf(fmaxf((p.x - lx) * sc, 0.0f), 2097151.0f);
+      const unsigned long long qy = (unsigned long long)fminf(fmaxf((p.y - ly) * sc, 0.0f), 2097151.0f);
+      const unsigned long long qz = (unsigned long long)fminf(fmaxf((p.z - lz) * sc, 0.0f), 2097151.0f);
+      key = spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2);
     }
     keys[i] = key;
     idx[i] = i;
@@ -115,11 +120,13 @@ __global__ void chunk_aabb_kernel(const float4* __restrict__ pts, uint32_t n, ui
 
 // Sorts `d_cloud` (n points, in place through a temporary) and fills d_perm (sorted position -> original index) and
 // d_aabb (2 float4 per chunk).  All buffers are allocated by the caller except the temporaries.  Synchronises the stream.
-cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, int sm_count, cudaStream_t s) {
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, float bbox6[6], int sm_count, cudaStream_t s) {
+  for (int k = 0; k < 6; k++) bbox6[k] = 0.0f;
   if (n == 0) return cudaSuccess;
   cudaError_t e;
   int* d_box = nullptr;
-  uint32_t *d_keys = nullptr, *d_keys_out = nullptr, *d_idx = nullptr;
+  unsigned long long *d_keys = nullptr, *d_keys_out = nullptr;
+  uint32_t* d_idx = nullptr;
   float4* d_tmp = nullptr;
   void* d_temp = nullptr;
   size_t temp_bytes = 0;
@@ -128,8 +135,8 @@ cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* 
   };
 #define PB(call) do { e = (call); if (e != cudaSuccess) { cleanup(); return e; } } while (0)
   PB(cudaMalloc(&d_box, 6 * sizeof(int)));
-  PB(cudaMalloc(&d_keys, sizeof(uint32_t) * n));
-  PB(cudaMalloc(&d_keys_out, sizeof(uint32_t) * n));
+  PB(cudaMalloc(&d_keys, sizeof(unsigned long long) * n));
+  PB(cudaMalloc(&d_keys_out, sizeof(unsigned long long) * n));
   PB(cudaMalloc(&d_idx, sizeof(uint32_t) * n));
   PB(cudaMalloc(&d_tmp, sizeof(float4) * n));
   const int h_box[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
@@ -137,15 +144,23 @@ cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* 
   const int grid = sm_count * 8;
   bbox_kernel<<<grid, 256, 0, s>>>(d_cloud, n, reinterpret_cast<float*>(d_box));
   morton_kernel<<<grid, 256, 0, s>>>(d_cloud, n, d_box, d_keys, d_idx);
-  PB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 30, s));
+  PB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 63, s));
   PB(cudaMalloc(&d_temp, temp_bytes ? temp_bytes : 1));
-  PB(cub::DeviceRadixSort::SortPairs(d_temp, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 30, s));  // stable: deterministic
+  PB(cub::DeviceRadixSort::SortPairs(d_temp, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 63, s));  // stable: deterministic
   gather_kernel<<<grid, 256, 0, s>>>(d_cloud, d_perm, n, d_tmp);
   PB(cudaMemcpyAsync(d_cloud, d_tmp, sizeof(float4) * n, cudaMemcpyDeviceToDevice, s));
   const uint32_t n_chunks = (n + kChunk - 1) / kChunk;
   chunk_aabb_kernel<<<(n_chunks * 32 + 255) / 256, 256, 0, s>>>(d_cloud, n, n_chunks, d_aabb);
   PB(cudaGetLastError());
+  int h_out[6];
+  PB(cudaMemcpyAsync(h_out, d_box, sizeof(h_out), cudaMemcpyDeviceToHost, s));
   PB(cudaStreamSynchronize(s));
+  for (int k = 0; k < 6; k++) {  // undo the order-preserving int mapping; no finite point at all leaves the initial values
+    const int v = h_out[k] >= 0 ? h_out[k] : h_out[k] ^ 0x7fffffff;
+    float f;
+    std::memcpy(&f, &v, sizeof(f));
+    bbox6[k] = (h_out[0] == 0x7fffffff) ? 0.0f : f;
+  }
 #undef PB
   cleanup();
   return cudaSuccess;
