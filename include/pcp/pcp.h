@@ -51,7 +51,10 @@ typedef struct {
   int prebin;                      /* 1 (default): Morton-sort the device copy of the cloud into 128-point chunks with bounding
                                     * boxes at set_cloud; chunks certainly behind the camera / outside the z-grid are skipped per
                                     * frame.  Every output stays in the caller's point order.  0: keep the caller's order. */
-  int reserved[7];
+  int frames_in_flight;            /* 1..3 (0 = default 3): frames run on that many internal streams, each with its own z-grid / record
+                                    * scratch, so that the scan of frame f+1 overlaps the tail of frame f and its resolve pass.
+                                    * Accumulator updates stay in frame order; results do not depend on this value. */
+  int reserved[6];
 } pcp_params;
 
 /* Optional per-frame outputs (host buffers, caller-owned; any pointer may be NULL). */
@@ -88,7 +91,8 @@ int pcp_host_free(void* p);
 
 /* loadPointCloud (cpp:92-154) hands over the map: `n` points, x,y,z floats at byte offsets 0,4,8 of each
  * `stride_bytes` record and intensity at `intensity_offset` (pcl::PointXYZI: stride 32, intensity at 16).
- * Copies; converts to float4 SoA on the device; resets the accumulators. */
+ * Copies (asynchronously when `points` is pinned memory: keep it valid until the next synchronising call, e.g.
+ * pcp_synchronize or pcp_finalize); converts to float4 SoA on the device; resets the accumulators. */
 int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset);
 /* Same with a device-resident float4 {x,y,z,intensity} array (no host copy). */
 int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n);

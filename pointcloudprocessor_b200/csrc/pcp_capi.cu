@@ -47,6 +47,7 @@ void pcp_default_params(pcp_params* p) {
   p->accum_mode = PCP_ACCUM_SUM;
   p->sample_mode = PCP_SAMPLE_NEAREST;
   p->top_m = 5;
+  p->frames_in_flight = 3;
   p->prebin = 1;  // Morton-sorted chunks with AABBs; PCP_NO_PREBIN=1 or prebin = 0 keeps the caller's order on the device
 }
 
@@ -60,7 +61,8 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   if (params->image_width <= 0 || params->image_height <= 0 || params->cull_width <= 0 || params->cull_height <= 0 ||
       params->downsample <= 0 || params->top_m < 1 || params->top_m > 16 ||
       (params->accum_mode != PCP_ACCUM_SUM && params->accum_mode != PCP_ACCUM_TOP5) ||
-      (params->sample_mode != PCP_SAMPLE_NEAREST && params->sample_mode != PCP_SAMPLE_BILINEAR)) {
+      (params->sample_mode != PCP_SAMPLE_NEAREST && params->sample_mode != PCP_SAMPLE_BILINEAR) || params->frames_in_flight < 0 ||
+      params->frames_in_flight > pcp_ctx::kMaxFlight) {
     g_create_error = "pcp_create: invalid params";
     return PCP_EINVAL;
   }
@@ -93,11 +95,20 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
     if ((e = cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaEventCreateWithFlags(&ctx->ev_free[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
   }
+  ctx->flight = params->frames_in_flight > 0 ? params->frames_in_flight : 3;
+  {
+    const char* e_fl = std::getenv("PCP_FLIGHT");
+    if (e_fl && e_fl[0] >= '1' && e_fl[0] <= '0' + pcp_ctx::kMaxFlight) ctx->flight = e_fl[0] - '0';
+  }
+  for (int i = 0; i < pcp_ctx::kMaxFlight; i++) {
+    if ((e = cudaStreamCreateWithFlags(&ctx->fs[i].stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->fs[i].ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->fs[i].ev_done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+  }
   const size_t cells = (size_t)ctx->Wc * ctx->Hc;
-  if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * 2 * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
-  if ((e = cudaMalloc(&ctx->d_counters, 2 * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
-  launch_zgrid_init(ctx->d_zgrid, 2 * (int)cells, ctx->d_counters, ctx->own_stream);  // both buffers start clean
-  if ((e = cudaStreamSynchronize(ctx->own_stream)) != cudaSuccess) return bail("zgrid init", e);
+  if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
+  if ((e = cudaMalloc(&ctx->d_counters, pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+  if ((e = cudaMemset(ctx->d_counters, 0, pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMemset counters", e);
   if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
@@ -115,8 +126,13 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
 void pcp_destroy(pcp_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
-  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  ctx->drain();
   nccl_teardown(ctx);
+  for (int i = 0; i < pcp_ctx::kMaxFlight; i++) {
+    if (ctx->fs[i].stream) cudaStreamDestroy(ctx->fs[i].stream);
+    if (ctx->fs[i].ev_fork) cudaEventDestroy(ctx->fs[i].ev_fork);
+    if (ctx->fs[i].ev_done) cudaEventDestroy(ctx->fs[i].ev_done);
+  }
   ctx->free_cloud();
   for (int i = 0; i < pcp_ctx::kSlots; i++) {
     if (ctx->d_img[i]) cudaFree(ctx->d_img[i]);
@@ -137,7 +153,7 @@ void pcp_destroy(pcp_ctx* ctx) {
 int pcp_set_stream(pcp_ctx* ctx, void* cuda_stream) {
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
-  CU(cudaStreamSynchronize(ctx->stream));
+  CU(ctx->drain());
   ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
   return PCP_OK;
 }
@@ -147,7 +163,7 @@ int pcp_synchronize(pcp_ctx* ctx) {
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   CU(cudaStreamSynchronize(ctx->copy_stream));
-  CU(cudaStreamSynchronize(ctx->stream));
+  CU(ctx->drain());
   return PCP_OK;
 }
 
@@ -174,10 +190,25 @@ int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[
 // ---------------------------------------------------------------------------------------------------------------------
 // cloud
 // ---------------------------------------------------------------------------------------------------------------------
+cudaError_t pcp_ctx::join() {
+  if (!last_done) return cudaSuccess;
+  return cudaStreamWaitEvent(stream, last_done, 0);
+}
+
+cudaError_t pcp_ctx::drain() {
+  cudaError_t e = cudaSuccess;
+  for (int i = 0; i < kMaxFlight; i++)
+    if (fs[i].stream) { const cudaError_t r = cudaStreamSynchronize(fs[i].stream); if (r != cudaSuccess) e = r; }
+  if (stream) { const cudaError_t r = cudaStreamSynchronize(stream); if (r != cudaSuccess) e = r; }
+  return e;
+}
+
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
   F(d_cloud); F(d_perm); F(d_aabb); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
-  F(d_pix); F(d_idx); F(d_scratch);
+  F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt);
+  if (d_prebin_scratch) { cudaFree(d_prebin_scratch); d_prebin_scratch = nullptr; prebin_scratch_bytes = 0; }
+  out_points = 0;
   n = 0;
 }
 
@@ -195,8 +226,8 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   const uint32_t n_chunks = (uint32_t)((n + kChunk - 1) / kChunk);
   if (!ctx->d_perm) CU(cudaMalloc(&ctx->d_perm, sizeof(uint32_t) * n));
   if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
-  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks));
-  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->bbox, ctx->sm_count, ctx->stream));
+  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks * pcp_ctx::kMaxFlight));
+  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, &ctx->d_prebin_scratch, &ctx->prebin_scratch_bytes, ctx->sm_count, ctx->stream));
   ctx->n_chunks = n_chunks;
   // odd multiplier coprime with n_chunks: the visiting order (slot * mul) % n_chunks is a permutation of the chunks
   auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };
@@ -211,7 +242,7 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
 static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
   const size_t n1 = n ? n : 1;
   CU(cudaMalloc(&ctx->d_acc, sizeof(uint4) * n1));
-  CU(cudaMalloc(&ctx->d_records, sizeof(Record) * (n1 + 64)));
+  CU(cudaMalloc(&ctx->d_records, sizeof(Record) * (n1 + 64) * ctx->flight));
   if (ctx->prm.accum_mode == PCP_ACCUM_TOP5) {
     CU(cudaMalloc(&ctx->d_top_score, sizeof(float) * n1 * ctx->prm.top_m));
     CU(cudaMalloc(&ctx->d_top_rgbf, sizeof(uint32_t) * n1 * ctx->prm.top_m));
@@ -227,6 +258,7 @@ int pcp_reset_accumulators(pcp_ctx* ctx) {
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   const size_t n1 = ctx->n ? ctx->n : 1;
+  CU(ctx->join());  // frames in flight still update the accumulators
   if (ctx->d_acc) CU(cudaMemsetAsync(ctx->d_acc, 0, sizeof(uint4) * n1, ctx->stream));
   if (ctx->d_mask_acc) CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * n1, ctx->stream));
   if (ctx->d_top_frame) {
@@ -248,8 +280,9 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
   CU(cudaSetDevice(ctx->device));
   const bool reuse = ctx->d_cloud && ctx->n == n && n > 0;  // same-size cloud: keep every allocation, only re-upload
   const size_t n1 = n ? n : 1;
+  CU(ctx->join());  // frames in flight still read the cloud
   if (!reuse) {
-    CU(cudaStreamSynchronize(ctx->stream));
+    CU(ctx->drain());
     ctx->free_cloud();
     CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * n1));
   }
@@ -280,7 +313,7 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
 int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n) {
   if (!ctx || (!d_xyzi && n) || n >= 0xfffffff0ull) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
-  CU(cudaStreamSynchronize(ctx->stream));
+  CU(ctx->drain());
   ctx->free_cloud();
   CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * (n ? n : 1)));
   if (n) CU(cudaMemcpyAsync(ctx->d_cloud, d_xyzi, sizeof(float4) * n, cudaMemcpyDeviceToDevice, ctx->stream));

@@ -33,23 +33,37 @@ struct pcp_ctx {
   float4* d_aabb = nullptr;       // 2 float4 per chunk of 128 sorted points (pre-binned mode)
   uint4* d_active = nullptr;      // per-frame list of chunks to scan + their cell rectangle / distance bound (pre-binned mode)
   uint32_t n_chunks = 0, chunk_mul = 1;
-  float bbox[6] = {0, 0, 0, 0, 0, 0};  // finite bounding box of the cloud {lo.xyz, hi.xyz} (pre-binned mode)
+  void* d_prebin_scratch = nullptr;  // sort keys / temporaries of the pre-binning, kept across uploads
+  size_t prebin_scratch_bytes = 0;
+  uint8_t* d_out_rgb = nullptr;      // staging of pcp_finalize's host outputs, kept across calls
+  uint32_t* d_out_cnt = nullptr;
+  size_t out_points = 0;
   uint4* d_acc = nullptr;         // N x 16 B  {sum_r,sum_g,sum_b,count}
   uint2* d_mask_acc = nullptr;    // N x 8 B   {hits, max}; allocated at the first frame that carries a mask
   float* d_top_score = nullptr;   // top_m x N
   uint32_t* d_top_rgbf = nullptr;
   uint32_t* d_top_frame = nullptr;
-  pcp::Record* d_records = nullptr;  // N x 32 B worst case
+  pcp::Record* d_records = nullptr;  // flight x (N + 64) x 32 B worst case (one region per frame slot)
   uint32_t* d_vis_bits = nullptr;    // ceil(N/32) words, lazily allocated
   int32_t* d_pix = nullptr;          // N, lazily allocated
   int32_t* d_idx = nullptr;          // N, lazily allocated (pcp_cull)
   uint32_t* d_scratch = nullptr;     // compaction tile sums
 
-  // double-buffered per-frame scratch: frame f uses buffer f & 1; its resolve kernel re-initialises the other buffer for
-  // frame f+1, so a frame is two launches (scan, resolve) and no separate clear
-  unsigned long long* d_zgrid = nullptr;       // 2 x Wc*Hc packed (fl32 depth, point index) keys
-  pcp::FrameCounters* d_counters = nullptr;    // 2 entries
-  int buf = 0;
+  // Frame slots: frame f runs on slot f % flight, each slot with its own stream, z-grid, counters, record region and
+  // active-chunk list.  The scan of frame f+1 therefore overlaps the tail of the scan of frame f and its resolve kernel
+  // (whose accumulator updates stay ordered: resolve f+1 waits for resolve f).  Work is forked from / joined to ctx->stream.
+  static constexpr int kMaxFlight = 3;
+  struct FrameSlot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_done = nullptr;
+  };
+  FrameSlot fs[kMaxFlight];
+  int flight = 3;                 // frames in flight (pcp_params.frames_in_flight; PCP_FLIGHT=1..3 overrides)
+  uint64_t frames_run = 0;        // frames submitted since creation (slot = frames_run % flight)
+  int last_slot = 0;              // slot of the last submitted frame
+  cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
+  unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys
+  pcp::FrameCounters* d_counters = nullptr;    // kMaxFlight entries
   pcp::FrameCounters* h_counters = nullptr;  // pinned
   uint32_t* d_total = nullptr;
 
@@ -71,6 +85,8 @@ struct pcp_ctx {
 
   void fail(const char* fmt, ...);
   void free_cloud();
+  cudaError_t join();   // ctx->stream waits (asynchronously) for the last submitted frame
+  cudaError_t drain();  // host waits for every frame slot and ctx->stream
 };
 
 int scan_ctas_per_sm();

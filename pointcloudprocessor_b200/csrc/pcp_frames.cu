@@ -73,9 +73,11 @@ int ensure_outputs(pcp_ctx* ctx, bool vis, bool pix) {
   return PCP_OK;
 }
 
-// Enqueue init + scan + resolve for one frame on ctx->stream.
+// Enqueue z-grid clear + classify/scan + resolve for one frame on its frame slot's stream (forked from ctx->stream).
+// img_ready: event the resolve kernel must wait for (the image upload), or null; img_free: recorded after the resolve kernel.
 int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t pitch, const uint8_t* d_mask, size_t mask_pitch,
-              bool want_vis, bool want_pix, bool accumulate, bool count_candidates) {
+              bool want_vis, bool want_pix, bool accumulate, bool count_candidates, cudaEvent_t img_ready = nullptr,
+              cudaEvent_t img_free = nullptr) {
   if (!ctx->d_cloud) { ctx->fail("no cloud: call pcp_set_cloud first"); return PCP_EINVAL; }
   int rc = ensure_outputs(ctx, want_vis, want_pix);
   if (rc != PCP_OK) return rc;
@@ -83,8 +85,15 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
     CU(cudaMalloc(&ctx->d_mask_acc, sizeof(uint2) * (ctx->n ? ctx->n : 1)));
     CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * (ctx->n ? ctx->n : 1), ctx->stream));
   }
+  if (want_vis || want_pix) CU(ctx->join());  // the previous frame's resolve kernel may still write these shared buffers
   if (want_vis) CU(cudaMemsetAsync(ctx->d_vis_bits, 0, sizeof(uint32_t) * ((ctx->n + 31) / 32), ctx->stream));
   if (want_pix) CU(cudaMemsetAsync(ctx->d_pix, 0xff, sizeof(int32_t) * ctx->n, ctx->stream));
+  // fork: everything enqueued on ctx->stream so far (cloud upload, accumulator reset, the memsets above) precedes this frame
+  const int si = (int)(ctx->frames_run % (uint64_t)ctx->flight);
+  pcp_ctx::FrameSlot& slot = ctx->fs[si];
+  cudaStream_t st = slot.stream;
+  CU(cudaEventRecord(slot.ev_fork, ctx->stream));
+  CU(cudaStreamWaitEvent(st, slot.ev_fork, 0));
 
   cudaEvent_t* pe = nullptr;
   if (ctx->profiling) {
@@ -97,41 +106,41 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
     ctx->prof_used += 4;
   }
   const int cells = ctx->Wc * ctx->Hc;
-  const int b = ctx->buf;
-  ctx->buf ^= 1;
-  unsigned long long* zg = ctx->d_zgrid + (size_t)b * (cells ? cells : 1);
-  FrameCounters* ctr = ctx->d_counters + b;
-  if (pe) CU(cudaEventRecord(pe[1], ctx->stream));
+  unsigned long long* zg = ctx->d_zgrid + (size_t)si * (cells ? cells : 1);
+  FrameCounters* ctr = ctx->d_counters + si;
+  Record* recs = ctx->d_records + (size_t)si * ((ctx->n ? ctx->n : 1) + 64);
+  launch_zgrid_init(zg, cells, ctr, st);  // this slot's z-grid and counters (overlaps the other slots' kernels)
+  if (pe) CU(cudaEventRecord(pe[1], st));
   ScanArgs sa;
   std::memset(&sa, 0, sizeof(sa));
   sa.cloud = ctx->d_cloud;
   sa.perm = ctx->d_perm;
   sa.aabb = ctx->d_perm ? ctx->d_aabb : nullptr;
-  sa.active = ctx->d_active;
+  sa.active = ctx->d_active ? ctx->d_active + (size_t)si * ctx->n_chunks : nullptr;
   sa.n_chunks = ctx->n_chunks;
   sa.chunk_mul = ctx->chunk_mul;
   sa.zgrid = zg;
-  sa.records = ctx->d_records;
+  sa.records = recs;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
   // shared-memory early-z variant when the z-grid's high words fit beside the queues (see scan_smz_kernel)
   const bool smz = ctx->use_smz && !ctx->d_perm && fp.use_prefilter && fp.depth_culling && !fp.use_T && scan_smz_smem_bytes(cells) <= 232448;
   if (smz) {
-    if (launch_scan_smz(sa, fp, ctx->sm_count, count_candidates, ctx->stream) != 0) { ctx->fail("scan_smz_kernel: cannot reserve shared memory"); return PCP_ECUDA; }
+    if (launch_scan_smz(sa, fp, ctx->sm_count, count_candidates, st) != 0) { ctx->fail("scan_smz_kernel: cannot reserve shared memory"); return PCP_ECUDA; }
   } else {
-    launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->stream);
+    launch_scan(sa, fp, ctx->scan_grid, count_candidates, st);
   }
-  if (pe) CU(cudaEventRecord(pe[2], ctx->stream));
+  if (pe) CU(cudaEventRecord(pe[2], st));
+  // the resolve kernels update the accumulators without atomics: they run in frame order
+  if (ctx->last_done && ctx->flight > 1) CU(cudaStreamWaitEvent(st, ctx->last_done, 0));
+  if (img_ready) CU(cudaStreamWaitEvent(st, img_ready, 0));
 
   ResolveArgs ra;
   std::memset(&ra, 0, sizeof(ra));
-  ra.records = ctx->d_records;
+  ra.records = recs;
   ra.zgrid = zg;
   ra.counters = ctr;
   ra.perm = ctx->d_perm;
-  ra.next_zgrid = ctx->d_zgrid + (size_t)(b ^ 1) * (cells ? cells : 1);
-  ra.next_counters = ctx->d_counters + (b ^ 1);
-  ra.cells = cells;
   ra.bgr = accumulate ? d_bgr : nullptr;
   ra.pitch = pitch;
   ra.mask = accumulate ? d_mask : nullptr;
@@ -147,15 +156,21 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ra.top_m = ctx->prm.top_m;
   ra.accum_mode = ctx->prm.accum_mode;
   ra.sample_mode = ctx->prm.sample_mode;
-  launch_resolve(ra, fp, ctx->resolve_grid, ctx->stream);
-  if (pe) CU(cudaEventRecord(pe[3], ctx->stream));
-  ctx->launches += ctx->d_perm ? 3 : 2;
+  launch_resolve(ra, fp, ctx->resolve_grid, st);
+  if (pe) CU(cudaEventRecord(pe[3], st));
+  CU(cudaEventRecord(slot.ev_done, st));
+  if (img_free) CU(cudaEventRecord(img_free, st));
+  ctx->last_done = slot.ev_done;
+  ctx->last_slot = si;
+  ctx->frames_run++;
+  ctx->launches += ctx->d_perm ? 4 : 3;
   CU(cudaGetLastError());
   return PCP_OK;
 }
 
 int fetch_outputs(pcp_ctx* ctx, pcp_frame_out* out) {
-  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters + (ctx->buf ^ 1), sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(ctx->join());
+  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters + ctx->last_slot, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->visible_bits) CU(cudaMemcpyAsync(out->visible_bits, ctx->d_vis_bits, sizeof(uint32_t) * ((ctx->n + 31) / 32), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->pixel_index) CU(cudaMemcpyAsync(out->pixel_index, ctx->d_pix, sizeof(int32_t) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -180,10 +195,8 @@ int frame_params_for_pose(pcp_ctx* ctx, const double pose7[7], const double* T_o
 
 }  // namespace
 
-extern "C" {
-
-int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
-                            const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out) {
+static int submit_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
+                         const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out, cudaEvent_t img_ready, cudaEvent_t img_free) {
   if (!ctx) return PCP_EINVAL;
   if (!d_bgr || pitch < (size_t)ctx->prm.image_width * 3 || (d_mask && mask_pitch < (size_t)ctx->prm.image_width)) {
     ctx->fail("pcp_submit_frame: bad image/pitch");
@@ -194,11 +207,18 @@ int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T
   int rc = frame_params_for_pose(ctx, pose7, T_opt16, fp);
   if (rc != PCP_OK) return rc;
   rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true,
-                 out && !(out->flags & PCP_OUT_SKIP_CANDIDATES));
+                 out && !(out->flags & PCP_OUT_SKIP_CANDIDATES), img_ready, img_free);
   if (rc != PCP_OK) return rc;
   ctx->frame_index++;
   if (out) return fetch_outputs(ctx, out);
   return PCP_OK;
+}
+
+extern "C" {
+
+int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
+                            const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out) {
+  return submit_device(ctx, pose7, T_opt16, d_bgr, pitch, d_mask, mask_pitch, out, nullptr, nullptr);
 }
 
 int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* bgr, size_t pitch,
@@ -216,17 +236,15 @@ int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16,
   CU(cudaMemcpy2DAsync(ctx->d_img[s], W * 3, bgr, pitch, W * 3, H, cudaMemcpyHostToDevice, ctx->copy_stream));
   if (mask) CU(cudaMemcpy2DAsync(ctx->d_mask[s], W, mask, mask_pitch, W, H, cudaMemcpyHostToDevice, ctx->copy_stream));
   CU(cudaEventRecord(ctx->ev_copied[s], ctx->copy_stream));
-  CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[s], 0));
-  const int rc = pcp_submit_frame_device(ctx, pose7, T_opt16, ctx->d_img[s], W * 3, mask ? ctx->d_mask[s] : nullptr, W, out);
-  if (rc != PCP_OK) return rc;
-  CU(cudaEventRecord(ctx->ev_free[s], ctx->stream));
-  return PCP_OK;
+  // only the resolve kernel reads the image: the scan of this frame does not wait for the upload
+  return submit_device(ctx, pose7, T_opt16, ctx->d_img[s], W * 3, mask ? ctx->d_mask[s] : nullptr, W, out, ctx->ev_copied[s], ctx->ev_free[s]);
 }
 
 static int cull_common(pcp_ctx* ctx, const FrameParams& fp, int32_t* idx_out, size_t* m_out) {
   if (!idx_out || !m_out) { ctx->fail("pcp_cull: null output"); return PCP_EINVAL; }
   int rc = run_frame(ctx, fp, nullptr, 0, nullptr, 0, true, false, false, false);
   if (rc != PCP_OK) return rc;
+  CU(ctx->join());
   const size_t n1 = ctx->n ? ctx->n : 1;
   if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n1));
   if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)ctx->n)));
@@ -264,6 +282,7 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
+  CU(ctx->join());
   // per-point state lives in sorted order when the cloud is pre-binned: hand it back in the caller's order
   uint32_t* d_tmp = nullptr;
   if (ctx->d_perm) CU(cudaMalloc(&d_tmp, sizeof(uint4) * ctx->n));
@@ -295,8 +314,8 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
 int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]) {
   if (!ctx || !out16) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
-  CU(cudaStreamSynchronize(ctx->stream));
-  CU(cudaMemcpy(out16, ctx->d_counters + (ctx->buf ^ 1), 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  CU(ctx->drain());
+  CU(cudaMemcpy(out16, ctx->d_counters + ctx->last_slot, 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
   return PCP_OK;
 }
 
@@ -311,10 +330,10 @@ int pcp_profile_enable(pcp_ctx* ctx, int on) {
 int pcp_profile_read(pcp_ctx* ctx, double ms3[3], uint64_t* frames) {
   if (!ctx || !ms3) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
-  CU(cudaStreamSynchronize(ctx->stream));
+  CU(ctx->drain());
   ms3[0] = ms3[1] = ms3[2] = 0.0;
   for (size_t i = 0; i + 4 <= ctx->prof_used; i += 4) {
-    for (int k = 1; k < 3; k++) {  // interval 0 (the separate z-grid clear) no longer exists: the resolve kernel clears
+    for (int k = 1; k < 3; k++) {  // interval 0 is unused (the z-grid clear precedes the first event)
       float ms = 0.f;
       CU(cudaEventElapsedTime(&ms, ctx->prof_events[i + k], ctx->prof_events[i + k + 1]));
       ms3[k] += ms;
@@ -330,6 +349,7 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
+  CU(ctx->join());
   if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->stream);
   else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
   ctx->launches++;
@@ -343,17 +363,21 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
   const size_t n = ctx->n;
   if (n == 0) return PCP_OK;
-  uint8_t* d_rgb = nullptr;
-  uint32_t* d_cnt = nullptr;
-  if (rgb_out) CU(cudaMallocAsync(&d_rgb, n * 3, ctx->stream));
-  if (count_out) CU(cudaMallocAsync(&d_cnt, n * sizeof(uint32_t), ctx->stream));
+  CU(ctx->join());
+  if (ctx->out_points < n) {
+    if (ctx->d_out_rgb) { cudaFree(ctx->d_out_rgb); ctx->d_out_rgb = nullptr; }
+    if (ctx->d_out_cnt) { cudaFree(ctx->d_out_cnt); ctx->d_out_cnt = nullptr; }
+    CU(cudaMalloc(&ctx->d_out_rgb, n * 3));
+    CU(cudaMalloc(&ctx->d_out_cnt, n * sizeof(uint32_t)));
+    ctx->out_points = n;
+  }
+  uint8_t* d_rgb = rgb_out ? ctx->d_out_rgb : nullptr;
+  uint32_t* d_cnt = count_out ? ctx->d_out_cnt : nullptr;
   if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm, (uint32_t)n, d_rgb, d_cnt, ctx->stream);
   else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
   ctx->launches++;
   if (rgb_out) CU(cudaMemcpyAsync(rgb_out, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream));
   if (count_out) CU(cudaMemcpyAsync(count_out, d_cnt, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-  if (d_rgb) CU(cudaFreeAsync(d_rgb, ctx->stream));
-  if (d_cnt) CU(cudaFreeAsync(d_cnt, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   return PCP_OK;
 }

@@ -83,9 +83,6 @@ struct ResolveArgs {
   const unsigned long long* __restrict__ zgrid;
   FrameCounters* counters;
   const uint32_t* __restrict__ perm;  // pre-binned: record.idx is a sorted position; outputs in caller order go through perm
-  unsigned long long* next_zgrid;     // the other z-grid buffer, re-initialised here for the next frame
-  FrameCounters* next_counters;
-  int cells;
   const uint8_t* __restrict__ bgr; size_t pitch;
   const uint8_t* __restrict__ mask; size_t mask_pitch;
   uint4* acc;                 // N x {sum_r,sum_g,sum_b,count}
@@ -111,7 +108,8 @@ void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uin
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
 // pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)
-cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, float bbox6[6], int sm_count, cudaStream_t s);
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, void** scratch, size_t* scratch_bytes, int sm_count,
+                         cudaStream_t s);
 void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s);
 // ascending index list from a visibility bitmask; returns through d_total the number of set bits
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,

@@ -29,7 +29,7 @@ static constexpr int kCandCap = 32 * (PCP_UNROLL_CAP + 1); // per-warp candidate
 __global__ void zgrid_init_kernel(unsigned long long* zgrid, int cells, FrameCounters* counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < cells) zgrid[i] = kZInit;
-  if (i < (int)(2 * sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(counters)[i] = 0u;
+  if (i < (int)(sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(counters)[i] = 0u;
 }
 
 void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s) {
@@ -903,10 +903,6 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
     if (cta_counts[0]) atomicAdd(&a.counters->n_visible, cta_counts[0]);
     if (cta_counts[1]) atomicAdd(&a.counters->n_colored, cta_counts[1]);
   }
-  // clear the OTHER buffer for the next frame (nobody reads it during this kernel)
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.cells; i += gridDim.x * blockDim.x) a.next_zgrid[i] = kZInit;
-  if (blockIdx.x == 0 && threadIdx.x < sizeof(FrameCounters) / sizeof(unsigned int))
-    reinterpret_cast<unsigned int*>(a.next_counters)[threadIdx.x] = 0u;
 }
 
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s) {

@@ -88,6 +88,7 @@ int pcp_allreduce(pcp_ctx* ctx) {
   if (!ctx->nccl_comm) { ctx->fail("pcp_allreduce: call pcp_nccl_init first"); return PCP_ENCCL; }
   if (ctx->prm.accum_mode != PCP_ACCUM_SUM) { ctx->fail("pcp_allreduce: only PCP_ACCUM_SUM accumulators are all-reducible"); return PCP_EINVAL; }
   if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->fail("cudaSetDevice failed"); return PCP_ECUDA; }
+  if (ctx->join() != cudaSuccess) { ctx->fail("pcp_allreduce: cudaStreamWaitEvent failed"); return PCP_ECUDA; }
   int rc = api().all_reduce(ctx->d_acc, ctx->d_acc, ctx->n * 4, kNcclUint32, kNcclSum, (NcclComm)ctx->nccl_comm, ctx->stream);
   if (rc == 0 && ctx->d_mask_acc) {
     // hits are summed; the per-point maximum is not a sum, so it is left rank-local (documented in DESIGN.md)

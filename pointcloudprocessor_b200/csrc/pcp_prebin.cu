@@ -119,51 +119,45 @@ __global__ void chunk_aabb_kernel(const float4* __restrict__ pts, uint32_t n, ui
 }  // namespace
 
 // Sorts `d_cloud` (n points, in place through a temporary) and fills d_perm (sorted position -> original index) and
-// d_aabb (2 float4 per chunk).  All buffers are allocated by the caller except the temporaries.  Synchronises the stream.
-cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, float bbox6[6], int sm_count, cudaStream_t s) {
-  for (int k = 0; k < 6; k++) bbox6[k] = 0.0f;
+// d_aabb (2 float4 per chunk).  All buffers are allocated by the caller.
+// `scratch` is a context-owned device buffer that is grown on demand and kept (cudaMalloc/cudaFree per upload cost tens of
+// milliseconds of host time on a busy box); nothing here synchronises the stream.
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, void** scratch, size_t* scratch_bytes, int sm_count,
+                         cudaStream_t s) {
   if (n == 0) return cudaSuccess;
   cudaError_t e;
-  int* d_box = nullptr;
-  unsigned long long *d_keys = nullptr, *d_keys_out = nullptr;
-  uint32_t* d_idx = nullptr;
-  float4* d_tmp = nullptr;
-  void* d_temp = nullptr;
+  auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
   size_t temp_bytes = 0;
-  auto cleanup = [&]() {
-    cudaFree(d_box); cudaFree(d_keys); cudaFree(d_keys_out); cudaFree(d_idx); cudaFree(d_tmp); cudaFree(d_temp);
-  };
-#define PB(call) do { e = (call); if (e != cudaSuccess) { cleanup(); return e; } } while (0)
-  PB(cudaMalloc(&d_box, 6 * sizeof(int)));
-  PB(cudaMalloc(&d_keys, sizeof(unsigned long long) * n));
-  PB(cudaMalloc(&d_keys_out, sizeof(unsigned long long) * n));
-  PB(cudaMalloc(&d_idx, sizeof(uint32_t) * n));
-  PB(cudaMalloc(&d_tmp, sizeof(float4) * n));
-  const int h_box[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
-  PB(cudaMemcpyAsync(d_box, h_box, sizeof(h_box), cudaMemcpyHostToDevice, s));
+  e = cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr, (uint32_t*)nullptr,
+                                      (uint32_t*)nullptr, (int)n, 0, 63, s);
+  if (e != cudaSuccess) return e;
+  const size_t o_box = 0, o_keys = up(6 * sizeof(int)), o_keys_out = o_keys + up(sizeof(unsigned long long) * n),
+               o_idx = o_keys_out + up(sizeof(unsigned long long) * n), o_tmp = o_idx + up(sizeof(uint32_t) * n),
+               o_temp = o_tmp + up(sizeof(float4) * n), total = o_temp + up(temp_bytes ? temp_bytes : 1);
+  if (*scratch_bytes < total) {
+    if (*scratch) { cudaStreamSynchronize(s); cudaFree(*scratch); *scratch = nullptr; *scratch_bytes = 0; }
+    if ((e = cudaMalloc(scratch, total)) != cudaSuccess) return e;
+    *scratch_bytes = total;
+  }
+  unsigned char* base = static_cast<unsigned char*>(*scratch);
+  int* d_box = reinterpret_cast<int*>(base + o_box);
+  unsigned long long* d_keys = reinterpret_cast<unsigned long long*>(base + o_keys);
+  unsigned long long* d_keys_out = reinterpret_cast<unsigned long long*>(base + o_keys_out);
+  uint32_t* d_idx = reinterpret_cast<uint32_t*>(base + o_idx);
+  float4* d_tmp = reinterpret_cast<float4*>(base + o_tmp);
+  void* d_temp = base + o_temp;
+  static const int h_box[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, (int)0x80000000, (int)0x80000000, (int)0x80000000};
+  if ((e = cudaMemcpyAsync(d_box, h_box, sizeof(h_box), cudaMemcpyHostToDevice, s)) != cudaSuccess) return e;
   const int grid = sm_count * 8;
   bbox_kernel<<<grid, 256, 0, s>>>(d_cloud, n, reinterpret_cast<float*>(d_box));
   morton_kernel<<<grid, 256, 0, s>>>(d_cloud, n, d_box, d_keys, d_idx);
-  PB(cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 63, s));
-  PB(cudaMalloc(&d_temp, temp_bytes ? temp_bytes : 1));
-  PB(cub::DeviceRadixSort::SortPairs(d_temp, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 63, s));  // stable: deterministic
+  e = cub::DeviceRadixSort::SortPairs(d_temp, temp_bytes, d_keys, d_keys_out, d_idx, d_perm, (int)n, 0, 63, s);  // stable: deterministic
+  if (e != cudaSuccess) return e;
   gather_kernel<<<grid, 256, 0, s>>>(d_cloud, d_perm, n, d_tmp);
-  PB(cudaMemcpyAsync(d_cloud, d_tmp, sizeof(float4) * n, cudaMemcpyDeviceToDevice, s));
+  if ((e = cudaMemcpyAsync(d_cloud, d_tmp, sizeof(float4) * n, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) return e;
   const uint32_t n_chunks = (n + kChunk - 1) / kChunk;
   chunk_aabb_kernel<<<(n_chunks * 32 + 255) / 256, 256, 0, s>>>(d_cloud, n, n_chunks, d_aabb);
-  PB(cudaGetLastError());
-  int h_out[6];
-  PB(cudaMemcpyAsync(h_out, d_box, sizeof(h_out), cudaMemcpyDeviceToHost, s));
-  PB(cudaStreamSynchronize(s));
-  for (int k = 0; k < 6; k++) {  // undo the order-preserving int mapping; no finite point at all leaves the initial values
-    const int v = h_out[k] >= 0 ? h_out[k] : h_out[k] ^ 0x7fffffff;
-    float f;
-    std::memcpy(&f, &v, sizeof(f));
-    bbox6[k] = (h_out[0] == 0x7fffffff) ? 0.0f : f;
-  }
-#undef PB
-  cleanup();
-  return cudaSuccess;
+  return cudaGetLastError();
 }
 
 }  // namespace pcp
