@@ -248,6 +248,29 @@ inline int color_pixel(const Camera& cam, int W, int H, float xf, float yf, floa
   return -1;
 }
 
+// BILINEAR sampling (north_star (c); an EXTENSION: the reference samples the nearest pixel, cpp:752-762).  Restated here as
+// the definition the CUDA path must reproduce bit for bit.  The point is coloured iff the nearest-pixel gate passes (same
+// coloured set as the reference); (ud, vd) is the double projection; x0 = int(ud), y0 = int(vd) (truncation == floor since
+// both are > -1 inside the gate; a fraction below 0 is clamped to 0); x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, H - 1); fx = ud - x0, fy = vd - y0;
+//   val = (p00 * (1 - fx) + p10 * fx) * (1 - fy) + (p01 * (1 - fx) + p11 * fx) * fy      (double, every operation rounded)
+// accumulated as 8.8 fixed point q = (uint32)(val * 256 + 0.5) in the same u32 sums as the nearest mode; the finalize step
+// rounds the mean: min(255, (sum / count + 128) >> 8).  Error against real-valued bilinear interpolation: < 1/256 of a level
+// per observation plus the final rounding, i.e. well inside the 1/255 per channel of north_star.
+inline uint32_t bilinear_q(const uint8_t* img, size_t pitch, int W, int H, int ch, double ud, double vd) {
+  const int x0 = (int)ud, y0 = (int)vd;
+  const int x1 = x0 + 1 < W ? x0 + 1 : W - 1, y1 = y0 + 1 < H ? y0 + 1 : H - 1;
+  double fx = ud - (double)x0, fy = vd - (double)y0;
+  if (fx < 0.0) fx = 0.0;   // ud in (-1, 0) truncates to column 0 (the reference's gate accepts it): no extrapolation
+  if (fy < 0.0) fy = 0.0;
+  const double gx = 1.0 - fx, gy = 1.0 - fy;
+  const double p00 = img[(size_t)y0 * pitch + (size_t)x0 * 3 + ch], p10 = img[(size_t)y0 * pitch + (size_t)x1 * 3 + ch];
+  const double p01 = img[(size_t)y1 * pitch + (size_t)x0 * 3 + ch], p11 = img[(size_t)y1 * pitch + (size_t)x1 * 3 + ch];
+  const double top = p00 * gx + p10 * fx;
+  const double bot = p01 * gx + p11 * fx;
+  const double val = top * gy + bot * fy;
+  return (uint32_t)(val * 256.0 + 0.5);
+}
+
 // Scores.  include/PointCloudProcessor.hpp:205-236, src/PointCloudProcessor.cpp:586-588.  [D11]
 inline float orientation_score(float px, float py, float pz, const double pose[7]) {
   const double vx = (double)px - pose[0], vy = (double)py - pose[1], vz = (double)pz - pose[2];
@@ -281,6 +304,7 @@ struct Colorizer {
   std::vector<uint32_t> mask_hits;     // n : #frames whose mask pixel == 255 (cpp:806)
   std::vector<uint32_t> mask_max;      // n : max mask value seen (cpp:804)
   bool keep_obs = false;
+  int sample_mode = 0;                 // 0 nearest (reference), 1 bilinear (extension, see bilinear_q)
   std::vector<std::vector<Obs>> obs;   // per-point observation lists (include/RGBCloud.hpp:29-41)
   int frame_counter = 0;
 };
@@ -351,9 +375,20 @@ FrameResult colorize_frame(Colorizer& S, const double pose[7], const double* T_o
       if (pix) pix[c.idx] = p;
       const int v = p / S.W, u = p % S.W;
       const uint8_t* px = bgr + (size_t)v * pitch + (size_t)u * 3;
-      const uint8_t b = px[0], g = px[1], r = px[2];          // cpp:760-762
+      uint8_t b = px[0], g = px[1], r = px[2];                // cpp:760-762
       uint32_t* a = &S.acc[4 * (size_t)c.idx];
-      a[0] += r; a[1] += g; a[2] += b; a[3] += 1;
+      if (S.sample_mode == 1) {
+        double ud, vd;
+        project(S.cam, (double)c.x, (double)c.y, (double)c.z, ud, vd);   // the same doubles color_pixel truncated
+        const uint32_t qr = bilinear_q(bgr, pitch, S.W, S.H, 2, ud, vd), qg = bilinear_q(bgr, pitch, S.W, S.H, 1, ud, vd),
+                       qb = bilinear_q(bgr, pitch, S.W, S.H, 0, ud, vd);
+        a[0] += qr; a[1] += qg; a[2] += qb; a[3] += 1;
+        r = (uint8_t)((qr + 128) >> 8 > 255 ? 255 : (qr + 128) >> 8);   // 8-bit colour of the observation (TOP5 lists)
+        g = (uint8_t)((qg + 128) >> 8 > 255 ? 255 : (qg + 128) >> 8);
+        b = (uint8_t)((qb + 128) >> 8 > 255 ? 255 : (qb + 128) >> 8);
+      } else {
+        a[0] += r; a[1] += g; a[2] += b; a[3] += 1;
+      }
       if (mask) {                                             // generateSegmentMap cpp:783-815
         const uint8_t mv = mask[(size_t)v * mask_pitch + u];
         if (mv == 255) S.mask_hits[c.idx] += 1;
@@ -503,6 +538,7 @@ void* orc_colorizer_create(const orc_camera* c, int W, int H, int cullW, int cul
   return S;
 }
 void orc_colorizer_destroy(void* h) { delete (Colorizer*)h; }
+void orc_colorizer_set_sample_mode(void* h, int mode) { ((Colorizer*)h)->sample_mode = mode; }
 
 void orc_colorizer_frame(void* h, const double* pose7, const double* T_opt16, const uint8_t* bgr, size_t pitch, const uint8_t* mask,
                          size_t mask_pitch, uint8_t* vis, int32_t* pix, int threads, int* counts3) {
@@ -522,7 +558,11 @@ void orc_colorizer_finalize_sum(void* h, uint8_t* rgb /*n x 3*/) {
   Colorizer* S = (Colorizer*)h;
   for (size_t i = 0; i < S->n; i++) {
     const uint32_t* a = &S->acc[4 * i];
-    for (int k = 0; k < 3; k++) rgb[3 * i + k] = a[3] ? (uint8_t)(a[k] / a[3]) : 0;
+    for (int k = 0; k < 3; k++) {
+      uint32_t m = a[3] ? a[k] / a[3] : 0;
+      if (S->sample_mode == 1) { m = (m + 128) >> 8; if (m > 255) m = 255; }   // 8.8 fixed point mean, rounded
+      rgb[3 * i + k] = (uint8_t)m;
+    }
   }
 }
 

@@ -117,7 +117,7 @@ def scores(pts_cam, pose7):
 class Colorizer:
     """The loop body of pcdColorizationAndSmooth (src/PointCloudProcessor.cpp:488-595) on the CPU."""
 
-    def __init__(self, cam, W, H, xyzi, cull_size=None, ds=14, tol=0.05, keep_obs=False):
+    def __init__(self, cam, W, H, xyzi, cull_size=None, ds=14, tol=0.05, keep_obs=False, bilinear=False):
         self.cam, self.W, self.H = cam, W, H
         self.xyzi = np.ascontiguousarray(xyzi, np.float32)
         assert self.xyzi.ndim == 2 and self.xyzi.shape[1] == 4
@@ -125,6 +125,8 @@ class Colorizer:
         cw, ch = cull_size if cull_size is not None else (W, H)
         self._h = C.c_void_p(lib().orc_colorizer_create(C.byref(cam), W, H, cw, ch, ds, C.c_double(tol), _p(self.xyzi),
                                                         C.c_size_t(self.n), int(keep_obs)))
+        if bilinear:
+            lib().orc_colorizer_set_sample_mode(self._h, 1)
 
     def close(self):
         if self._h:

@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import ACCUM_SUM, ACCUM_TOP5, Camera, FrameOut, Params
+from ._capi import ACCUM_SUM, ACCUM_TOP5, SAMPLE_BILINEAR, SAMPLE_NEAREST, Camera, FrameOut, Params
 
 
 class PcpError(RuntimeError):

@@ -104,7 +104,7 @@ size_t scan_smz_smem_bytes(int cells);
 int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
-void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);
+void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
 // pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)

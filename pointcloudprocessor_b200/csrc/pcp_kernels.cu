@@ -779,6 +779,35 @@ __device__ __forceinline__ void top_insert(const ResolveArgs& a, uint32_t idx, f
   }
 }
 
+// PCP_SAMPLE_BILINEAR (north_star (c); the reference samples the nearest pixel): 8.8 fixed-point bilinear value of the three
+// channels at the double projection of the record's float point, operation by operation as oracle/pcp_oracle.cpp bilinear_q.
+// Kept out of line: it is the rare mode and must not cost the nearest path registers.
+__device__ __noinline__ void bilinear_sample(const uint8_t* __restrict__ bgr, size_t pitch, const FrameParams& fp, const Record* rp, int pix,
+                                             uint32_t& qr, uint32_t& qg, uint32_t& qb) {
+  const float rx = rp->x, ry = rp->y, rz = rp->z;
+  double u, v;
+  project(fp.cam, (double)rx, (double)ry, (double)rz, u, v);  // the doubles whose truncation is `pix`
+  const int y0 = pix / fp.imgW, x0 = pix - y0 * fp.imgW;
+  const int x1 = x0 + 1 < fp.imgW ? x0 + 1 : fp.imgW - 1, y1 = y0 + 1 < fp.imgH ? y0 + 1 : fp.imgH - 1;
+  double fx = __dsub_rn(u, (double)x0), fy = __dsub_rn(v, (double)y0);
+  if (fx < 0.0) fx = 0.0;  // u in (-1, 0) truncates to column 0: no extrapolation
+  if (fy < 0.0) fy = 0.0;
+  const double gx = __dsub_rn(1.0, fx), gy = __dsub_rn(1.0, fy);
+  const uint8_t* r0 = bgr + (size_t)y0 * pitch;
+  const uint8_t* r1 = bgr + (size_t)y1 * pitch;
+  uint32_t q[3];
+#pragma unroll
+  for (int ch = 0; ch < 3; ch++) {
+    const double p00 = (double)__ldg(r0 + (size_t)x0 * 3 + ch), p10 = (double)__ldg(r0 + (size_t)x1 * 3 + ch);
+    const double p01 = (double)__ldg(r1 + (size_t)x0 * 3 + ch), p11 = (double)__ldg(r1 + (size_t)x1 * 3 + ch);
+    const double top = __dadd_rn(__dmul_rn(p00, gx), __dmul_rn(p10, fx));
+    const double bot = __dadd_rn(__dmul_rn(p01, gx), __dmul_rn(p11, fx));
+    const double val = __dadd_rn(__dmul_rn(top, gy), __dmul_rn(bot, fy));
+    q[ch] = (uint32_t)__double2uint_rz(__dadd_rn(__dmul_rn(val, 256.0), 0.5));
+  }
+  qb = q[0]; qg = q[1]; qr = q[2];
+}
+
 // kRes records per thread, processed phase by phase so that the kRes independent chains of dependent loads (record ->
 // z-grid cell -> pixel -> accumulator) are in flight together: the kernel is latency-bound, not bandwidth-bound.  Only the
 // fields every record needs (index, dist, cell, pixel) stay in registers; x,y,z are re-read for the rare paths that use
@@ -868,7 +897,14 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       if (!live[k]) continue;
-      s[k].x += rgb[k] & 255u; s[k].y += (rgb[k] >> 8) & 255u; s[k].z += rgb[k] >> 16; s[k].w += 1u;
+      if (a.sample_mode == 0) {
+        s[k].x += rgb[k] & 255u; s[k].y += (rgb[k] >> 8) & 255u; s[k].z += rgb[k] >> 16; s[k].w += 1u;
+      } else {
+        uint32_t qr, qg, qb;
+        bilinear_sample(a.bgr, a.pitch, fp, a.records + (base + k * blockDim.x + threadIdx.x), pix[k], qr, qg, qb);
+        s[k].x += qr; s[k].y += qg; s[k].z += qb; s[k].w += 1u;
+        rgb[k] = min((qr + 128u) >> 8, 255u) | (min((qg + 128u) >> 8, 255u) << 8) | (min((qb + 128u) >> 8, 255u) << 16);  // TOP5 lists
+      }
       a.acc[idx[k]] = s[k];
       if (a.accum_mode != 0) {
         const Record* rp = a.records + (base + k * blockDim.x + threadIdx.x);
@@ -928,21 +964,23 @@ void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t iof
 // ---------------------------------------------------------------------------------------------------------------------
 // Finalize.
 // ---------------------------------------------------------------------------------------------------------------------
+// `fixed88`: the sums hold 8.8 fixed-point samples (PCP_SAMPLE_BILINEAR): the integer mean is rounded to 8 bits.
 __global__ void finalize_sum_kernel(const uint4* __restrict__ acc, const uint32_t* __restrict__ perm, uint32_t n, uint8_t* __restrict__ rgb,
-                                    uint32_t* __restrict__ count) {
+                                    uint32_t* __restrict__ count, int fixed88) {
   for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
     const uint4 s = acc[j];
     const uint32_t i = perm ? perm[j] : j;  // outputs in the caller's point order
     uint32_t r = 0, g = 0, b = 0;
     if (s.w) { r = s.x / s.w; g = s.y / s.w; b = s.z / s.w; }
+    if (fixed88) { r = min((r + 128u) >> 8, 255u); g = min((g + 128u) >> 8, 255u); b = min((b + 128u) >> 8, 255u); }
     if (rgb) { rgb[3 * (size_t)i] = (uint8_t)r; rgb[3 * (size_t)i + 1] = (uint8_t)g; rgb[3 * (size_t)i + 2] = (uint8_t)b; }
     if (count) count[i] = s.w;
   }
 }
-void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s) {
+void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s) {
   if (n == 0) return;
   const int grid = (n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16;
-  finalize_sum_kernel<<<grid, 256, 0, s>>>(acc, perm, n, rgb, count);
+  finalize_sum_kernel<<<grid, 256, 0, s>>>(acc, perm, n, rgb, count, fixed88);
 }
 
 // smoothColors (cpp:612-629): slots are already sorted by (score desc, frame asc); weighted mean in float, truncation.

@@ -8,14 +8,15 @@ from conftest import make_scene
 pytestmark = pytest.mark.gpu
 
 
-def _run_pair(oracle, sc, accum="sum", cull_size=None, T_opt=None, ds=14, tol=0.05, masks=False):
+def _run_pair(oracle, sc, accum="sum", cull_size=None, T_opt=None, ds=14, tol=0.05, masks=False, bilinear=False, flight=0):
     from pointcloudprocessor_b200 import api
     cam_o = oracle.camera(sc["intr"], sc["dist"])
     cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
     W, H = sc["W"], sc["H"]
     p = api.default_params(image_size=(W, H), cull_size=cull_size, downsample=ds, depth_tolerance=tol,
-                           accum_mode=api.ACCUM_TOP5 if accum == "top5" else api.ACCUM_SUM)
-    oc = oracle.Colorizer(cam_o, W, H, sc["cloud"], cull_size=cull_size, ds=ds, tol=tol, keep_obs=(accum == "top5"))
+                           accum_mode=api.ACCUM_TOP5 if accum == "top5" else api.ACCUM_SUM,
+                           sample_mode=api.SAMPLE_BILINEAR if bilinear else api.SAMPLE_NEAREST, frames_in_flight=flight)
+    oc = oracle.Colorizer(cam_o, W, H, sc["cloud"], cull_size=cull_size, ds=ds, tol=tol, keep_obs=(accum == "top5"), bilinear=bilinear)
     with api.Colorizer(cam_g, p) as gc:
         gc.set_cloud(sc["cloud"])
         for i, pose in enumerate(sc["poses"]):
@@ -45,6 +46,56 @@ def _run_pair(oracle, sc, accum="sum", cull_size=None, T_opt=None, ds=14, tol=0.
 
 def test_tiny_sum(oracle, built_lib):
     _run_pair(oracle, make_scene(20_000, 3, 320, 240))
+
+
+def test_tiny_bilinear_sum(oracle, built_lib):
+    """PCP_SAMPLE_BILINEAR (north_star (c)): 8.8 fixed-point sums and rounded means, bit-exact against the restated oracle."""
+    _run_pair(oracle, make_scene(20_000, 3, 320, 240), bilinear=True)
+
+
+def test_bilinear_top5(oracle, built_lib):
+    _run_pair(oracle, make_scene(30_000, 6, 320, 240), accum="top5", bilinear=True)
+
+
+def test_bilinear_close_to_nearest(oracle, built_lib):
+    """On the smooth synthetic images the bilinear colour stays within the local pixel range of the nearest one."""
+    from pointcloudprocessor_b200 import api
+    sc = make_scene(50_000, 4, 640, 480)
+    out = []
+    for mode in (api.SAMPLE_NEAREST, api.SAMPLE_BILINEAR):
+        with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(640, 480), sample_mode=mode)) as gc:
+            gc.set_cloud(sc["cloud"])
+            for i, pose in enumerate(sc["poses"]):
+                gc.submit_frame(pose, sc["images"][i])
+            out.append(gc.finalize())
+    (rgb_n, cnt_n), (rgb_b, cnt_b) = out
+    assert np.array_equal(cnt_n, cnt_b)  # same coloured set
+    assert cnt_n.sum() > 0
+    assert np.abs(rgb_n.astype(int) - rgb_b.astype(int)).mean() < 8.0
+
+
+@pytest.mark.parametrize("flight", [1, 2, 3])
+def test_frames_in_flight_invariant(oracle, built_lib, flight):
+    """Results do not depend on how many frames run concurrently on the internal streams."""
+    _run_pair(oracle, make_scene(200_000, 8, 640, 480), flight=flight)
+
+
+def test_async_pipeline_matches_oracle(oracle, built_lib):
+    """Frames submitted without per-frame outputs (fully asynchronous, 3 in flight) give the oracle's accumulators."""
+    from pointcloudprocessor_b200 import api
+    sc = make_scene(300_000, 12, 640, 480, masks=True)
+    oc = oracle.Colorizer(oracle.camera(sc["intr"], sc["dist"]), 640, 480, sc["cloud"])
+    with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(640, 480), frames_in_flight=3)) as gc:
+        gc.set_cloud(sc["cloud"])
+        for rep in range(2):  # the second round re-uses every frame slot and staging buffer
+            gc.reset_accumulators()
+            for i, pose in enumerate(sc["poses"]):
+                gc.submit_frame(pose, sc["images"][i], mask=sc["masks"][i])
+        for i, pose in enumerate(sc["poses"]):
+            oc.frame(pose, sc["images"][i], mask=sc["masks"][i], threads=4)
+        acc_g, mh_g, mm_g = gc.accumulators()
+        acc_o, mh_o, mm_o = oc.accumulators()
+        assert np.array_equal(acc_g, acc_o) and np.array_equal(mh_g, mh_o) and np.array_equal(mm_g, mm_o)
 
 
 def test_tiny_masks(oracle, built_lib):

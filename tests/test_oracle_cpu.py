@@ -307,3 +307,43 @@ def test_scores_range_and_formula(oracle):
     cz = v[:, 2] / np.linalg.norm(v, axis=1)
     assert np.abs(s[:, 0] - (0.2 + 0.8 * (cz + 1) / 2)).max() < 1e-5
     assert np.abs(s[:, 2] - (s[:, 0] + s[:, 1]) / 2).max() < 1e-6
+
+
+def test_bilinear_mode_against_numpy(oracle):
+    """The oracle's bilinear extension (bilinear_q) against a vectorised numpy evaluation of the same definition, and its
+    distance from the nearest-pixel colour on the coloured set (same set in both modes)."""
+    from pointcloudprocessor_b200 import synth
+    W, H, n = 320, 240, 20_000
+    intr, dist = synth.make_camera(W, H)
+    cam = oracle.camera(intr, dist)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(2)
+    img = synth.make_image(0, W, H)
+    on = oracle.Colorizer(cam, W, H, cloud)
+    ob = oracle.Colorizer(cam, W, H, cloud, bilinear=True)
+    rn = on.frame(poses[0], img, want_vis=True, want_pix=True)
+    rb = ob.frame(poses[0], img, want_vis=True, want_pix=True)
+    assert np.array_equal(rn["pix"], rb["pix"]) and np.array_equal(rn["vis"], rb["vis"])
+    sel = np.nonzero(rb["pix"] >= 0)[0]
+    assert sel.size > 100
+    w2c, _ = oracle.pose_matrices(poses[0])
+    pc = oracle.transform(cloud[sel, :3].copy(), w2c)
+    uv = oracle.project(cam, pc.astype(np.float64))
+    x0 = uv[:, 0].astype(np.int64); y0 = uv[:, 1].astype(np.int64)
+    assert np.array_equal(y0 * W + x0, rb["pix"][sel])
+    x1 = np.minimum(x0 + 1, W - 1); y1 = np.minimum(y0 + 1, H - 1)
+    fx = np.maximum(uv[:, 0] - x0, 0.0); fy = np.maximum(uv[:, 1] - y0, 0.0)
+    gx = 1.0 - fx; gy = 1.0 - fy
+    acc = ob.accumulators()[0]
+    for k, ch in enumerate((2, 1, 0)):  # sums are r, g, b; the image is b, g, r
+        p = img[:, :, ch].astype(np.float64)
+        top = p[y0, x0] * gx + p[y0, x1] * fx
+        bot = p[y1, x0] * gx + p[y1, x1] * fx
+        q = (((top * gy) + (bot * fy)) * 256.0 + 0.5).astype(np.uint32)
+        assert np.array_equal(q, acc[sel, k])
+    assert np.all(acc[sel, 3] == 1)
+    rgb_b, rgb_n = ob.finalize_sum(), on.finalize_sum()
+    lo = np.minimum.reduce([img[y0, x0], img[y0, x1], img[y1, x0], img[y1, x1]])[:, ::-1].astype(int)
+    hi = np.maximum.reduce([img[y0, x0], img[y0, x1], img[y1, x0], img[y1, x1]])[:, ::-1].astype(int)
+    assert np.all(rgb_b[sel].astype(int) >= lo) and np.all(rgb_b[sel].astype(int) <= hi)  # an interpolation stays in the local range
+    assert np.array_equal(rgb_n[sel], img[y0, x0][:, ::-1])
