@@ -54,7 +54,13 @@ typedef struct {
   int frames_in_flight;            /* 1..3 (0 = default 3): frames run on that many internal streams, each with its own z-grid / record
                                     * scratch, so that the scan of frame f+1 overlaps the tail of frame f and its resolve pass.
                                     * Accumulator updates stay in frame order; results do not depend on this value. */
-  int reserved[6];
+  int hsv_adjust;                  /* 1: pcp_submit_frame applies generateColorMap's 8-bit BGR->HSV->BGR round trip (cpp:722-741) to the
+                                    * uploaded image on the device before sampling; 0 (default): the caller passes the adjusted image */
+  float saturation_scale;          /* 1.0 (cpp:726) */
+  float brightness_scale;          /* 1.0 (cpp:727) */
+  int hsv_vector_block;            /* pixels per vector iteration of the OpenCV build to reproduce (its scalar row tail rounds
+                                    * differently from its vector body): 32 = cv2 4.13 AVX2 build; 0 = whole row is vector body */
+  int reserved[2];
 } pcp_params;
 
 /* Optional per-frame outputs (host buffers, caller-owned; any pointer may be NULL). */
@@ -119,6 +125,12 @@ int pcp_cull(pcp_ctx* ctx, const float* w2c16, const double* T16, int32_t* idx_o
 int pcp_cull_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, int32_t* idx_out, size_t* m_out);
 /* Host helper: the float matrices the reference derives from a pose (cpp:495-519). */
 int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[16], float c2w16[16]);
+
+/* cv::cvtColor(BGR2HSV) -> S *= saturation_scale, V *= brightness_scale (saturate_cast) -> cv::cvtColor(HSV2BGR), 8-bit, of
+ * generateColorMap (src/PointCloudProcessor.cpp:722-741) on the device; host buffers in and out (may alias).  Uses the
+ * context's hsv_vector_block. */
+int pcp_hsv_roundtrip(pcp_ctx* ctx, const uint8_t* bgr_in, size_t pitch_in, uint8_t* bgr_out, size_t pitch_out, int width, int height,
+                      float saturation_scale, float brightness_scale);
 
 /* Raw accumulators: acc4 = N x {sum_r, sum_g, sum_b, count} u32; mask_hits/mask_max = N u32 (may be NULL). */
 int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint32_t* mask_max);

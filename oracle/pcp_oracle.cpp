@@ -31,6 +31,8 @@
 //  D8 std::sort (unstable) on finalScore in smoothColors: ties broken by ascending keyframe index.
 //  D9 static_cast<uint8_t>(NaN) for points never observed: defined as 0 (what x86 produces in practice).
 //  D10 Sophus SE3d * point: p + w*uv + qv x uv with uv = 2*(qv x p), then + translation.
+//  D12 cv::cvtColor BGR<->HSV 8-bit: restated from OpenCV 4.x and pinned against cv2 4.13.0 over all 2^24 inputs; the
+//      backward conversion differs between OpenCV's vector body and its scalar row tail (see hsv_roundtrip).
 //  D11 kd-tree re-indexing (PointCloudProcessor.cpp:557-593) is replaced by carrying the point index
 //      ("reindex=carry"); scores are computed from the camera-frame float point directly.
 
@@ -474,6 +476,81 @@ bool nid_eval(const Camera& cam, const double* image, int W, int H, const float*
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------------
+// generateColorMap's image preparation: BGR -> HSV -> (S * saturation_scale, V * brightness_scale, saturate_cast) -> BGR,
+// all 8-bit (src/PointCloudProcessor.cpp:722-741).  cv::cvtColor is third-party (OpenCV, unpinned by the reference's
+// CMakeLists.txt:19); restated from OpenCV 4.x imgproc color_hsv and PINNED against cv2 4.13.0 in this container over all
+// 2^24 inputs of each direction (tests/test_oracle_cpu.py).  [D12]
+//   forward  (RGB2HSV_b, hrange 180): integer, hsv_shift = 12, sdiv_table[i] = cvRound((255 << 12) / i),
+//            hdiv_table180[i] = cvRound((180 << 12) / (6 i)).
+//   backward (HSV2RGB_b): float.  OpenCV's vector body and its scalar row tail are DIFFERENT functions of the pixel:
+//            body  (x < floor(W / block) * block; block = 32 pixels in the cv2 4.13 AVX2 build measured here):
+//                  h = H * (6/180); sector = trunc(h) mod 6; f = h - trunc(h); tab = {v, v(1-s), v*fma(-s,f,1), v*fma(-s,1-f,1)};
+//                  channel = trunc(tab * 255)            (no s == 0 shortcut, no fmod)
+//            tail: h = fmod(H * (6/180), 6); sector = floor(h); s == 0 -> grey; same tab; channel = cvRound(tab * 255).
+// ---------------------------------------------------------------------------------------------------
+inline uint8_t sat_u8_round(float x) { long v = lrintf(x); return (uint8_t)(v < 0 ? 0 : v > 255 ? 255 : v); }  // cvRound + saturate
+inline uint8_t sat_u8_trunc(float x) { int v = (int)x; return (uint8_t)(v < 0 ? 0 : v > 255 ? 255 : v); }
+
+void hsv_roundtrip(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int W, int H, float sat_scale, float val_scale, int block) {
+  static int sdiv[256], hdiv[256];
+  static bool init = false;
+  if (!init) {
+    sdiv[0] = hdiv[0] = 0;
+    for (int i = 1; i < 256; i++) {
+      sdiv[i] = (int)lrint((255 << 12) / (1. * i));
+      hdiv[i] = (int)lrint((180 << 12) / (6. * i));
+    }
+    init = true;
+  }
+  static const int sector_data[6][3] = {{1, 3, 0}, {1, 0, 2}, {3, 0, 1}, {0, 2, 1}, {0, 1, 3}, {2, 1, 0}};
+  const int body = block > 0 ? (W / block) * block : W;
+  for (int y = 0; y < H; y++) {
+    const uint8_t* sp = src + (size_t)y * spitch;
+    uint8_t* dp = dst + (size_t)y * dpitch;
+    for (int x = 0; x < W; x++) {
+      const int b = sp[3 * x], g = sp[3 * x + 1], r = sp[3 * x + 2];
+      int v = b, vmin = b;
+      if (g > v) v = g;
+      if (r > v) v = r;
+      if (g < vmin) vmin = g;
+      if (r < vmin) vmin = r;
+      const int diff = v - vmin;
+      int sI = (diff * sdiv[v] + (1 << 11)) >> 12;
+      int hI = v == r ? (g - b) : (v == g ? (b - r + 2 * diff) : (r - g + 4 * diff));
+      hI = (hI * hdiv[diff] + (1 << 11)) >> 12;
+      if (hI < 0) hI += 180;
+      const uint8_t h8 = (uint8_t)(hI < 0 ? 0 : hI > 255 ? 255 : hI);
+      const uint8_t s8 = sat_u8_round((float)(uint8_t)sI * sat_scale);   // cpp:733
+      const uint8_t v8 = sat_u8_round((float)(uint8_t)v * val_scale);    // cpp:734
+      const float hs = 6.0f / 180.0f;
+      const float sf = s8 * (1.0f / 255.0f), vf = v8 * (1.0f / 255.0f);
+      float h = h8 * hs, f, tab[4];
+      int sector;
+      const bool in_body = x < body;
+      if (in_body) {
+        const float pre = truncf(h);
+        f = h - pre;
+        sector = (int)pre % 6;
+      } else {
+        h = fmodf(h, 6.0f);
+        sector = (int)floorf(h);
+        f = h - (float)sector;
+        if ((unsigned)sector >= 6u) { sector = 0; f = 0.0f; }
+      }
+      tab[0] = vf;
+      tab[1] = vf * (1.0f - sf);
+      tab[2] = vf * fmaf(-sf, f, 1.0f);
+      tab[3] = vf * fmaf(-sf, 1.0f - f, 1.0f);
+      for (int k = 0; k < 3; k++) {
+        float c = tab[sector_data[sector][k]];
+        if (!in_body && sf == 0.0f) c = vf;
+        dp[3 * x + k] = in_body ? sat_u8_trunc(c * 255.0f) : sat_u8_round(c * 255.0f);
+      }
+    }
+  }
+}
+
 // ===================================================================================================
 // C interface for ctypes (tests / bench cpu_baseline only)
 // ===================================================================================================
@@ -536,6 +613,9 @@ void* orc_colorizer_create(const orc_camera* c, int W, int H, int cullW, int cul
   S->keep_obs = keep_obs != 0;
   if (S->keep_obs) S->obs.resize(n);
   return S;
+}
+void orc_hsv_roundtrip(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int W, int H, float sat_scale, float val_scale, int block) {
+  hsv_roundtrip(src, spitch, dst, dpitch, W, H, sat_scale, val_scale, block);
 }
 void orc_colorizer_destroy(void* h) { delete (Colorizer*)h; }
 void orc_colorizer_set_sample_mode(void* h, int mode) { ((Colorizer*)h)->sample_mode = mode; }

@@ -169,6 +169,16 @@ class Colorizer:
         return rgb
 
 
+def hsv_roundtrip(bgr, sat_scale=1.0, val_scale=1.0, block=32):
+    """generateColorMap's 8-bit BGR->HSV->BGR image preparation (src/PointCloudProcessor.cpp:722-741)."""
+    bgr = np.ascontiguousarray(bgr, np.uint8)
+    H, W, _ = bgr.shape
+    out = np.empty_like(bgr)
+    lib().orc_hsv_roundtrip(_p(bgr), C.c_size_t(bgr.strides[0]), _p(out), C.c_size_t(out.strides[0]), W, H, C.c_float(sat_scale),
+                            C.c_float(val_scale), int(block))
+    return out
+
+
 def nid(cam, image_f64, xyzi, se3, bins=16, want_hist=False):
     image_f64 = np.ascontiguousarray(image_f64, np.float64)
     H, W = image_f64.shape

@@ -24,7 +24,8 @@ class Params(C.Structure):
     _fields_ = [
         ("image_width", C.c_int), ("image_height", C.c_int), ("cull_width", C.c_int), ("cull_height", C.c_int),
         ("downsample", C.c_int), ("depth_tolerance", C.c_double), ("enable_depth_buffer_culling", C.c_int),
-        ("accum_mode", C.c_int), ("sample_mode", C.c_int), ("top_m", C.c_int), ("prebin", C.c_int), ("frames_in_flight", C.c_int), ("reserved", C.c_int * 6),
+        ("accum_mode", C.c_int), ("sample_mode", C.c_int), ("top_m", C.c_int), ("prebin", C.c_int), ("frames_in_flight", C.c_int), ("hsv_adjust", C.c_int), ("saturation_scale", C.c_float),
+        ("brightness_scale", C.c_float), ("hsv_vector_block", C.c_int), ("reserved", C.c_int * 2),
     ]
 
 
@@ -42,7 +43,7 @@ SYMBOLS = [
     "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_device", "pcp_num_points",
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
-    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count", "pcp_debug_counters",
+    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip",
 ]
 
 _lib = None
@@ -97,6 +98,7 @@ def load():
     L.pcp_nid_eval.argtypes = [vp, vp, i32, vp, vp]
     L.pcp_nid_eval_multi.argtypes = [C.POINTER(vp), i32, vp, vp, i32, vp, vp]
     L.pcp_debug_counters.argtypes = [vp, vp]
+    L.pcp_hsv_roundtrip.argtypes = [vp, vp, sz, vp, sz, i32, i32, C.c_float, C.c_float]
     L.pcp_launch_count.argtypes = [vp]
     L.pcp_launch_count.restype = C.c_uint64
     _lib = L

@@ -101,6 +101,15 @@ class Colorizer:
     def launch_count(self) -> int:
         return int(self._L.pcp_launch_count(self._h))
 
+    def hsv_roundtrip(self, bgr: np.ndarray, saturation_scale: float = 1.0, brightness_scale: float = 1.0) -> np.ndarray:
+        """generateColorMap's 8-bit BGR->HSV->BGR image preparation (src/PointCloudProcessor.cpp:722-741) on the device."""
+        if bgr.dtype != np.uint8 or bgr.ndim != 3 or bgr.shape[2] != 3 or bgr.strides[2] != 1 or bgr.strides[1] != 3:
+            raise PcpError("hsv_roundtrip: bgr must be HxWx3 uint8 with packed pixels")
+        out = np.empty((bgr.shape[0], bgr.shape[1], 3), np.uint8)
+        self._check(self._L.pcp_hsv_roundtrip(self._h, _ptr(bgr), bgr.strides[0], _ptr(out), out.strides[0], bgr.shape[1], bgr.shape[0],
+                                              C.c_float(saturation_scale), C.c_float(brightness_scale)), "pcp_hsv_roundtrip")
+        return out
+
     def debug_counters(self) -> dict:
         """Device counters of the last submitted frame (see pcp_debug_counters)."""
         out = np.zeros(16, np.uint32)

@@ -48,6 +48,10 @@ void pcp_default_params(pcp_params* p) {
   p->sample_mode = PCP_SAMPLE_NEAREST;
   p->top_m = 5;
   p->frames_in_flight = 3;
+  p->hsv_adjust = 0;
+  p->saturation_scale = 1.0f;  // cpp:726-727
+  p->brightness_scale = 1.0f;
+  p->hsv_vector_block = 32;
   p->prebin = 1;  // Morton-sorted chunks with AABBs; PCP_NO_PREBIN=1 or prebin = 0 keeps the caller's order on the device
 }
 
@@ -62,7 +66,7 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
       params->downsample <= 0 || params->top_m < 1 || params->top_m > 16 ||
       (params->accum_mode != PCP_ACCUM_SUM && params->accum_mode != PCP_ACCUM_TOP5) ||
       (params->sample_mode != PCP_SAMPLE_NEAREST && params->sample_mode != PCP_SAMPLE_BILINEAR) || params->frames_in_flight < 0 ||
-      params->frames_in_flight > pcp_ctx::kMaxFlight) {
+      params->frames_in_flight > pcp_ctx::kMaxFlight || params->hsv_vector_block < 0) {
     g_create_error = "pcp_create: invalid params";
     return PCP_EINVAL;
   }

@@ -235,9 +235,37 @@ int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16,
   CU(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_free[s], 0));
   CU(cudaMemcpy2DAsync(ctx->d_img[s], W * 3, bgr, pitch, W * 3, H, cudaMemcpyHostToDevice, ctx->copy_stream));
   if (mask) CU(cudaMemcpy2DAsync(ctx->d_mask[s], W, mask, mask_pitch, W, H, cudaMemcpyHostToDevice, ctx->copy_stream));
+  if (ctx->prm.hsv_adjust) {  // cpp:722-741, in place, on the copy stream (overlaps the scan of this frame)
+    launch_hsv_roundtrip(ctx->d_img[s], W * 3, ctx->d_img[s], W * 3, (int)W, (int)H, ctx->prm.saturation_scale, ctx->prm.brightness_scale,
+                         ctx->prm.hsv_vector_block, ctx->sm_count, ctx->copy_stream);
+    ctx->launches++;
+  }
   CU(cudaEventRecord(ctx->ev_copied[s], ctx->copy_stream));
   // only the resolve kernel reads the image: the scan of this frame does not wait for the upload
   return submit_device(ctx, pose7, T_opt16, ctx->d_img[s], W * 3, mask ? ctx->d_mask[s] : nullptr, W, out, ctx->ev_copied[s], ctx->ev_free[s]);
+}
+
+int pcp_hsv_roundtrip(pcp_ctx* ctx, const uint8_t* bgr_in, size_t pitch_in, uint8_t* bgr_out, size_t pitch_out, int width, int height,
+                      float saturation_scale, float brightness_scale) {
+  if (!ctx) return PCP_EINVAL;
+  if (!bgr_in || !bgr_out || width <= 0 || height <= 0 || pitch_in < (size_t)width * 3 || pitch_out < (size_t)width * 3) {
+    ctx->fail("pcp_hsv_roundtrip: bad image/pitch");
+    return PCP_EINVAL;
+  }
+  CU(cudaSetDevice(ctx->device));
+  uint8_t* d = nullptr;
+  const size_t row = (size_t)width * 3;
+  CU(cudaMalloc(&d, row * height));
+  cudaError_t e = cudaMemcpy2DAsync(d, row, bgr_in, pitch_in, row, height, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) {
+    launch_hsv_roundtrip(d, row, d, row, width, height, saturation_scale, brightness_scale, ctx->prm.hsv_vector_block, ctx->sm_count, ctx->stream);
+    ctx->launches++;
+    e = cudaMemcpy2DAsync(bgr_out, pitch_out, d, row, row, height, cudaMemcpyDeviceToHost, ctx->stream);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) { ctx->fail("pcp_hsv_roundtrip: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+  return PCP_OK;
 }
 
 static int cull_common(pcp_ctx* ctx, const FrameParams& fp, int32_t* idx_out, size_t* m_out) {

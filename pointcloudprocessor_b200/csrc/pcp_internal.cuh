@@ -107,6 +107,9 @@ void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t iof
 void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
+// generateColorMap's 8-bit HSV round trip (pcp_image.cu); src and dst may alias
+void launch_hsv_roundtrip(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int W, int H, float sat_scale, float val_scale, int block,
+                          int sm_count, cudaStream_t s);
 // pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)
 cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, void** scratch, size_t* scratch_bytes, int sm_count,
                          cudaStream_t s);

@@ -264,3 +264,42 @@ def test_nid(oracle, built_lib):
         assert abs(s[0] - 2 * r2) <= 2e-5 * abs(r2)
         assert oracle.nid_gate(cands[0], cands[2]) and not oracle.nid_gate(cands[0], far)
         cost.close()
+
+
+@pytest.mark.parametrize("width", [4096, 4099, 33])
+def test_hsv_roundtrip_device(oracle, built_lib, width):
+    """hsv_roundtrip_kernel against the oracle on every 24-bit colour (and against cv2 when it is importable on the box)."""
+    from pointcloudprocessor_b200 import api, synth
+    v = np.arange(1 << 24, dtype=np.uint32)
+    bgr = np.stack([(v & 255), (v >> 8) & 255, (v >> 16) & 255], axis=1).astype(np.uint8)
+    rows = (1 << 24) // width
+    img = np.ascontiguousarray(bgr[: rows * width].reshape(rows, width, 3))
+    intr, dist = synth.make_camera(64, 64)
+    with api.Colorizer(api.create_camera("pinhole", intr, dist), api.default_params(image_size=(64, 64))) as gc:
+        for sat, val in ((1.0, 1.0), (1.2, 0.9)):
+            out = gc.hsv_roundtrip(img, sat, val)
+            assert np.array_equal(out, oracle.hsv_roundtrip(img, sat, val))
+            try:
+                import cv2
+            except ImportError:
+                continue
+            hsv = cv2.cvtColor(img, cv2.COLOR_BGR2HSV)
+            hsv[..., 1] = np.clip(np.rint(hsv[..., 1].astype(np.float32) * np.float32(sat)), 0, 255).astype(np.uint8)
+            hsv[..., 2] = np.clip(np.rint(hsv[..., 2].astype(np.float32) * np.float32(val)), 0, 255).astype(np.uint8)
+            assert np.array_equal(out, cv2.cvtColor(hsv, cv2.COLOR_HSV2BGR))
+
+
+def test_hsv_adjust_in_pipeline(oracle, built_lib):
+    """hsv_adjust = 1: raw images go in, the device applies the round trip; equals the oracle fed with adjusted images."""
+    from pointcloudprocessor_b200 import api
+    sc = make_scene(50_000, 4, 330, 240)  # 330 = 10 * 32 + 10: vector body and scalar tail
+    rng = np.random.default_rng(5)
+    raw = [rng.integers(0, 256, (240, 330, 3), dtype=np.uint8) for _ in sc["poses"]]
+    oc = oracle.Colorizer(oracle.camera(sc["intr"], sc["dist"]), 330, 240, sc["cloud"])
+    with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(330, 240), hsv_adjust=1)) as gc:
+        gc.set_cloud(sc["cloud"])
+        for i, pose in enumerate(sc["poses"]):
+            gc.submit_frame(pose, raw[i])
+            oc.frame(pose, oracle.hsv_roundtrip(raw[i]))
+        assert np.array_equal(gc.accumulators()[0], oc.accumulators()[0])
+        assert oc.accumulators()[0][:, 3].sum() > 0

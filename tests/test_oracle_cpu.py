@@ -347,3 +347,36 @@ def test_bilinear_mode_against_numpy(oracle):
     hi = np.maximum.reduce([img[y0, x0], img[y0, x1], img[y1, x0], img[y1, x1]])[:, ::-1].astype(int)
     assert np.all(rgb_b[sel].astype(int) >= lo) and np.all(rgb_b[sel].astype(int) <= hi)  # an interpolation stays in the local range
     assert np.array_equal(rgb_n[sel], img[y0, x0][:, ::-1])
+
+
+def _all_colours(width):
+    v = np.arange(1 << 24, dtype=np.uint32)
+    bgr = np.stack([(v & 255), (v >> 8) & 255, (v >> 16) & 255], axis=1).astype(np.uint8)
+    rows = (1 << 24) // width
+    return bgr[: rows * width].reshape(rows, width, 3)
+
+
+def _cv2_roundtrip(img, sat=1.0, val=1.0):
+    import cv2
+    hsv = cv2.cvtColor(img, cv2.COLOR_BGR2HSV)
+    # hsv.at<Vec3b>[1] = saturate_cast<uchar>(hsv[1] * saturation_scale)   (src/PointCloudProcessor.cpp:733-734)
+    hsv[..., 1] = np.clip(np.rint(hsv[..., 1].astype(np.float32) * np.float32(sat)), 0, 255).astype(np.uint8)
+    hsv[..., 2] = np.clip(np.rint(hsv[..., 2].astype(np.float32) * np.float32(val)), 0, 255).astype(np.uint8)
+    return cv2.cvtColor(hsv, cv2.COLOR_HSV2BGR)
+
+
+@pytest.mark.parametrize("width", [4096, 4099, 1])
+def test_hsv_roundtrip_pinned_against_cv2(oracle, width):
+    """D12: the 8-bit BGR->HSV->BGR round trip of generateColorMap (cpp:722-741) equals OpenCV's (cv2 here) on every colour,
+    in the vector body of a row (width 4096), with a scalar tail (4099 = 128 * 32 + 3) and in tail-only rows (width 1)."""
+    pytest.importorskip("cv2")
+    img = _all_colours(width) if width > 1 else _all_colours(4096).reshape(-1, 1, 3)[:: 7]
+    img = np.ascontiguousarray(img)
+    assert np.array_equal(oracle.hsv_roundtrip(img), _cv2_roundtrip(img))
+
+
+def test_hsv_roundtrip_scales(oracle):
+    pytest.importorskip("cv2")
+    img = np.ascontiguousarray(_all_colours(4096)[::16])
+    for sat, val in ((1.2, 1.0), (1.0, 1.2), (0.7, 0.9)):
+        assert np.array_equal(oracle.hsv_roundtrip(img, sat, val), _cv2_roundtrip(img, sat, val)), (sat, val)
