@@ -174,6 +174,50 @@ int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_
 int pcp_nid_eval_multi(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
                        uint8_t* ok_out);
 
+/* PointCloudProcessor(pointCloudPath, odometryPath, imagesFolder, maskImageFolder, outputPath, enableMLS, enableNIDOptimize,
+ * enableInitialGuessManual) + process()  (include/PointCloudProcessor.hpp:17-27, src/PointCloudProcessor.cpp:1007-1032).
+ * Folders are used as prefixes exactly as the reference does (imagesFolder + std::to_string(ts) + ".jpg", cpp:981; outputPath +
+ * "filtered_pcd/", cpp:1038), so they normally end with '/'.  Files read: PCD (ascii / binary / binary_compressed), the
+ * odometry text "ts x y z qw qx qy qz", <ts>.jpg images (nvJPEG; <ts>.ppm / .png accepted as a lossless extension) and <ts>.png
+ * masks (<ts>.pgm accepted).  Files written (ASCII PCD, PCL 1.10 layout): scans-crop.pcd, filtered_pcd/<ts>_beforeNID.pcd,
+ * filtered_pcd/<ts>_rgb-mask.pcd, cloudInWorldWithRGB.pcd, cloudInWorldWithRGBandMask.pcd.
+ * The constants the reference hard-codes (cpp:51-62, :525) are the defaults of the optional fields. */
+typedef struct {
+  const char* point_cloud_path;
+  const char* odometry_path;
+  const char* images_folder;
+  const char* mask_image_folder;       /* NULL or "" disables the mask path (cpp:89) */
+  const char* output_path;
+  int enable_mls;                      /* must be 0: pcl::MovingLeastSquares is out of scope (-> PCP_EINVAL) */
+  int enable_nid_optimize;             /* must be 0: the Ceres optimiser is out of scope; pass T_camera_lidar_optimized instead */
+  int enable_initial_guess_manual;     /* must be 0: the GUI needs a graphics stack (unavailable on this box) */
+  int device;
+  const pcp_camera* camera;            /* NULL: the reference camera (cpp:57-60) */
+  int cull_width, cull_height;         /* 0: 4096 x 3000 (cpp:525) */
+  const double* T_camera_lidar_optimized; /* optional 4x4 column-major: the result NID / the manual guess would have produced (cpp:504-519) */
+  int skip_outputs;                    /* 1: compute everything but write no PCD (benchmarks) */
+  int sample_mode;                     /* PCP_SAMPLE_NEAREST (reference) | PCP_SAMPLE_BILINEAR */
+  int reserved[9];
+} pcp_process_args;
+
+typedef struct {
+  int64_t n_points, n_cropped, n_frames, n_keyframes, n_colored_points, n_mask_points;
+  int64_t n_visible_total;             /* sum over keyframes of the culled cloud sizes (loop #1) */
+  double seconds_load, seconds_cull_pass, seconds_color_pass, seconds_write, seconds_total;
+} pcp_process_stats;
+
+/* Returns a pcp_status; on failure `err` (if given) receives the message the reference would have thrown. */
+int pcp_process(const pcp_process_args* args, pcp_process_stats* stats, char* err, size_t err_len);
+
+/* File formats at the boundary (host side; replace pcl::io::loadPCDFile<PointXYZI>, pcl::io::savePCDFileASCII and cv::imread at
+ * src/PointCloudProcessor.cpp:112, :135, :716, :774).  Buffers returned through *_out are released with pcp_io_free.
+ * pcp_pcd_read_xyzi: n x {x,y,z,intensity} floats from an ascii / binary / binary_compressed PCD.
+ * pcp_image_read: 8-bit image, grayscale != 0 -> 1 channel, else 3 channels B,G,R; JPEG is decoded with nvJPEG (needs a GPU). */
+int pcp_pcd_read_xyzi(const char* path, float** xyzi_out, size_t* n_out);
+int pcp_pcd_write_xyzi(const char* path, const float* xyzi, size_t n);
+int pcp_image_read(const char* path, int grayscale, uint8_t** data_out, int* width, int* height, int* channels);
+void pcp_io_free(void* p);
+
 /* Debug/bench: the 16 u32 device counters of the last submitted frame: {records emitted by the scan, candidates, visible,
  * coloured, active chunks, then (library built with -DPCP_STATS only) chunks skipped whole, points kept by the chunk-level
  * depth test, points kept by the FP32 projection pre-filter}.  No reference counterpart. */

@@ -38,12 +38,29 @@ OUT_SKIP_CANDIDATES = 1
 
 
 # every symbol include/pcp/pcp.h declares
+class ProcessArgs(C.Structure):
+    _fields_ = [
+        ("point_cloud_path", C.c_char_p), ("odometry_path", C.c_char_p), ("images_folder", C.c_char_p), ("mask_image_folder", C.c_char_p),
+        ("output_path", C.c_char_p), ("enable_mls", C.c_int), ("enable_nid_optimize", C.c_int), ("enable_initial_guess_manual", C.c_int),
+        ("device", C.c_int), ("camera", C.POINTER(Camera)), ("cull_width", C.c_int), ("cull_height", C.c_int),
+        ("T_camera_lidar_optimized", C.POINTER(C.c_double)), ("skip_outputs", C.c_int), ("sample_mode", C.c_int), ("reserved", C.c_int * 9),
+    ]
+
+
+class ProcessStats(C.Structure):
+    _fields_ = [
+        ("n_points", C.c_int64), ("n_cropped", C.c_int64), ("n_frames", C.c_int64), ("n_keyframes", C.c_int64), ("n_colored_points", C.c_int64),
+        ("n_mask_points", C.c_int64), ("n_visible_total", C.c_int64), ("seconds_load", C.c_double), ("seconds_cull_pass", C.c_double),
+        ("seconds_color_pass", C.c_double), ("seconds_write", C.c_double), ("seconds_total", C.c_double),
+    ]
+
+
 SYMBOLS = [
     "pcp_default_params", "pcp_abi_version", "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_set_stream", "pcp_get_stream",
     "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_device", "pcp_num_points",
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
-    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip",
+    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
 ]
 
 _lib = None
@@ -98,6 +115,12 @@ def load():
     L.pcp_nid_eval.argtypes = [vp, vp, i32, vp, vp]
     L.pcp_nid_eval_multi.argtypes = [C.POINTER(vp), i32, vp, vp, i32, vp, vp]
     L.pcp_debug_counters.argtypes = [vp, vp]
+    L.pcp_pcd_read_xyzi.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(sz)]
+    L.pcp_pcd_write_xyzi.argtypes = [C.c_char_p, vp, sz]
+    L.pcp_image_read.argtypes = [C.c_char_p, i32, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    L.pcp_io_free.argtypes = [vp]
+    L.pcp_io_free.restype = None
+    L.pcp_process.argtypes = [C.POINTER(ProcessArgs), C.POINTER(ProcessStats), C.c_char_p, sz]
     L.pcp_hsv_roundtrip.argtypes = [vp, vp, sz, vp, sz, i32, i32, C.c_float, C.c_float]
     L.pcp_launch_count.argtypes = [vp]
     L.pcp_launch_count.restype = C.c_uint64

@@ -268,6 +268,80 @@ class Colorizer:
         self._check(self._L.pcp_allreduce(self._h), "pcp_allreduce")
 
 
+def load_pcd_xyzi(path) -> np.ndarray:
+    """pcl::io::loadPCDFile<pcl::PointXYZI> (src/PointCloudProcessor.cpp:112): (N,4) float32 {x,y,z,intensity}."""
+    L = _capi.load()
+    ptr = C.POINTER(C.c_float)()
+    n = C.c_size_t(0)
+    rc = L.pcp_pcd_read_xyzi(str(path).encode(), C.byref(ptr), C.byref(n))
+    if rc != 0:
+        raise PcpError("Couldn't read point cloud file.", rc)
+    try:
+        return np.ctypeslib.as_array(ptr, shape=(n.value, 4)).copy() if n.value else np.zeros((0, 4), np.float32)
+    finally:
+        L.pcp_io_free(ptr)
+
+
+def save_pcd_xyzi_ascii(path, xyzi: np.ndarray):
+    """pcl::io::savePCDFileASCII (src/PointCloudProcessor.cpp:135)."""
+    a = np.ascontiguousarray(xyzi, np.float32)
+    rc = _capi.load().pcp_pcd_write_xyzi(str(path).encode(), _ptr(a), a.shape[0])
+    if rc != 0:
+        raise PcpError(f"cannot write {path}", rc)
+
+
+def imread(path, grayscale=False) -> np.ndarray:
+    """cv::imread(path[, IMREAD_GRAYSCALE]): HxWx3 B,G,R or HxW uint8 (JPEG through nvJPEG, PNG / PGM / PPM on the host)."""
+    L = _capi.load()
+    ptr = C.POINTER(C.c_uint8)()
+    w, h, c = C.c_int(0), C.c_int(0), C.c_int(0)
+    rc = L.pcp_image_read(str(path).encode(), int(grayscale), C.byref(ptr), C.byref(w), C.byref(h), C.byref(c))
+    if rc != 0:
+        raise PcpError(f"Failed to read image from: {path}", rc)
+    try:
+        shape = (h.value, w.value) if c.value == 1 else (h.value, w.value, c.value)
+        return np.ctypeslib.as_array(ptr, shape=shape).copy()
+    finally:
+        L.pcp_io_free(ptr)
+
+
+class PointCloudProcessor:
+    """PointCloudProcessor(pointCloudPath, odometryPath, imagesFolder, maskImageFolder, outputPath, enableMLS, enableNIDOptimize,
+    enableInitialGuessManual).process()   (include/PointCloudProcessor.hpp:17-27, src/PointCloudProcessor.cpp:1007-1032)."""
+
+    def __init__(self, pointCloudPath, odometryPath, imagesFolder, maskImageFolder="", outputPath=".", enableMLS=False, enableNIDOptimize=False,
+                 enableInitialGuessManual=False, camera: Camera | None = None, cull_size=None, T_camera_lidar_optimized=None, device=0,
+                 skip_outputs=False, sample_mode=SAMPLE_NEAREST):
+        self._keep = [str(pointCloudPath).encode(), str(odometryPath).encode(), str(imagesFolder).encode(), str(maskImageFolder or "").encode(),
+                      str(outputPath).encode()]
+        a = _capi.ProcessArgs()
+        a.point_cloud_path, a.odometry_path, a.images_folder, a.mask_image_folder, a.output_path = self._keep
+        a.enable_mls, a.enable_nid_optimize, a.enable_initial_guess_manual = int(enableMLS), int(enableNIDOptimize), int(enableInitialGuessManual)
+        a.device = device
+        self._cam = camera
+        if camera is not None:
+            a.camera = C.pointer(camera)
+        if cull_size is not None:
+            a.cull_width, a.cull_height = int(cull_size[0]), int(cull_size[1])
+        self._T = None
+        if T_camera_lidar_optimized is not None:
+            self._T = np.ascontiguousarray(np.asarray(T_camera_lidar_optimized, np.float64).T.reshape(-1))
+            a.T_camera_lidar_optimized = self._T.ctypes.data_as(C.POINTER(C.c_double))
+        a.skip_outputs = int(skip_outputs)
+        a.sample_mode = int(sample_mode)
+        self._args = a
+        self.stats = None
+
+    def process(self) -> dict:
+        st = _capi.ProcessStats()
+        err = C.create_string_buffer(1024)
+        rc = _capi.load().pcp_process(C.byref(self._args), C.byref(st), err, len(err))
+        self.stats = {k: getattr(st, k) for k, _ in st._fields_}
+        if rc != 0:
+            raise PcpError(err.value.decode(errors="replace") or f"pcp_process failed ({rc})", rc)
+        return self.stats
+
+
 def pose_matrices(pose7, T_opt=None):
     """(w2c, c2w) float32 4x4 as derived at src/PointCloudProcessor.cpp:495-519 (host helper of the library)."""
     pose = np.ascontiguousarray(pose7, np.float64)

@@ -12,7 +12,7 @@ import sys
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libpcp_b200.so")
-SOURCES = ["pcp_kernels.cu", "pcp_capi.cu", "pcp_frames.cu", "pcp_nid.cu", "pcp_nccl.cu", "pcp_prebin.cu", "pcp_image.cu"]
+SOURCES = ["pcp_kernels.cu", "pcp_capi.cu", "pcp_frames.cu", "pcp_nid.cu", "pcp_nccl.cu", "pcp_prebin.cu", "pcp_image.cu", "pcp_jpeg.cu", "pcp_process.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
@@ -62,7 +62,7 @@ def build_library(force: bool = False, verbose: bool = False, defines=(), out: s
             rebuilt = True
         objs.append(obj)
     if rebuilt or not os.path.exists(lib_path):
-        cmd = [nvcc, "-shared", "-o", lib_path] + objs + ARCH + ["-ccbin", _host_cxx(), "-ldl", "-Xlinker", "--no-undefined"]
+        cmd = [nvcc, "-shared", "-o", lib_path] + objs + ARCH + ["-ccbin", _host_cxx(), "-ldl", "-lz", "-Xlinker", "--no-undefined"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
