@@ -194,4 +194,52 @@ class NIDCost {
 
 }  // namespace vlcal
 
+// PointCloudProcessor(pointCloudPath, odometryPath, imagesFolder, maskImageFolder, outputPath, enableMLS, enableNIDOptimize,
+// enableInitialGuessManual) + process() — include/PointCloudProcessor.hpp:17-27, src/PointCloudProcessor.cpp:24-90, :1007-1032.
+// Same argument order and the same exception type / messages (std::runtime_error) as the reference class.
+class PointCloudProcessor {
+ public:
+  PointCloudProcessor(const std::string& pointCloudPath, const std::string& odometryPath, const std::string& imagesFolder,
+                      const std::string& maskImageFolder, const std::string& outputPath, const bool& enableMLS, const bool& enableNIDOptimize,
+                      const bool& enableInitialGuessManual)
+      : pointCloudPath_(pointCloudPath), odometryPath_(odometryPath), imagesFolder_(imagesFolder), maskImageFolder_(maskImageFolder),
+        outputPath_(outputPath), enableMLS_(enableMLS), enableNIDOptimize_(enableNIDOptimize), enableInitialGuessManual_(enableInitialGuessManual) {}
+
+  // Optional overrides of what the reference hard-codes (cpp:51-62, :525); defaults reproduce it.
+  void setCamera(const pcp_camera& cam) { cam_ = cam; have_cam_ = true; }
+  void setCullSize(int width, int height) { cull_w_ = width; cull_h_ = height; }
+  void setOptimizedExtrinsic(const pcp::Isometry3d& T_camera_lidar_optimized) { T_ = T_camera_lidar_optimized; have_T_ = true; }
+  void setDevice(int device) { device_ = device; }
+
+  void process() {
+    pcp_process_args a{};
+    a.point_cloud_path = pointCloudPath_.c_str();
+    a.odometry_path = odometryPath_.c_str();
+    a.images_folder = imagesFolder_.c_str();
+    a.mask_image_folder = maskImageFolder_.c_str();
+    a.output_path = outputPath_.c_str();
+    a.enable_mls = enableMLS_;
+    a.enable_nid_optimize = enableNIDOptimize_;
+    a.enable_initial_guess_manual = enableInitialGuessManual_;
+    a.device = device_;
+    a.camera = have_cam_ ? &cam_ : nullptr;
+    a.cull_width = cull_w_;
+    a.cull_height = cull_h_;
+    a.T_camera_lidar_optimized = have_T_ ? T_.m : nullptr;
+    char err[1024];
+    const int rc = pcp_process(&a, &stats_, err, sizeof(err));
+    if (rc != PCP_OK) throw std::runtime_error(err[0] ? err : "pcp_process failed");
+  }
+  const pcp_process_stats& stats() const { return stats_; }
+
+ private:
+  std::string pointCloudPath_, odometryPath_, imagesFolder_, maskImageFolder_, outputPath_;
+  bool enableMLS_, enableNIDOptimize_, enableInitialGuessManual_;
+  pcp_camera cam_{};
+  bool have_cam_ = false, have_T_ = false;
+  int cull_w_ = 0, cull_h_ = 0, device_ = 0;
+  pcp::Isometry3d T_{};
+  pcp_process_stats stats_{};
+};
+
 #endif  // PCP_PCP_HPP_

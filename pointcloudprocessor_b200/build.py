@@ -67,7 +67,24 @@ def build_library(force: bool = False, verbose: bool = False, defines=(), out: s
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError("link failed")
+    if out is None:
+        build_cli(lib_path)
     return lib_path
+
+
+def build_cli(lib_path: str = LIB_PATH) -> str:
+    """pcp_colorize: the reference's executable (src/main.cpp) over the C++ facade."""
+    exe = os.path.join(_HERE, "pcp_colorize")
+    src = os.path.join(CSRC, "pcp_main.cpp")
+    deps = [src, os.path.join(_HERE, "..", "include", "pcp", "pcp.hpp"), os.path.join(_HERE, "..", "include", "pcp", "pcp.h"), lib_path]
+    if _newer(exe, deps):
+        cmd = [_host_cxx(), "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(_HERE, "..", "include"), src, "-o", exe, "-L" + _HERE, "-lpcp_b200",
+               "-Wl,-rpath,$ORIGIN"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("pcp_colorize: link failed")
+    return exe
 
 
 if __name__ == "__main__":

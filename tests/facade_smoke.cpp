@@ -9,6 +9,13 @@ int main() {
     camera::create_camera("fisheye", {1, 1, 0, 0}, {});
     return 10;
   } catch (const std::runtime_error&) {}
+  try {  // PointCloudProcessor: reference constructor signature; a missing PCD throws the reference's message
+    PointCloudProcessor proc("/nonexistent/scans.pcd", "/nonexistent/odom.txt", "/nonexistent/", "", "/tmp/", false, false, false);
+    proc.process();
+    return 12;
+  } catch (const std::runtime_error& e) {
+    if (std::string(e.what()).find("Couldn't read point cloud file") == std::string::npos) { std::printf("unexpected: %s\n", e.what()); return 13; }
+  }
   std::vector<pcp::PointXYZI> pts;
   for (int i = 0; i < 1000; i++) pts.push_back({0.001f * (i % 50) - 0.025f, 0.001f * (i / 50) - 0.01f, 1.0f + 0.01f * (i % 7), 1.0f, 0.5f, 0, 0, 0});
   try {

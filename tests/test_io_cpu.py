@@ -97,3 +97,16 @@ def test_png_pgm_ppm_against_cv2(api, tmp_path):
     rgba = np.dstack([bgr, rng.integers(0, 256, (37, 53), dtype=np.uint8)])
     assert cv2.imwrite(str(tmp_path / "a.png"), rgba)
     assert np.array_equal(api.imread(tmp_path / "a.png"), cv2.imread(str(tmp_path / "a.png")))
+
+
+def test_cli_exit_codes(built_lib, tmp_path):
+    """pcp_colorize keeps the exit codes of the reference's main (src/main.cpp:28-68): 1 help, -1 missing arguments, -2 exception."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(built_lib), "pcp_colorize")
+    assert os.path.exists(exe)
+    assert subprocess.run([exe, "--help"], capture_output=True).returncode == 1
+    r = subprocess.run([exe, "-p", "x.pcd"], capture_output=True, text=True)
+    assert r.returncode == 255 and "Missing required arguments" in r.stderr
+    r = subprocess.run([exe, "-p", str(tmp_path / "no.pcd"), "-o", str(tmp_path / "no.txt"), "-i", str(tmp_path) + "/"], capture_output=True, text=True)
+    assert r.returncode == 254 and "Couldn't read point cloud file." in r.stderr

@@ -181,3 +181,25 @@ def test_process_errors(built_lib, tmp_path):
         api.PointCloudProcessor(tmp_path / "missing.pcd", tmp_path / "odom.txt", str(tmp_path) + "/", "", str(tmp_path) + "/").process()
     with pytest.raises(api.PcpError, match="enableMLS"):
         api.PointCloudProcessor(tmp_path / "missing.pcd", tmp_path / "odom.txt", str(tmp_path) + "/", "", str(tmp_path) + "/", enableMLS=True).process()
+
+
+def test_cli_matches_library(built_lib, tmp_path):
+    """pcp_colorize (src/main.cpp's options) writes the same files as the library call."""
+    import subprocess
+    from pointcloudprocessor_b200 import api
+    W, H = 330, 240
+    sc, frames, img_dir, mask_dir, out_dir = _dataset(tmp_path, W=W, H=H, masks=True)
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    api.PointCloudProcessor(tmp_path / "scans.pcd", tmp_path / "odom.txt", str(img_dir) + "/", str(mask_dir) + "/", str(out_dir) + "/", camera=cam,
+                            cull_size=(W, H)).process()
+    out2 = tmp_path / "out2"
+    out2.mkdir()
+    exe = os.path.join(os.path.dirname(built_lib), "pcp_colorize")
+    r = subprocess.run([exe, "-p", str(tmp_path / "scans.pcd"), "-o", str(tmp_path / "odom.txt"), "-i", str(img_dir) + "/", "-m", str(mask_dir) + "/",
+                        "-t", str(out2) + "/", "--cull_size", f"{W}x{H}", "--intrinsics", ",".join(repr(float(x)) for x in sc["intr"]),
+                        "--distortion", ",".join(repr(float(x)) for x in sc["dist"])], capture_output=True, text=True)
+    assert r.returncode == 0 and "Processing completed successfully." in r.stdout, r.stdout + r.stderr
+    names = ["scans-crop.pcd", "cloudInWorldWithRGB.pcd", "cloudInWorldWithRGBandMask.pcd"] + ["filtered_pcd/" + p.name for p in (out_dir / "filtered_pcd").iterdir()]
+    assert len(names) > 8
+    for nme in names:
+        assert (out_dir / nme).read_bytes() == (out2 / nme).read_bytes(), nme
