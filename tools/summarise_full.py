@@ -54,7 +54,7 @@ def main(path, traffic_out=None):
         print(f"| {k} | {n} | " + " | ".join(f"{x:.2f}" if x < 1e5 else f"{x:.3e}" for x in m) + " |")
         out[k] = {"dram_bytes_per_launch": (m[1] + m[2]) * 1e6, "time_us": m[0]}
     if traffic_out:
-        scan = next((v for k, v in out.items() if k.startswith("scan_kernel")), None)
+        scan = next((v for k, v in out.items() if k.startswith("scan")), None)
         doc = {"source": path, "kernels": out}
         if scan:
             doc["scan_kernel_dram_bytes_per_launch"] = scan["dram_bytes_per_launch"]
