@@ -223,6 +223,14 @@ void pcp_io_free(void* p);
  * depth test, points kept by the FP32 projection pre-filter}.  No reference counterpart. */
 int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]);
 
+/* NIDCost::operator()<ceres::Jet<double, 7>> — the instantiation ceres::AutoDiffFirstOrderFunction<MultiNIDCost, 7> evaluates
+ * (visual_camera_calibration.cpp:204-233): value and the 7 partial derivatives over the ambient Sophus parameters
+ * {qx,qy,qz,qw,tx,ty,tz} (the manifold projection stays with the caller, as with ceres).  grad_out: B x 7. */
+int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, double* grad_out, uint8_t* ok_out);
+/* MultiNIDCost::operator()<Jet>: pose gate, then sums of values and gradients over the frames. */
+int pcp_nid_eval_multi_grad(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
+                            double* grad_sum_out, uint8_t* ok_out);
+
 /* Counters for benches: kernels launched by this context since creation. */
 uint64_t pcp_launch_count(const pcp_ctx* ctx);
 

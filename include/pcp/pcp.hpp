@@ -185,11 +185,44 @@ class NIDCost {
   void evaluate(const double* params_Bx7, int B, double* nid_out, uint8_t* ok_out) const {
     pcp::check(pcp_nid_eval(nid_, params_Bx7, B, nid_out, ok_out), ctx_, "pcp_nid_eval");
   }
+  // operator()<ceres::Jet<double, 7>>: value and the 7 partials over the ambient parameters (what AutoDiffFirstOrderFunction
+  // hands to the solver before the manifold projection), visual_camera_calibration.cpp:204-233.
+  bool operator()(const double* T_camera_lidar_params, double* residual, double* gradient7) const {
+    uint8_t ok = 0;
+    pcp::check(pcp_nid_eval_grad(nid_, T_camera_lidar_params, 1, residual, gradient7, &ok), ctx_, "pcp_nid_eval_grad");
+    return ok != 0;
+  }
   pcp_nid* handle() const { return nid_; }
 
  private:
   pcp_ctx* ctx_;
   pcp_nid* nid_ = nullptr;
+};
+
+// MultiNIDCost (src/vlcal/calib/visual_camera_calibration.cpp:86-129): pose gate (0.2 m / 2 deg from init) + sum over the frames.
+// Evaluate() has the signature of ceres::FirstOrderFunction, so the reference's GradientProblem can wrap it directly.
+class MultiNIDCost {
+ public:
+  explicit MultiNIDCost(const double init_T_camera_lidar_params[7]) { for (int i = 0; i < 7; i++) init_[i] = init_T_camera_lidar_params[i]; }
+  void add(const std::shared_ptr<NIDCost>& cost) { costs_.push_back(cost); handles_.push_back(cost->handle()); }
+  bool operator()(const double* params, double* residual) const {
+    uint8_t ok = 0;
+    if (pcp_nid_eval_multi(handles_.data(), (int)handles_.size(), init_, params, 1, residual, &ok) != PCP_OK) throw std::runtime_error("pcp_nid_eval_multi failed");
+    return ok != 0;
+  }
+  bool Evaluate(const double* parameters, double* cost, double* gradient) const {
+    if (!gradient) return (*this)(parameters, cost);
+    uint8_t ok = 0;
+    if (pcp_nid_eval_multi_grad(handles_.data(), (int)handles_.size(), init_, parameters, 1, cost, gradient, &ok) != PCP_OK)
+      throw std::runtime_error("pcp_nid_eval_multi_grad failed");
+    return ok != 0;
+  }
+  int NumParameters() const { return 7; }
+
+ private:
+  double init_[7];
+  std::vector<std::shared_ptr<NIDCost>> costs_;
+  std::vector<pcp_nid*> handles_;
 };
 
 }  // namespace vlcal

@@ -474,6 +474,102 @@ bool nid_eval(const Camera& cam, const double* image, int W, int H, const float*
   return std::isfinite(NID);                                                           // :107-111
 }
 
+// ---------------------------------------------------------------------------------------------------
+// NID value + gradient: NIDCost::operator()<ceres::Jet<double, 7>> (nid_cost.hpp:42-116) as instantiated by
+// ceres::AutoDiffFirstOrderFunction<MultiNIDCost, 7> (visual_camera_calibration.cpp:204-233): forward-mode dual numbers over
+// the 7 ambient Sophus parameters {qx,qy,qz,qw,tx,ty,tz}.  Jet7 restates ceres::Jet's arithmetic (ceres/jet.h: +, -, *, /, log;
+// third party, not vendored): f(a + v eps) = f(a) + f'(a) v eps.  floor()/knots/bins are taken on the real part (get_real, :61),
+// hist_points and H_points are plain doubles (:50, :102).  The statement order is that of nid_eval above.
+// ---------------------------------------------------------------------------------------------------
+struct Jet7 {
+  double a;
+  double v[7];
+  Jet7() : a(0.0) { for (double& x : v) x = 0.0; }
+  Jet7(double s) : a(s) { for (double& x : v) x = 0.0; }  // NOLINT: implicit like ceres::Jet(const T&)
+  static Jet7 var(double s, int k) { Jet7 j(s); j.v[k] = 1.0; return j; }
+};
+inline Jet7 operator+(const Jet7& f, const Jet7& g) { Jet7 h; h.a = f.a + g.a; for (int k = 0; k < 7; k++) h.v[k] = f.v[k] + g.v[k]; return h; }
+inline Jet7 operator-(const Jet7& f, const Jet7& g) { Jet7 h; h.a = f.a - g.a; for (int k = 0; k < 7; k++) h.v[k] = f.v[k] - g.v[k]; return h; }
+inline Jet7 operator-(const Jet7& f) { Jet7 h; h.a = -f.a; for (int k = 0; k < 7; k++) h.v[k] = -f.v[k]; return h; }
+inline Jet7 operator*(const Jet7& f, const Jet7& g) { Jet7 h; h.a = f.a * g.a; for (int k = 0; k < 7; k++) h.v[k] = f.a * g.v[k] + f.v[k] * g.a; return h; }
+inline Jet7 operator/(const Jet7& f, const Jet7& g) {  // ceres: g_a_inverse = 1 / g.a; f_a_by_g_a = f.a * g_a_inverse; (f.v - f_a_by_g_a * g.v) * g_a_inverse
+  Jet7 h; const double gi = 1.0 / g.a; const double fg = f.a * gi; h.a = fg; for (int k = 0; k < 7; k++) h.v[k] = (f.v[k] - fg * g.v[k]) * gi; return h;
+}
+inline Jet7 jlog(const Jet7& f) { Jet7 h; h.a = std::log(f.a); const double i = 1.0 / f.a; for (int k = 0; k < 7; k++) h.v[k] = f.v[k] * i; return h; }
+inline Jet7& operator+=(Jet7& f, const Jet7& g) { f = f + g; return f; }
+
+inline void project_jet(const Camera& cam, const Jet7& X, const Jet7& Y, const Jet7& Z, Jet7& u, Jet7& v) {  // pinhole.hpp:12-51 with T = Jet
+  const Jet7 x = X / Z, y = Y / Z;
+  const Jet7 x2 = x * x, y2 = y * y;
+  const Jet7 r2 = x2 + y2, r4 = r2 * r2, r6 = r2 * r4;
+  const Jet7 rc = ((Jet7(1.0) + Jet7(cam.D[0]) * r2) + Jet7(cam.D[1]) * r4) + Jet7(cam.D[4]) * r6;
+  const Jet7 t1 = (Jet7(2.0) * x) * y;
+  const Jet7 t2 = r2 + Jet7(2.0) * x2, t3 = r2 + Jet7(2.0) * y2;
+  const Jet7 xd = (rc * x + Jet7(cam.D[2]) * t1) + Jet7(cam.D[3]) * t2;
+  const Jet7 yd = (rc * y + Jet7(cam.D[2]) * t3) + Jet7(cam.D[3]) * t1;
+  u = Jet7(cam.fx) * xd + Jet7(cam.cx);
+  v = Jet7(cam.fy) * yd + Jet7(cam.cy);
+}
+
+bool nid_eval_grad(const Camera& cam, const double* image, int W, int H, const float* xyzi, size_t n, int bins, const double se3[7], double* nid_out,
+                   double* grad_out /*7*/) {
+  const Jet7 qx = Jet7::var(se3[0], 0), qy = Jet7::var(se3[1], 1), qz = Jet7::var(se3[2], 2), qw = Jet7::var(se3[3], 3), tx = Jet7::var(se3[4], 4),
+             ty = Jet7::var(se3[5], 5), tz = Jet7::var(se3[6], 6);
+  std::vector<Jet7> hist((size_t)bins * bins), hist_image(bins);
+  std::vector<double> hist_points(bins, 0.0);
+  static const double C[4][4] = {{1.0, -3.0, 3.0, -1.0}, {4.0, 0.0, -6.0, 3.0}, {1.0, 3.0, 3.0, -3.0}, {0.0, 0.0, 0.0, 1.0}};
+  double Cn[4][4];
+  for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) Cn[i][j] = C[i][j] / 6.0;
+  for (size_t i = 0; i < n; i++) {
+    const Jet7 px(xyzi[4 * i]), py(xyzi[4 * i + 1]), pz(xyzi[4 * i + 2]);
+    Jet7 uvx = qy * pz - qz * py, uvy = qz * px - qx * pz, uvz = qx * py - qy * px;  // [D10]
+    uvx += uvx; uvy += uvy; uvz += uvz;
+    const Jet7 X = (px + qw * uvx + (qy * uvz - qz * uvy)) + tx;
+    const Jet7 Y = (py + qw * uvy + (qz * uvx - qx * uvz)) + ty;
+    const Jet7 Z = (pz + qw * uvz + (qx * uvy - qy * uvx)) + tz;
+    const double ib = (double)xyzi[4 * i + 3] * bins;
+    int bin_p;
+    if (!(ib == ib)) bin_p = 0; else if (ib >= (double)(bins - 1)) bin_p = bins - 1; else if (ib <= 0.0) bin_p = 0; else bin_p = (int)ib;
+    Jet7 u, v;
+    project_jet(cam, X, Y, Z, u, v);
+    if (!std::isfinite(u.a) || !std::isfinite(v.a)) continue;
+    const double fu = std::floor(u.a), fv = std::floor(v.a);
+    if (fu < 0 || fv < 0 || fu >= (double)W || fv >= (double)H) continue;
+    const int kx = (int)fu, ky = (int)fv;
+    const Jet7 sx = u - Jet7((double)kx), sy = v - Jet7((double)ky);
+    hist_points[bin_p] += 1.0;
+    const Jet7 sex[4] = {Jet7(1.0), sx, sx * sx, (sx * sx) * sx}, sey[4] = {Jet7(1.0), sy, sy * sy, (sy * sy) * sy};
+    Jet7 bx[4], by[4];
+    for (int r = 0; r < 4; r++) {
+      bx[r] = ((Jet7(Cn[r][0]) * sex[0] + Jet7(Cn[r][1]) * sex[1]) + Jet7(Cn[r][2]) * sex[2]) + Jet7(Cn[r][3]) * sex[3];
+      by[r] = ((Jet7(Cn[r][0]) * sey[0] + Jet7(Cn[r][1]) * sey[1]) + Jet7(Cn[r][2]) * sey[2]) + Jet7(Cn[r][3]) * sey[3];
+    }
+    for (int a = 0; a < 4; a++) {
+      const int x = std::min(std::max(kx - 1 + a, 0), W - 1);
+      for (int b = 0; b < 4; b++) {
+        const int y = std::min(std::max(ky - 1 + b, 0), H - 1);
+        const Jet7 w = bx[a] * by[b];
+        const int bin_i = std::min<int>((int)(image[(size_t)y * W + x] * bins), bins - 1);
+        hist[(size_t)bin_i * bins + bin_p] += w;
+        hist_image[bin_i] += w;
+      }
+    }
+  }
+  double sum = 0.0;
+  for (int i = 0; i < bins; i++) sum += hist_points[i];
+  Jet7 Hi, Hj;
+  double Hp = 0.0;
+  for (int i = 0; i < bins; i++) { const Jet7 p = hist_image[i] / Jet7(sum); Hi += p * jlog(p + Jet7(1e-6)); }
+  for (int i = 0; i < bins; i++) { const double p = hist_points[i] / sum; Hp += p * std::log(p + 1e-6); }
+  for (int i = 0; i < bins * bins; i++) { const Jet7 p = hist[i] / Jet7(sum); Hj += p * jlog(p + Jet7(1e-6)); }
+  Hi = -Hi; Hp = -Hp; Hj = -Hj;
+  const Jet7 MI = (Hi + Jet7(Hp)) - Hj;
+  const Jet7 NID = (Hj - MI) / Hj;
+  *nid_out = NID.a;
+  for (int k = 0; k < 7; k++) grad_out[k] = NID.v[k];
+  return std::isfinite(NID.a);
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------
@@ -666,6 +762,11 @@ void orc_colorizer_finalize_top5(void* h, uint8_t* rgb /*n x 3*/, int top_m) {
 int orc_nid(const orc_camera* c, const double* image, int W, int H, const float* xyzi, size_t n, int bins, const double* se3,
             double* nid_out, double* hist_out, double* counts_out) {
   return nid_eval(to_cam(c), image, W, H, xyzi, n, bins, se3, nid_out, hist_out, counts_out) ? 1 : 0;
+}
+
+int orc_nid_grad(const orc_camera* c, const double* image, int W, int H, const float* xyzi, size_t n, int bins, const double* se3,
+                 double* nid_out, double* grad7_out) {
+  return nid_eval_grad(to_cam(c), image, W, H, xyzi, n, bins, se3, nid_out, grad7_out) ? 1 : 0;
 }
 
 // MultiNIDCost pose gate.  src/vlcal/calib/visual_camera_calibration.cpp:99-105.

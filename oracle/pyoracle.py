@@ -194,6 +194,20 @@ def nid(cam, image_f64, xyzi, se3, bins=16, want_hist=False):
     return out.value, bool(ok)
 
 
+def nid_grad(cam, image_f64, xyzi, se3, bins=16):
+    """NIDCost::operator()<ceres::Jet<double,7>>: -> (ok, nid, grad[7]) over the ambient Sophus parameters."""
+    img = np.ascontiguousarray(image_f64, np.float64)
+    H, W = img.shape
+    xyzi = np.ascontiguousarray(xyzi, np.float32)
+    se3 = np.ascontiguousarray(se3, np.float64)
+    out = np.zeros(1, np.float64)
+    g = np.zeros(7, np.float64)
+    L = lib()
+    L.orc_nid_grad.restype = C.c_int
+    ok = L.orc_nid_grad(C.byref(cam), _p(img), W, H, _p(xyzi), C.c_size_t(xyzi.shape[0]), int(bins), _p(se3), _p(out), _p(g))
+    return bool(ok), float(out[0]), g
+
+
 def nid_gate(init_se3, se3) -> bool:
     a = np.ascontiguousarray(init_se3, np.float64)
     b = np.ascontiguousarray(se3, np.float64)

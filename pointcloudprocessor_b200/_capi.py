@@ -60,7 +60,7 @@ SYMBOLS = [
     "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_device", "pcp_num_points",
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
-    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
+    "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
 ]
 
 _lib = None
@@ -122,6 +122,8 @@ def load():
     L.pcp_io_free.restype = None
     L.pcp_process.argtypes = [C.POINTER(ProcessArgs), C.POINTER(ProcessStats), C.c_char_p, sz]
     L.pcp_hsv_roundtrip.argtypes = [vp, vp, sz, vp, sz, i32, i32, C.c_float, C.c_float]
+    L.pcp_nid_eval_grad.argtypes = [vp, vp, i32, vp, vp, vp]
+    L.pcp_nid_eval_multi_grad.argtypes = [C.POINTER(vp), i32, vp, vp, i32, vp, vp, vp]
     L.pcp_launch_count.argtypes = [vp]
     L.pcp_launch_count.restype = C.c_uint64
     _lib = L

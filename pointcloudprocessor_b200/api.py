@@ -397,6 +397,16 @@ class NIDCost:
         self._ctx._check(self._L.pcp_nid_eval(self._h, _ptr(se3), B, _ptr(out), _ptr(ok)), "pcp_nid_eval")
         return out, ok.astype(bool)
 
+    def evaluate_with_gradient(self, se3_params):
+        """NIDCost::operator()<ceres::Jet<double,7>>: -> (nid (B,), grad (B,7) over {qx,qy,qz,qw,tx,ty,tz}, ok (B,))."""
+        se3 = np.ascontiguousarray(np.atleast_2d(se3_params), np.float64)
+        B = se3.shape[0]
+        out = np.empty(B, np.float64)
+        grad = np.empty((B, 7), np.float64)
+        ok = np.empty(B, np.uint8)
+        self._ctx._check(self._L.pcp_nid_eval_grad(self._h, _ptr(se3), B, _ptr(out), _ptr(grad), _ptr(ok)), "pcp_nid_eval_grad")
+        return out, grad, ok.astype(bool)
+
     def close(self):
         if self._h:
             self._L.pcp_nid_destroy(self._h)
@@ -407,6 +417,21 @@ class NIDCost:
             self.close()
         except Exception:
             pass
+
+
+def multi_nid_with_gradient(costs, init_se3, se3_params):
+    """MultiNIDCost::operator()<ceres::Jet<double,7>> (visual_camera_calibration.cpp:93-124, :204-233): -> (sum, grad, ok)."""
+    L = _capi.load()
+    se3 = np.ascontiguousarray(np.atleast_2d(se3_params), np.float64)
+    init = np.ascontiguousarray(init_se3, np.float64)
+    B = se3.shape[0]
+    arr = (C.c_void_p * len(costs))(*[c._h for c in costs])
+    out = np.empty(B, np.float64)
+    grad = np.empty((B, 7), np.float64)
+    ok = np.empty(B, np.uint8)
+    rc = L.pcp_nid_eval_multi_grad(arr, len(costs), _ptr(init), _ptr(se3), B, _ptr(out), _ptr(grad), _ptr(ok))
+    costs[0]._ctx._check(rc, "pcp_nid_eval_multi_grad")
+    return out, grad, ok.astype(bool)
 
 
 def multi_nid(costs, init_se3, se3_params):

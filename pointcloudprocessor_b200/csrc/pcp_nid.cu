@@ -21,6 +21,9 @@ struct pcp_nid {
   double* d_hist = nullptr;     // B x (bins*bins + bins): joint histogram then point-bin counts
   double* d_out = nullptr;      // B x 2: NID, ok flag
   int cap_B = 0;
+  double* d_hist_g = nullptr;   // gradient path: B x (8 * bins*bins + bins)
+  double* d_out_g = nullptr;    // B x 9: NID, ok flag, 7 partials
+  int cap_Bg = 0;
 };
 
 namespace {
@@ -166,6 +169,196 @@ __global__ void nid_entropy_kernel(const double* __restrict__ hist, int bins, in
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Value + gradient: NIDCost::operator()<ceres::Jet<double, 7>> (what ceres::AutoDiffFirstOrderFunction<MultiNIDCost, 7>
+// evaluates, visual_camera_calibration.cpp:204-233).  The dual parts are propagated analytically: per point the 3x7 Jacobian
+// of Sophus' SE3 * p over the ambient parameters {qx,qy,qz,qw,tx,ty,tz}, the 2x3 Jacobian of the plumb_bob projection, the
+// derivative of the cubic B-spline weights; floor / knots / bins carry no derivative (get_real, nid_cost.hpp:61).  Per bin
+// the kernel accumulates {w, dw/dtheta_0..6}: 8 planes of bins x bins doubles in shared memory per CTA.
+// Same mathematics as the Jets, different rounding order: tolerance 1e-5 relative (north_star) against the oracle's Jet7.
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bspline_d(double s, double b[4], double d[4]) {
+  const double s2 = s * s, s3 = s2 * s;
+  const double k = 1.0 / 6.0;
+  b[0] = ((k + (-3.0 * k) * s) + (3.0 * k) * s2) + (-k) * s3;
+  b[1] = ((4.0 * k) + (-6.0 * k) * s2) + (3.0 * k) * s3;
+  b[2] = ((k + (3.0 * k) * s) + (3.0 * k) * s2) + (-3.0 * k) * s3;
+  b[3] = k * s3;
+  d[0] = ((-3.0 * k) + (6.0 * k) * s) + (-3.0 * k) * s2;
+  d[1] = (-12.0 * k) * s + (9.0 * k) * s2;
+  d[2] = ((3.0 * k) + (6.0 * k) * s) + (-9.0 * k) * s2;
+  d[3] = (3.0 * k) * s2;
+}
+
+__global__ void __launch_bounds__(kNidThreads) nid_hist_grad_kernel(const NidArgs a) {
+  extern __shared__ double shg[];  // 8 planes x bins x bins
+  __shared__ unsigned int sh_pts[8 * 32];
+  const int bins = a.bins, nb2 = bins * bins;
+  const int pose = blockIdx.y;
+  for (int i = threadIdx.x; i < 8 * nb2; i += blockDim.x) shg[i] = 0.0;
+  for (int i = threadIdx.x; i < 8 * 32; i += blockDim.x) sh_pts[i] = 0u;
+  __syncthreads();
+  unsigned int* myp = sh_pts + (threadIdx.x >> 5) * 32;
+  const double* q = a.se3 + (size_t)pose * 7;
+  const double qx = q[0], qy = q[1], qz = q[2], qw = q[3], tx = q[4], ty = q[5], tz = q[6];
+  const CamD& c = a.cam;
+
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.m; i += gridDim.x * blockDim.x) {
+    const float4 p4 = __ldg(a.pts + i);
+    const double px = p4.x, py = p4.y, pz = p4.z;
+    double ux = qy * pz - qz * py, uy = qz * px - qx * pz, uz = qx * py - qy * px;
+    ux += ux; uy += uy; uz += uz;
+    const double X = (px + qw * ux + (qy * uz - qz * uy)) + tx;
+    const double Y = (py + qw * uy + (qz * ux - qx * uz)) + ty;
+    const double Z = (pz + qw * uz + (qx * uy - qy * ux)) + tz;
+    const double ib = (double)p4.w * (double)bins;
+    int bin_p;
+    if (!(ib == ib)) bin_p = 0; else if (ib >= (double)(bins - 1)) bin_p = bins - 1; else if (ib <= 0.0) bin_p = 0; else bin_p = (int)ib;
+    double u, v;
+    project(c, X, Y, Z, u, v);
+    if (!finite_d(u) || !finite_d(v)) continue;
+    const double fu = floor(u), fv = floor(v);
+    if (fu < 0.0 || fv < 0.0 || fu >= (double)a.W || fv >= (double)a.H) continue;
+    const int kx = (int)fu, ky = (int)fv;
+    atomicAdd(&myp[bin_p], 1u);
+
+    // d(pc)/d(theta): columns qx, qy, qz (d uv = 2 e_k x p; d pc = w d uv + e_k x uv + qv x d uv), qw (uv), t (identity)
+    double JX[7], JY[7], JZ[7];
+    {
+      // k = x: e = (1,0,0): e x p = (0, -pz, py)
+      double dx = 0.0, dy = -2.0 * pz, dz = 2.0 * py;
+      JX[0] = qw * dx + (0.0) + (qy * dz - qz * dy);
+      JY[0] = qw * dy + (-uz) + (qz * dx - qx * dz);
+      JZ[0] = qw * dz + (uy) + (qx * dy - qy * dx);
+      // k = y: e = (0,1,0): e x p = (pz, 0, -px); e x uv = (uz, 0, -ux)
+      dx = 2.0 * pz; dy = 0.0; dz = -2.0 * px;
+      JX[1] = qw * dx + (uz) + (qy * dz - qz * dy);
+      JY[1] = qw * dy + (0.0) + (qz * dx - qx * dz);
+      JZ[1] = qw * dz + (-ux) + (qx * dy - qy * dx);
+      // k = z: e = (0,0,1): e x p = (-py, px, 0); e x uv = (-uy, ux, 0)
+      dx = -2.0 * py; dy = 2.0 * px; dz = 0.0;
+      JX[2] = qw * dx + (-uy) + (qy * dz - qz * dy);
+      JY[2] = qw * dy + (ux) + (qz * dx - qx * dz);
+      JZ[2] = qw * dz + (0.0) + (qx * dy - qy * dx);
+      JX[3] = ux; JY[3] = uy; JZ[3] = uz;
+      JX[4] = 1.0; JY[4] = 0.0; JZ[4] = 0.0;
+      JX[5] = 0.0; JY[5] = 1.0; JZ[5] = 0.0;
+      JX[6] = 0.0; JY[6] = 0.0; JZ[6] = 1.0;
+    }
+    // projection Jacobian: (u, v) over the normalised (x, y), then (x, y) over (X, Y, Z)
+    const double iz = 1.0 / Z, x = X * iz, y = Y * iz;
+    const double x2 = x * x, y2 = y * y, r2 = x2 + y2, r4 = r2 * r2;
+    const double rc = 1.0 + c.k1 * r2 + c.k2 * r4 + c.k3 * (r2 * r4);
+    const double drc = c.k1 + 2.0 * c.k2 * r2 + 3.0 * c.k3 * r4;  // d rc / d r2
+    // d xd / dx, d xd / dy, d yd / dx, d yd / dy   (r2_x = 2x, r2_y = 2y)
+    const double xd_x = drc * 2.0 * x * x + rc + 2.0 * c.p1 * y + c.p2 * (2.0 * x + 4.0 * x);
+    const double xd_y = drc * 2.0 * y * x + 2.0 * c.p1 * x + c.p2 * (2.0 * y);
+    const double yd_x = drc * 2.0 * x * y + c.p1 * (2.0 * x) + 2.0 * c.p2 * y;
+    const double yd_y = drc * 2.0 * y * y + rc + c.p1 * (2.0 * y + 4.0 * y) + 2.0 * c.p2 * x;
+    double gu[7], gv[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) {
+      const double dxn = (JX[k] - x * JZ[k]) * iz, dyn = (JY[k] - y * JZ[k]) * iz;
+      gu[k] = c.fx * (xd_x * dxn + xd_y * dyn);
+      gv[k] = c.fy * (yd_x * dxn + yd_y * dyn);
+    }
+    double bx[4], by[4], dbx[4], dby[4];
+    bspline_d(u - fu, bx, dbx);
+    bspline_d(v - fv, by, dby);
+    int cur = -1;
+    double acc = 0.0, accA = 0.0, accB = 0.0;
+    auto flush = [&]() {
+      double* h = shg + cur * bins + bin_p;
+      atomicAdd(h, acc);
+#pragma unroll
+      for (int k = 0; k < 7; k++) atomicAdd(h + (k + 1) * nb2, accA * gu[k] + accB * gv[k]);
+    };
+#pragma unroll
+    for (int ia = 0; ia < 4; ia++) {
+      const int xx = min(max(kx - 1 + ia, 0), a.W - 1);
+#pragma unroll
+      for (int jb = 0; jb < 4; jb++) {
+        const int yy = min(max(ky - 1 + jb, 0), a.H - 1);
+        const int bi = __ldg(a.binimg + (size_t)yy * a.W + xx);
+        if (bi != cur) {
+          if (cur >= 0) flush();
+          cur = bi;
+          acc = accA = accB = 0.0;
+        }
+        acc += bx[ia] * by[jb];
+        accA += dbx[ia] * by[jb];   // d w / d u
+        accB += bx[ia] * dby[jb];   // d w / d v
+      }
+    }
+    if (cur >= 0) flush();
+  }
+  __syncthreads();
+  double* gh = a.hist + (size_t)pose * (8 * nb2 + bins);
+  for (int i = threadIdx.x; i < 8 * nb2; i += blockDim.x)
+    if (shg[i] != 0.0) atomicAdd(&gh[i], shg[i]);
+  for (int i = threadIdx.x; i < bins; i += blockDim.x) {
+    unsigned int s = 0;
+    for (int w = 0; w < 8; w++) s += sh_pts[w * 32 + i];
+    if (s) atomicAdd(&gh[8 * nb2 + i], (double)s);
+  }
+}
+
+// Entropies, NID and d NID / d theta; one warp per pose.  out: {NID, ok, g0..g6} per pose.
+//   H = -sum p log(p + eps), dH = -sum dp (log(p + eps) + p / (p + eps));  NID = (2 Hj - Hi - Hp) / Hj
+__global__ void nid_entropy_grad_kernel(const double* __restrict__ hist, int bins, int B, double* __restrict__ out) {
+  const int pose = blockIdx.x;
+  if (pose >= B) return;
+  const int nb2 = bins * bins;
+  const double* h = hist + (size_t)pose * (8 * nb2 + bins);
+  const int lane = threadIdx.x;
+  double sum = 0.0;
+  for (int i = lane; i < bins; i += 32) sum += h[8 * nb2 + i];
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  double Hi = 0.0, Hp = 0.0, Hj = 0.0, dHi[7], dHj[7];
+  for (int k = 0; k < 7; k++) dHi[k] = dHj[k] = 0.0;
+  for (int i = lane; i < bins; i += 32) {
+    double hi = 0.0, dhi[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int j = 0; j < bins; j++) {
+      hi += h[i * bins + j];
+      for (int k = 0; k < 7; k++) dhi[k] += h[(k + 1) * nb2 + i * bins + j];
+    }
+    const double p = hi / sum, lg = log(p + 1e-6);
+    Hi += p * lg;
+    const double f = lg + p / (p + 1e-6);
+    for (int k = 0; k < 7; k++) dHi[k] += (dhi[k] / sum) * f;
+    const double pp = h[8 * nb2 + i] / sum;
+    Hp += pp * log(pp + 1e-6);
+  }
+  for (int i = lane; i < nb2; i += 32) {
+    const double p = h[i] / sum, lg = log(p + 1e-6);
+    Hj += p * lg;
+    const double f = lg + p / (p + 1e-6);
+    for (int k = 0; k < 7; k++) dHj[k] += (h[(k + 1) * nb2 + i] / sum) * f;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    Hi += __shfl_xor_sync(0xffffffffu, Hi, o);
+    Hp += __shfl_xor_sync(0xffffffffu, Hp, o);
+    Hj += __shfl_xor_sync(0xffffffffu, Hj, o);
+    for (int k = 0; k < 7; k++) {
+      dHi[k] += __shfl_xor_sync(0xffffffffu, dHi[k], o);
+      dHj[k] += __shfl_xor_sync(0xffffffffu, dHj[k], o);
+    }
+  }
+  if (lane == 0) {
+    Hi = -Hi; Hp = -Hp; Hj = -Hj;
+    const double MI = Hi + Hp - Hj;
+    const double num = Hj - MI;
+    const double nid = num / Hj;
+    out[9 * pose] = nid;
+    out[9 * pose + 1] = finite_d(nid) ? 1.0 : 0.0;
+    for (int k = 0; k < 7; k++) {
+      const double dHi_k = -dHi[k], dHj_k = -dHj[k];
+      const double dnum = 2.0 * dHj_k - dHi_k;          // Hp is a constant
+      out[9 * pose + 2 + k] = (dnum * Hj - num * dHj_k) / (Hj * Hj);
+    }
+  }
+}
+
 #define CUN(call)                                                                                 \
   do {                                                                                            \
     cudaError_t e_ = (call);                                                                      \
@@ -246,6 +439,8 @@ void pcp_nid_destroy(pcp_nid* nid) {
   if (nid->d_se3) cudaFree(nid->d_se3);
   if (nid->d_hist) cudaFree(nid->d_hist);
   if (nid->d_out) cudaFree(nid->d_out);
+  if (nid->d_hist_g) cudaFree(nid->d_hist_g);
+  if (nid->d_out_g) cudaFree(nid->d_out_g);
   delete nid;
 }
 
@@ -292,6 +487,57 @@ int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_
   return PCP_OK;
 }
 
+int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, double* grad_out, uint8_t* ok_out) {
+  if (!nid || !se3 || B <= 0 || !nid_out || !grad_out) return PCP_EINVAL;
+  pcp_ctx* ctx = nid->ctx;
+  CUN(cudaSetDevice(ctx->device));
+  const int nb2 = nid->bins * nid->bins, nb = 8 * nb2 + nid->bins;
+  if (B > nid->cap_Bg) {
+    if (nid->d_hist_g) cudaFree(nid->d_hist_g);
+    if (nid->d_out_g) cudaFree(nid->d_out_g);
+    nid->d_hist_g = nullptr; nid->d_out_g = nullptr; nid->cap_Bg = 0;
+    CUN(cudaMalloc(&nid->d_hist_g, sizeof(double) * nb * B));
+    CUN(cudaMalloc(&nid->d_out_g, sizeof(double) * 9 * B));
+    nid->cap_Bg = B;
+  }
+  int rc = ensure_batch(nid, B);  // d_se3
+  if (rc != PCP_OK) return rc;
+  cudaStream_t s = ctx->stream;
+  CUN(cudaMemcpyAsync(nid->d_se3, se3, sizeof(double) * 7 * B, cudaMemcpyHostToDevice, s));
+  CUN(cudaMemsetAsync(nid->d_hist_g, 0, sizeof(double) * nb * B, s));
+  NidArgs a;
+  a.pts = nid->d_pts; a.binimg = nid->d_binimg; a.se3 = nid->d_se3; a.hist = nid->d_hist_g;
+  a.m = (uint32_t)nid->m; a.W = nid->W; a.H = nid->H; a.bins = nid->bins; a.copies = 1;
+  const pcp_camera& c = ctx->cam;
+  a.cam = CamD{c.fx, c.fy, c.cx, c.cy, c.dist[0], c.dist[1], c.dist[2], c.dist[3], c.dist[4]};
+  const size_t smem = sizeof(double) * 8 * nb2;
+  CUN(cudaFuncSetAttribute(nid_hist_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_pose = (int)((nid->m + 2047) / 2048);
+  const int want = (ctx->sm_count * 4 + B - 1) / B;
+  if (per_pose > want) per_pose = want;
+  if (per_pose < 1) per_pose = 1;
+  for (int b0 = 0; b0 < B; b0 += 65535) {
+    const int bn = B - b0 < 65535 ? B - b0 : 65535;
+    NidArgs ab = a;
+    ab.se3 = a.se3 + (size_t)b0 * 7;
+    ab.hist = a.hist + (size_t)b0 * nb;
+    nid_hist_grad_kernel<<<dim3(per_pose, bn), kNidThreads, smem, s>>>(ab);
+    ctx->launches++;
+  }
+  nid_entropy_grad_kernel<<<B, 32, 0, s>>>(nid->d_hist_g, nid->bins, B, nid->d_out_g);
+  ctx->launches++;
+  std::vector<double> h(9 * (size_t)B);
+  CUN(cudaMemcpyAsync(h.data(), nid->d_out_g, sizeof(double) * 9 * B, cudaMemcpyDeviceToHost, s));
+  CUN(cudaStreamSynchronize(s));
+  CUN(cudaGetLastError());
+  for (int b = 0; b < B; b++) {
+    nid_out[b] = h[9 * b];
+    if (ok_out) ok_out[b] = h[9 * b + 1] != 0.0 ? 1 : 0;
+    for (int k = 0; k < 7; k++) grad_out[7 * (size_t)b + k] = h[9 * b + 2 + k];
+  }
+  return PCP_OK;
+}
+
 // Pose gate of MultiNIDCost (visual_camera_calibration.cpp:99-105): delta = init^-1 * T.
 static bool nid_pose_gate(const double* i7, const double* t7) {
   const double ax = -i7[0], ay = -i7[1], az = -i7[2], aw = i7[3];  // conjugate of the (unit) init quaternion
@@ -325,6 +571,28 @@ int pcp_nid_eval_multi(pcp_nid* const* costs, int n_costs, const double init_se3
     for (int b = 0; b < B; b++) {
       sum_out[b] += vals[b];                       // visual_camera_calibration.cpp:116-119
       if (!oks[b]) ok_out[b] = 0;                  // :123
+    }
+  }
+  return PCP_OK;
+}
+
+int pcp_nid_eval_multi_grad(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
+                            double* grad_sum_out, uint8_t* ok_out) {
+  if (!costs || n_costs <= 0 || !init_se3 || !se3 || B <= 0 || !sum_out || !grad_sum_out || !ok_out) return PCP_EINVAL;
+  std::vector<double> vals(B), grads(7 * (size_t)B);
+  std::vector<uint8_t> oks(B);
+  for (int b = 0; b < B; b++) {
+    ok_out[b] = nid_pose_gate(init_se3, se3 + 7 * (size_t)b) ? 1 : 0;
+    sum_out[b] = 0.0;
+    for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] = 0.0;
+  }
+  for (int c = 0; c < n_costs; c++) {
+    const int rc = pcp_nid_eval_grad(costs[c], se3, B, vals.data(), grads.data(), oks.data());
+    if (rc != PCP_OK) return rc;
+    for (int b = 0; b < B; b++) {
+      sum_out[b] += vals[b];  // residuals[0] += residuals[i] on Jets: values and dual parts add (visual_camera_calibration.cpp:116-119)
+      for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] += grads[7 * (size_t)b + k];
+      if (!oks[b]) ok_out[b] = 0;
     }
   }
   return PCP_OK;

@@ -266,6 +266,33 @@ def test_nid(oracle, built_lib):
         cost.close()
 
 
+def test_nid_gradient(oracle, built_lib):
+    """NIDCost::operator()<ceres::Jet<double,7>>: value and the 7 ambient partials within 1e-5 relative of the oracle's Jet7."""
+    from pointcloudprocessor_b200 import api, synth
+    W, H = 640, 480
+    sc = make_scene(120_000, 1, W, H)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    w2c, _ = oracle.pose_matrices(sc["poses"][0])
+    pts_cam = oracle.transform(sc["cloud"], w2c)
+    keep = oracle.view_culling(cam_o, W, H, pts_cam)
+    culled = np.concatenate([pts_cam[keep], sc["cloud"][keep, 3:]], 1)
+    grey = synth.grey_plane(sc["images"][0])
+    cands = synth.make_nid_candidates(6)
+    with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(W, H))) as gc:
+        cost = api.NIDCost(gc, grey, culled, 16)
+        val, grad, ok = cost.evaluate_with_gradient(cands)
+        val0, ok0 = cost(cands)
+        assert np.allclose(val, val0, rtol=1e-12, atol=0) and np.array_equal(ok, ok0)
+        for b in range(cands.shape[0]):
+            rok, rv, rg = oracle.nid_grad(cam_o, grey, culled, cands[b])
+            assert ok[b] == rok
+            assert abs(val[b] - rv) <= 1e-5 * abs(rv)
+            assert np.abs(grad[b] - rg).max() <= 1e-5 * np.abs(rg).max(), (b, grad[b], rg)
+        s, g, okm = api.multi_nid_with_gradient([cost, cost], cands[0], cands[1:3])
+        assert okm.all() and np.allclose(s, 2 * val[1:3], rtol=1e-12) and np.allclose(g, 2 * grad[1:3], rtol=1e-12)
+        cost.close()
+
+
 @pytest.mark.parametrize("width", [4096, 4099, 33])
 def test_hsv_roundtrip_device(oracle, built_lib, width):
     """hsv_roundtrip_kernel against the oracle on every 24-bit colour (and against cv2 when it is importable on the box)."""

@@ -380,3 +380,27 @@ def test_hsv_roundtrip_scales(oracle):
     img = np.ascontiguousarray(_all_colours(4096)[::16])
     for sat, val in ((1.2, 1.0), (1.0, 1.2), (0.7, 0.9)):
         assert np.array_equal(oracle.hsv_roundtrip(img, sat, val), _cv2_roundtrip(img, sat, val)), (sat, val)
+
+
+def test_nid_jet_gradient_matches_finite_differences(oracle):
+    """The oracle's Jet7 restatement of NIDCost::operator()<ceres::Jet<double,7>>: same value as the double path, gradient equal to
+    central differences of the double path."""
+    from pointcloudprocessor_b200 import synth
+    W, H = 320, 240
+    intr, dist = synth.make_camera(W, H)
+    cam = oracle.camera(intr, dist)
+    rng = np.random.default_rng(0)
+    n = 4000
+    pts = np.zeros((n, 4), np.float32)
+    pts[:, 0] = rng.uniform(-1, 1, n); pts[:, 1] = rng.uniform(-0.8, 0.8, n); pts[:, 2] = rng.uniform(2, 6, n); pts[:, 3] = rng.random(n)
+    img = synth.grey_plane(synth.make_image(0, W, H))
+    se3 = np.array([0.01, -0.02, 0.005, 0.9997, 0.03, -0.02, 0.01])
+    ok, v, g = oracle.nid_grad(cam, img, pts, se3)
+    v0, ok0 = oracle.nid(cam, img, pts, se3)[:2]
+    assert ok and ok0 and abs(v - v0) <= 1e-13
+    fd = np.zeros(7)
+    for k in range(7):
+        a, b = se3.copy(), se3.copy()
+        a[k] += 1e-6; b[k] -= 1e-6
+        fd[k] = (oracle.nid(cam, img, pts, a)[0] - oracle.nid(cam, img, pts, b)[0]) / 2e-6
+    assert np.abs(g - fd).max() <= 1e-5 * np.abs(g).max()
