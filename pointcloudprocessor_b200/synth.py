@@ -92,7 +92,7 @@ def _path_vertices(n_needed: int, step: float):
         xa, xb = (x0, x0 + pass_len) if k % 2 == 0 else (x0 + pass_len, x0)
         verts.append((xa, y, z))
         verts.append((xb, y, z))
-        total += 317 + 30
+        total += 300  # a pass yields 317 poses plus the short lateral move: under-count so that enough vertices exist
         k += 1
     return verts
 
