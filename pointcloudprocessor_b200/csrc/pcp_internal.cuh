@@ -10,7 +10,10 @@ namespace pcp {
 // Initial z-grid key: fl32 FLT_MAX in the high word (view_culling.cpp:64), index 0xffffffff (= -1, :65).
 static constexpr unsigned long long kZInit = (0x7f7fffffull << 32) | 0xffffffffull;
 static constexpr unsigned int kZBoundInit = 0x7f7fffffu;  // FLT_MAX
-static constexpr int kChunk = 128;  // points per pre-binned chunk = one warp iteration of the scan kernel (4 x 32)
+#ifndef PCP_CHUNK
+#define PCP_CHUNK 64
+#endif
+static constexpr int kChunk = PCP_CHUNK;  // points per pre-binned chunk = one warp iteration of the scan kernel (kChunk/32 x 32)
 
 // One candidate that may still be visible after pass 1 (32 bytes, written/read as two 16-byte words).
 struct __align__(16) Record {

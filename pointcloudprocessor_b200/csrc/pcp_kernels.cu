@@ -201,7 +201,8 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
 #define PCP_ZLOAD0(p) __ldcg(p)
 #endif
 static constexpr int kUnroll = PCP_UNROLL;
-static_assert(kUnroll * 32 == kChunk, "one pre-binned chunk = one warp iteration");
+static constexpr int kGroups = kChunk / 32;  // pre-binned scan: one chunk = one warp iteration of kGroups x 32 points
+static_assert(kGroups >= 1 && kGroups * 32 == kChunk, "chunk size must be a multiple of 32");
 
 // ---------------------------------------------------------------------------------------------------------------------
 // classify_kernel (pre-binned cloud): one lane per chunk runs classify_chunk; chunks that must be processed are appended to
@@ -377,7 +378,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
 #define PCP_A1W 2
 #endif
 static constexpr int kA1 = PCP_A1W;
-static constexpr int kQ0Cap = 32 * (kUnroll + 1);  // < 32 left over + one chunk
+static constexpr int kQ0Cap = 32 * (kGroups + 1);  // < 32 left over + one chunk
 static constexpr int kQ1Cap = 32 * (kA1 + 1);      // < 32 left over + one A1 batch
 static constexpr size_t kBinnedSmem = (size_t)kWarpsPerCta * ((kQ0Cap + kQ1Cap) * sizeof(float4) + kQueueCap * sizeof(Record));
 
@@ -512,7 +513,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
     uint4 nent = kNoEnt;
     if (nitem < n_active) {
       nent = __ldg(a.active + nitem);
-      if (lane < 16) prefetch_l2(a.cloud + (size_t)nent.x * kChunk + lane * 8);  // 16 lines of 128 B
+      if (lane < kChunk / 8) prefetch_l2(a.cloud + (size_t)nent.x * kChunk + lane * 8);  // the chunk in lines of 128 B
     }
     const unsigned int zb = rect_bits(ent);
     const uint32_t base = ent.x * kChunk;
@@ -528,16 +529,16 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
       st_skipped++;
 #endif
     } else {
-      float4 p[kUnroll];
-      bool valid[kUnroll];
+      float4 p[kGroups];
+      bool valid[kGroups];
 #pragma unroll
-      for (int k = 0; k < kUnroll; k++) {
+      for (int k = 0; k < kGroups; k++) {
         const uint32_t i = base + k * 32 + lane;  // sorted position: the accumulator slot
         valid[k] = i < a.n;
         p[k] = valid[k] ? __ldcs(a.cloud + i) : make_float4(0.f, 0.f, -1.f, 0.f);
       }
 #pragma unroll
-      for (int k = 0; k < kUnroll; k++) {
+      for (int k = 0; k < kGroups; k++) {
         float x = p[k].x, y = p[k].y, z = p[k].z;
         if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x, y, z);  // pcl::transformPointCloud (cpp:521)
         const bool front = valid[k] && !(z < 0.0f);  // view_culling.cpp:76 (exact: double(z) < 0 <=> z < 0)
