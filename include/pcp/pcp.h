@@ -48,7 +48,7 @@ typedef struct {
   int accum_mode;                  /* PCP_ACCUM_SUM (u32 sums+count, all-reducible) | PCP_ACCUM_TOP5 (cpp:604-631) */
   int sample_mode;                 /* PCP_SAMPLE_NEAREST (reference, cpp:752-762) | PCP_SAMPLE_BILINEAR (extension) */
   int top_m;                       /* 5 (cpp:615) */
-  int prebin;                      /* 1 (default): Morton-sort the device copy of the cloud into 128-point chunks with bounding
+  int prebin;                      /* 1 (default): Morton-sort the device copy of the cloud into 64-point chunks with bounding
                                     * boxes at set_cloud; chunks certainly behind the camera / outside the z-grid are skipped per
                                     * frame.  Every output stays in the caller's point order.  0: keep the caller's order. */
   int frames_in_flight;            /* 1..3 (0 = default 3): frames run on that many internal streams, each with its own z-grid / record
@@ -189,12 +189,13 @@ typedef struct {
   const char* mask_image_folder;       /* NULL or "" disables the mask path (cpp:89) */
   const char* output_path;
   int enable_mls;                      /* must be 0: pcl::MovingLeastSquares is out of scope (-> PCP_EINVAL) */
-  int enable_nid_optimize;             /* must be 0: the Ceres optimiser is out of scope; pass T_camera_lidar_optimized instead */
+  int enable_nid_optimize;             /* applyNIDBasedPoseOptimization (cpp:156-164): pcp_calibrate over the keyframes' NID costs, from Identity */
   int enable_initial_guess_manual;     /* must be 0: the GUI needs a graphics stack (unavailable on this box) */
   int device;
   const pcp_camera* camera;            /* NULL: the reference camera (cpp:57-60) */
   int cull_width, cull_height;         /* 0: 4096 x 3000 (cpp:525) */
-  const double* T_camera_lidar_optimized; /* optional 4x4 column-major: the result NID / the manual guess would have produced (cpp:504-519) */
+  const double* T_camera_lidar_optimized; /* optional 4x4 column-major: the result NID / the manual guess would have produced (cpp:504-519);
+                                          * with enable_nid_optimize it is the initial guess instead of Identity */
   int skip_outputs;                    /* 1: compute everything but write no PCD (benchmarks) */
   int sample_mode;                     /* PCP_SAMPLE_NEAREST (reference) | PCP_SAMPLE_BILINEAR */
   int reserved[9];
@@ -204,6 +205,10 @@ typedef struct {
   int64_t n_points, n_cropped, n_frames, n_keyframes, n_colored_points, n_mask_points;
   int64_t n_visible_total;             /* sum over keyframes of the culled cloud sizes (loop #1) */
   double seconds_load, seconds_cull_pass, seconds_color_pass, seconds_write, seconds_total;
+  double seconds_nid;                  /* enable_nid_optimize: image planes + NID costs + the solver */
+  int64_t nid_outer_iterations, nid_inner_iterations, nid_cost_evaluations, nid_converged;
+  double nid_initial_cost, nid_final_cost;
+  double T_camera_lidar[16];           /* the extrinsic the colour pass used (column-major; identity when none) */
 } pcp_process_stats;
 
 /* Returns a pcp_status; on failure `err` (if given) receives the message the reference would have thrown. */
@@ -230,6 +235,68 @@ int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, d
 /* MultiNIDCost::operator()<Jet>: pose gate, then sums of values and gradients over the frames. */
 int pcp_nid_eval_multi_grad(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
                             double* grad_sum_out, uint8_t* ok_out);
+
+/* ---- pose refinement: the caller of the NID cost ------------------------------------------------------
+ * ceres::GradientProblemSolver with line_search_direction_type = BFGS on Sophus::Manifold<SE3>
+ * (src/vlcal/calib/visual_camera_calibration.cpp:204-233).  Ceres / Sophus are not vendored by the reference; the
+ * solver is a restatement of their published algorithms with ceres' default constants (csrc/pcp_calib.cu). */
+typedef struct {
+  int max_num_iterations;                        /* 50 */
+  double function_tolerance;                     /* 1e-6 */
+  double gradient_tolerance;                     /* 1e-10 */
+  double parameter_tolerance;                    /* 1e-8 */
+  double sufficient_function_decrease;           /* 1e-4 */
+  double sufficient_curvature_decrease;          /* 0.9 */
+  double max_line_search_step_expansion;         /* 10 */
+  double min_line_search_step_contraction;       /* 0.6 */
+  double max_line_search_step_contraction;       /* 1e-3 */
+  double min_line_search_step_size;              /* 1e-9 */
+  int max_num_line_search_step_size_iterations;  /* 20 */
+  int max_num_line_search_direction_restarts;    /* 5 */
+  int verbose;                                   /* 1: one line per iteration on stderr (minimizer_progress_to_stdout) */
+  int reserved[5];
+} pcp_bfgs_options;
+
+enum { PCP_BFGS_CONVERGENCE = 0, PCP_BFGS_NO_CONVERGENCE = 1, PCP_BFGS_FAILURE = 2 };
+
+typedef struct {
+  int iterations, termination;                   /* termination: PCP_BFGS_* */
+  int num_cost_evaluations, num_line_search_steps;
+  double initial_cost, final_cost;
+  char message[96];
+} pcp_bfgs_summary;
+
+/* A first-order function over SE3 in Sophus' ambient order {qx,qy,qz,qw,tx,ty,tz}: writes the value and the 7 ambient partial
+ * derivatives (what AutoDiffFirstOrderFunction<F, 7> produces); returns 0 where the functor returns false. */
+typedef int (*pcp_se3_cost_fn)(void* user, const double se3[7], double* value, double grad7[7]);
+
+void pcp_bfgs_default_options(pcp_bfgs_options* options);
+/* ceres::Solve(options, GradientProblem(cost, Sophus::Manifold<SE3>), x) for any first-order function (host callback). */
+int pcp_se3_bfgs(pcp_se3_cost_fn fn, void* user, const double init_se3[7], const pcp_bfgs_options* options, double out_se3[7],
+                 pcp_bfgs_summary* summary);
+
+/* vlcal::VisualCameraCalibrationParams (include/vlcal/calib/visual_camera_calibration.hpp:14-48). */
+typedef struct {
+  int max_outer_iterations;                      /* 10 */
+  double delta_trans_thresh;                     /* 0.01 m */
+  double delta_rot_thresh;                       /* 1 degree in radians */
+  pcp_bfgs_options inner;
+} pcp_calib_params;
+
+typedef struct {
+  int outer_iterations, converged;               /* converged: the outer loop met both thresholds */
+  int inner_iterations, cost_evaluations, last_inner_termination;
+  double initial_cost, final_cost;               /* sum of the frames' NID at the first / last pose */
+  double delta_t, delta_r;                       /* last outer step */
+} pcp_calib_summary;
+
+void pcp_calib_default_params(pcp_calib_params* params);
+/* VisualCameraCalibration::calibrate(init_T_camera_lidar) (visual_camera_calibration.cpp:49-84) over the per-keyframe NID
+ * costs (estimate_pose_bfgs, :142-252): outer loop of BFGS solves, each with the pose gate re-centred on its start, until
+ * the step between two solves is below both thresholds.  Every cost / gradient evaluation runs on the device
+ * (pcp_nid_eval_multi_grad).  Matrices 4x4 column-major. */
+int pcp_calibrate(pcp_nid* const* costs, int n_costs, const double init_T_camera_lidar[16], const pcp_calib_params* params,
+                  double out_T_camera_lidar[16], pcp_calib_summary* summary);
 
 /* Counters for benches: kernels launched by this context since creation. */
 uint64_t pcp_launch_count(const pcp_ctx* ctx);

@@ -225,6 +225,41 @@ class MultiNIDCost {
   std::vector<pcp_nid*> handles_;
 };
 
+// VisualCameraCalibrationParams / VisualCameraCalibration (include/vlcal/calib/visual_camera_calibration.hpp:14-70).  The keyframes'
+// culled clouds and normalised images are handed over as NIDCost objects (estimate_pose_bfgs builds exactly these, :150-181).
+struct VisualCameraCalibrationParams {
+  int max_outer_iterations = 10;
+  double delta_trans_thresh = 0.01;
+  double delta_rot_thresh = 1.0 * 3.14159265358979323846 / 180.0;
+  bool verbose = false;
+};
+
+class VisualCameraCalibration {
+ public:
+  VisualCameraCalibration(const std::vector<std::shared_ptr<NIDCost>>& keyframe_costs, const VisualCameraCalibrationParams& params = VisualCameraCalibrationParams())
+      : costs_(keyframe_costs), params_(params) {}
+  // Eigen::Isometry3d calibrate(const Eigen::Isometry3d& init_T_camera_lidar)  (visual_camera_calibration.cpp:49-84)
+  pcp::Isometry3d calibrate(const pcp::Isometry3d& init_T_camera_lidar) {
+    std::vector<pcp_nid*> h;
+    for (const auto& c : costs_) h.push_back(c->handle());
+    pcp_calib_params p;
+    pcp_calib_default_params(&p);
+    p.max_outer_iterations = params_.max_outer_iterations;
+    p.delta_trans_thresh = params_.delta_trans_thresh;
+    p.delta_rot_thresh = params_.delta_rot_thresh;
+    p.inner.verbose = params_.verbose;
+    pcp::Isometry3d out;
+    if (pcp_calibrate(h.data(), (int)h.size(), init_T_camera_lidar.data(), &p, out.m, &summary_) != PCP_OK) throw std::runtime_error("pcp_calibrate failed");
+    return out;
+  }
+  const pcp_calib_summary& summary() const { return summary_; }
+
+ private:
+  std::vector<std::shared_ptr<NIDCost>> costs_;
+  VisualCameraCalibrationParams params_;
+  pcp_calib_summary summary_{};
+};
+
 }  // namespace vlcal
 
 // PointCloudProcessor(pointCloudPath, odometryPath, imagesFolder, maskImageFolder, outputPath, enableMLS, enableNIDOptimize,

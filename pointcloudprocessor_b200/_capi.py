@@ -51,7 +51,9 @@ class ProcessStats(C.Structure):
     _fields_ = [
         ("n_points", C.c_int64), ("n_cropped", C.c_int64), ("n_frames", C.c_int64), ("n_keyframes", C.c_int64), ("n_colored_points", C.c_int64),
         ("n_mask_points", C.c_int64), ("n_visible_total", C.c_int64), ("seconds_load", C.c_double), ("seconds_cull_pass", C.c_double),
-        ("seconds_color_pass", C.c_double), ("seconds_write", C.c_double), ("seconds_total", C.c_double),
+        ("seconds_color_pass", C.c_double), ("seconds_write", C.c_double), ("seconds_total", C.c_double), ("seconds_nid", C.c_double),
+        ("nid_outer_iterations", C.c_int64), ("nid_inner_iterations", C.c_int64), ("nid_cost_evaluations", C.c_int64), ("nid_converged", C.c_int64),
+        ("nid_initial_cost", C.c_double), ("nid_final_cost", C.c_double), ("T_camera_lidar", C.c_double * 16),
     ]
 
 
@@ -61,7 +63,34 @@ SYMBOLS = [
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
+    "pcp_bfgs_default_options", "pcp_se3_bfgs", "pcp_calib_default_params", "pcp_calibrate",
 ]
+class BfgsOptions(C.Structure):
+    _fields_ = [
+        ("max_num_iterations", C.c_int), ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double), ("parameter_tolerance", C.c_double),
+        ("sufficient_function_decrease", C.c_double), ("sufficient_curvature_decrease", C.c_double), ("max_line_search_step_expansion", C.c_double),
+        ("min_line_search_step_contraction", C.c_double), ("max_line_search_step_contraction", C.c_double), ("min_line_search_step_size", C.c_double),
+        ("max_num_line_search_step_size_iterations", C.c_int), ("max_num_line_search_direction_restarts", C.c_int), ("verbose", C.c_int),
+        ("reserved", C.c_int * 5),
+    ]
+
+
+class BfgsSummary(C.Structure):
+    _fields_ = [("iterations", C.c_int), ("termination", C.c_int), ("num_cost_evaluations", C.c_int), ("num_line_search_steps", C.c_int),
+                ("initial_cost", C.c_double), ("final_cost", C.c_double), ("message", C.c_char * 96)]
+
+
+class CalibParams(C.Structure):
+    _fields_ = [("max_outer_iterations", C.c_int), ("delta_trans_thresh", C.c_double), ("delta_rot_thresh", C.c_double), ("inner", BfgsOptions)]
+
+
+class CalibSummary(C.Structure):
+    _fields_ = [("outer_iterations", C.c_int), ("converged", C.c_int), ("inner_iterations", C.c_int), ("cost_evaluations", C.c_int),
+                ("last_inner_termination", C.c_int), ("initial_cost", C.c_double), ("final_cost", C.c_double), ("delta_t", C.c_double),
+                ("delta_r", C.c_double)]
+
+
+SE3_COST_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double))
 
 _lib = None
 
@@ -124,6 +153,12 @@ def load():
     L.pcp_hsv_roundtrip.argtypes = [vp, vp, sz, vp, sz, i32, i32, C.c_float, C.c_float]
     L.pcp_nid_eval_grad.argtypes = [vp, vp, i32, vp, vp, vp]
     L.pcp_nid_eval_multi_grad.argtypes = [C.POINTER(vp), i32, vp, vp, i32, vp, vp, vp]
+    L.pcp_bfgs_default_options.argtypes = [C.POINTER(BfgsOptions)]
+    L.pcp_bfgs_default_options.restype = None
+    L.pcp_se3_bfgs.argtypes = [SE3_COST_FN, vp, vp, C.POINTER(BfgsOptions), vp, C.POINTER(BfgsSummary)]
+    L.pcp_calib_default_params.argtypes = [C.POINTER(CalibParams)]
+    L.pcp_calib_default_params.restype = None
+    L.pcp_calibrate.argtypes = [C.POINTER(vp), i32, vp, C.POINTER(CalibParams), vp, C.POINTER(CalibSummary)]
     L.pcp_launch_count.argtypes = [vp]
     L.pcp_launch_count.restype = C.c_uint64
     _lib = L

@@ -434,6 +434,69 @@ def multi_nid_with_gradient(costs, init_se3, se3_params):
     return out, grad, ok.astype(bool)
 
 
+def bfgs_options(**kw) -> _capi.BfgsOptions:
+    """ceres::GradientProblemSolver::Options at their defaults with line_search_direction_type = BFGS."""
+    o = _capi.BfgsOptions()
+    _capi.load().pcp_bfgs_default_options(C.byref(o))
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise AttributeError(k)
+        setattr(o, k, v)
+    return o
+
+
+def _summary_dict(st):
+    d = {k: getattr(st, k) for k, _ in st._fields_}
+    if "message" in d:
+        d["message"] = d["message"].decode(errors="replace")
+    return d
+
+
+def se3_bfgs(fn, init_se3, options: _capi.BfgsOptions | None = None):
+    """ceres::Solve over Sophus::Manifold<SE3> for a host first-order function: fn(se3[7]) -> (value, grad7, ok).
+    Returns (se3, summary)."""
+    def cb(_user, x, value, grad):
+        v, g, ok = fn(np.array([x[i] for i in range(7)], np.float64))
+        value[0] = float(v)
+        for i in range(7):
+            grad[i] = float(g[i])
+        return 1 if ok else 0
+    cfn = _capi.SE3_COST_FN(cb)
+    init = np.ascontiguousarray(init_se3, np.float64)
+    out = np.empty(7, np.float64)
+    st = _capi.BfgsSummary()
+    rc = _capi.load().pcp_se3_bfgs(cfn, None, _ptr(init), C.byref(options) if options is not None else None, _ptr(out), C.byref(st))
+    if rc != _capi.PCP_OK:
+        raise PcpError(f"pcp_se3_bfgs failed ({rc})", rc)
+    return out, _summary_dict(st)
+
+
+def calibrate(costs, init_T_camera_lidar=None, max_outer_iterations=None, delta_trans_thresh=None, delta_rot_thresh=None, **inner):
+    """vlcal::VisualCameraCalibration(proj, keyframes, params).calibrate(init_T_camera_lidar)
+    (src/vlcal/calib/visual_camera_calibration.cpp:49-84, :142-252) over NIDCost objects.  Returns (T 4x4, summary)."""
+    L = _capi.load()
+    p = _capi.CalibParams()
+    L.pcp_calib_default_params(C.byref(p))
+    if max_outer_iterations is not None:
+        p.max_outer_iterations = int(max_outer_iterations)
+    if delta_trans_thresh is not None:
+        p.delta_trans_thresh = float(delta_trans_thresh)
+    if delta_rot_thresh is not None:
+        p.delta_rot_thresh = float(delta_rot_thresh)
+    for k, v in inner.items():
+        if not hasattr(p.inner, k):
+            raise AttributeError(k)
+        setattr(p.inner, k, v)
+    T0 = np.eye(4) if init_T_camera_lidar is None else np.asarray(init_T_camera_lidar, np.float64)
+    t_in = np.ascontiguousarray(T0.T.reshape(-1))
+    t_out = np.empty(16, np.float64)
+    st = _capi.CalibSummary()
+    arr = (C.c_void_p * len(costs))(*[c._h for c in costs])
+    rc = L.pcp_calibrate(arr, len(costs), _ptr(t_in), C.byref(p), _ptr(t_out), C.byref(st))
+    costs[0]._ctx._check(rc, "pcp_calibrate")
+    return t_out.reshape(4, 4).T.copy(), _summary_dict(st)
+
+
 def multi_nid(costs, init_se3, se3_params):
     """MultiNIDCost::operator()<double> (src/vlcal/calib/visual_camera_calibration.cpp:93-124)."""
     L = _capi.load()

@@ -170,6 +170,13 @@ inline int fmt_f(char* b, float v) {
 }
 inline uint32_t pack_rgb(uint8_t r, uint8_t g, uint8_t b, uint8_t a = 255) { return ((uint32_t)a << 24) | ((uint32_t)r << 16) | ((uint32_t)g << 8) | b; }
 
+// A float as it comes back from the ASCII PCD (written with 8 significant digits, read with strtof).
+inline float through_text(float v) {
+  char b[40];
+  b[fmt_f(b, v)] = 0;
+  return std::strtof(b, nullptr);
+}
+
 inline bool write_pcd_xyzi(const std::string& path, const XYZI* pts, size_t n) {
   FILE* f = std::fopen(path.c_str(), "wb");
   if (!f) return false;

@@ -18,7 +18,7 @@ static const char* kHelp =
     "  -m [ --mask_image_folder ] arg        Path to directory for segmented images\n"
     "  -t [ --output_path ] arg (=.)         Path to save processed output\n"
     "  --enableMLS arg (=0)                  Enable MLS smoothing (not available in this build)\n"
-    "  --enableNIDOptimize arg (=0)          Enable NID-based camera pose optimization (not available in this build)\n"
+    "  --enableNIDOptimize arg (=0)          Enable NID-based camera pose optimization\n"
     "  --enableInitialGuessManual arg (=0)   Enable manual pickup point based camera pose optimization (not available)\n"
     "  --cull_size WxH                       image_size handed to ViewCulling (reference: 4096x3000)\n"
     "  --intrinsics fx,fy,cx,cy              pinhole intrinsics (reference values by default)\n"

@@ -5,8 +5,9 @@
 // Host control flow only; every per-point computation of the hot path runs in the CUDA kernels behind pcp_cull_pose /
 // pcp_submit_frame / pcp_finalize.  The host re-derives camera-frame coordinates of the (few) points it writes to disk with
 // the same float arithmetic (PCL order, no FMA: this file is compiled with -ffp-contract=off).
-// Not available here: MLS smoothing, the Ceres NID optimiser, the manual-guess GUI; an already
-// optimised T_camera_lidar can be passed in instead (pcp_process_args.T_camera_lidar_optimized).
+// enableNIDOptimize runs the extrinsic refinement of csrc/pcp_calib.cu over the device NID costs.  Not available here (SURVEY.md §2
+// rows 6, 12): MLS smoothing and the manual-guess GUI; an already optimised T_camera_lidar can be passed in instead
+// (pcp_process_args.T_camera_lidar_optimized).
 #include <chrono>
 #include <cfloat>
 #include <cmath>
@@ -90,7 +91,6 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
   const double t_start = now_s();
   if (!A.point_cloud_path || !A.odometry_path || !A.images_folder || !A.output_path) throw ProcError(PCP_EINVAL, "pcp_process: missing path");
   if (A.enable_mls) throw ProcError(PCP_EINVAL, "pcp_process: enableMLS is not available in this build (pcl::MovingLeastSquares is out of scope)");
-  if (A.enable_nid_optimize) throw ProcError(PCP_EINVAL, "pcp_process: enableNIDOptimize is not available in this build (pass T_camera_lidar_optimized)");
   if (A.enable_initial_guess_manual) throw ProcError(PCP_EINVAL, "pcp_process: enableInitialGuessManual needs a graphics stack (unavailable)");
   const std::string images_folder = A.images_folder, out_path = A.output_path;
   const std::string mask_folder = A.mask_image_folder ? A.mask_image_folder : "";
@@ -193,11 +193,12 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
   const double t_cull = now_s();
   std::vector<int32_t> idx(N);
   std::vector<io::XYZI> culled;
+  std::vector<std::vector<io::XYZI>> culled_for_nid;  // what estimate_pose_bfgs reads back from <ts>_beforeNID.pcd
   for (const Frame* kf : keyframes) {
     size_t m = 0;
     check(ctx, pcp_cull_pose(ctx, kf->pose, nullptr, idx.data(), &m), "pcp_cull_pose");  // the un-optimised pose, cpp:188-196
     S.n_visible_total += (int64_t)m;
-    if (A.skip_outputs) continue;
+    if (A.skip_outputs && !A.enable_nid_optimize) continue;
     host::M4f w2c, c2w;
     host::pose_matrices(kf->pose, nullptr, w2c, c2w);
     culled.resize(m);
@@ -206,10 +207,68 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
       xform(w2c, p.x, p.y, p.z, culled[j].x, culled[j].y, culled[j].z);
       culled[j].intensity = p.intensity;
     }
-    const std::string path = out_path + "filtered_pcd/" + io::to_string_f(kf->ts) + "_beforeNID.pcd";  // cpp:213
-    if (!io::write_pcd_xyzi(path, culled.data(), m)) throw ProcError(PCP_EIO, "Couldn't save filtered point cloud to PCD file.");  // cpp:220
+    if (!A.skip_outputs) {
+      const std::string path = out_path + "filtered_pcd/" + io::to_string_f(kf->ts) + "_beforeNID.pcd";  // cpp:213
+      if (!io::write_pcd_xyzi(path, culled.data(), m)) throw ProcError(PCP_EIO, "Couldn't save filtered point cloud to PCD file.");  // cpp:220
+    }
+    if (A.enable_nid_optimize) {
+      // the optimiser re-reads the ASCII file (visual_camera_calibration.cpp:163): 8 significant digits do not round-trip every
+      // float, so the in-memory copy goes through the same text form
+      for (size_t j = 0; j < m; j++) {
+        culled[j].x = io::through_text(culled[j].x); culled[j].y = io::through_text(culled[j].y);
+        culled[j].z = io::through_text(culled[j].z); culled[j].intensity = io::through_text(culled[j].intensity);
+      }
+      culled_for_nid.push_back(culled);
+    }
   }
   S.seconds_cull_pass = now_s() - t_cull;
+
+  // ---- applyNIDBasedPoseOptimization (cpp:156-164, src/calibrate.cpp:42-79, visual_camera_calibration.cpp:49-252) ------------
+  double T_nid[16];
+  const double* T_opt = A.T_camera_lidar_optimized;
+  if (A.enable_nid_optimize) {
+    const double t_nid = now_s();
+    struct NidGuard { std::vector<pcp_nid*> v; ~NidGuard() { for (pcp_nid* n : v) pcp_nid_destroy(n); } } nids;
+    std::vector<double> plane;
+    for (size_t k = 0; k < keyframes.size(); k++) {
+      HostImage img;
+      if (k == 0) img = first;
+      else if (!load_image(keyframes[k]->image_path, false, img, why)) throw ProcError(PCP_EIO, "Failed to read image from: " + keyframes[k]->image_path);
+      // cv::imread gives a 3-channel image and convertTo(CV_64FC1, 1/255) keeps the channels (only the depth changes), yet NIDCost reads
+      // it with at<double>(y, x) and cols x rows bounds (nid_cost.hpp:61, :88): element x of row y of the INTERLEAVED doubles, i.e. the
+      // first cols values B0 G0 R0 B1 ... of each row.  Restated literally (PCP_NID_GREY_PLANE=1 in the environment takes the grey image
+      // a single-channel reading would have seen instead).
+      const int w = img.width, h = img.height;
+      static const bool grey = std::getenv("PCP_NID_GREY_PLANE") != nullptr;
+      if (grey) io::to_grey(img);
+      plane.resize((size_t)w * h);
+      const size_t row = (size_t)w * (size_t)img.channels;
+      for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) plane[(size_t)y * w + x] = (double)img.data[(size_t)y * row + x] * (1.0 / 255.0);
+      pcp_nid* nid = nullptr;
+      const std::vector<io::XYZI>& pts = culled_for_nid[k];
+      if (pts.empty()) continue;  // a frame that sees nothing adds no cost
+      check(ctx, pcp_nid_create(ctx, pts.data(), pts.size(), sizeof(io::XYZI), 12, plane.data(), w, h, 16, &nid), "pcp_nid_create");  // nid_bins = 16, calibrate.cpp:52
+      nids.v.push_back(nid);
+    }
+    if (nids.v.empty()) throw ProcError(PCP_EINVAL, "pcp_process: NID optimisation has no visible points in any keyframe");
+    pcp_calib_params cp;
+    pcp_calib_default_params(&cp);
+    cp.inner.verbose = std::getenv("PCP_VERBOSE") != nullptr;
+    double T0[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};  // init_T_camera_lidar = Identity, calibrate.cpp:46
+    if (A.T_camera_lidar_optimized) std::memcpy(T0, A.T_camera_lidar_optimized, sizeof(T0));  // extension: a caller-supplied initial guess
+    pcp_calib_summary cs;
+    check(ctx, pcp_calibrate(nids.v.data(), (int)nids.v.size(), T0, &cp, T_nid, &cs), "pcp_calibrate");
+    T_opt = T_nid;
+    S.nid_outer_iterations = cs.outer_iterations;
+    S.nid_inner_iterations = cs.inner_iterations;
+    S.nid_cost_evaluations = cs.cost_evaluations;
+    S.nid_converged = cs.converged;
+    S.nid_initial_cost = cs.initial_cost;
+    S.nid_final_cost = cs.final_cost;
+    S.seconds_nid = now_s() - t_nid;
+  }
+  for (int i = 0; i < 16; i++) S.T_camera_lidar[i] = T_opt ? T_opt[i] : (i % 5 == 0 ? 1.0 : 0.0);
 
   // ---- pcdColorizationAndSmooth (cpp:474-602) ---------------------------------------------------------------------------
   const double t_col = now_s();
@@ -252,13 +311,13 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
     std::memset(&fo, 0, sizeof(fo));
     fo.flags = PCP_OUT_SKIP_CANDIDATES;
     fo.pixel_index = have_mask ? pix.data() : nullptr;
-    check(ctx, pcp_submit_frame(ctx, kf->pose, A.T_camera_lidar_optimized, h_img[sb], (size_t)W * 3, have_mask ? h_msk[sb] : nullptr, (size_t)W,
+    check(ctx, pcp_submit_frame(ctx, kf->pose, T_opt, h_img[sb], (size_t)W * 3, have_mask ? h_msk[sb] : nullptr, (size_t)W,
                                 have_mask ? &fo : nullptr),
           "pcp_submit_frame");
     if (!have_mask) continue;
     // generateSegmentMap (cpp:769-816) for this keyframe + the concatenated world cloud (cpp:533-551)
     host::M4f w2c, c2w;
-    host::pose_matrices(kf->pose, A.T_camera_lidar_optimized, w2c, c2w);
+    host::pose_matrices(kf->pose, T_opt, w2c, c2w);
     frame_mask_cloud.clear();
     for (size_t i = 0; i < N; i++) {
       const int32_t p = pix[i];

@@ -21,7 +21,21 @@ int main() {
   try {
     vlcal::ViewCulling vc(proj, 320, 240, vlcal::ViewCullingParams());
     auto kept = vc.cull(pts, pcp::Isometry3d::Identity());
-    std::printf("facade ok: kept %zu of %zu\n", kept.size(), pts.size());
+    // vlcal::VisualCameraCalibration over one NIDCost (visual_camera_calibration.cpp:49-84)
+    pcp_params p;
+    pcp_default_params(&p);
+    p.image_width = p.cull_width = 320;
+    p.image_height = p.cull_height = 240;
+    pcp::Colorizer col(proj, p, 0);
+    std::vector<double> img(320 * 240);
+    for (size_t i = 0; i < img.size(); i++) img[i] = (double)((i % 320) / 2 % 160) / 160.0;
+    for (size_t i = 0; i < kept.size(); i++) kept[i].intensity = (float)(i % 97) / 97.0f;
+    std::vector<std::shared_ptr<vlcal::NIDCost>> costs{std::make_shared<vlcal::NIDCost>(col, img.data(), 320, 240, kept)};
+    vlcal::VisualCameraCalibration calib(costs);
+    const pcp::Isometry3d T = calib.calibrate(pcp::Isometry3d::Identity());
+    const pcp_calib_summary& cs = calib.summary();
+    if (!(cs.final_cost <= cs.initial_cost) || !(T.m[15] == 1.0)) { std::printf("calibrate: %f -> %f\n", cs.initial_cost, cs.final_cost); return 14; }
+    std::printf("facade ok: kept %zu of %zu, calibrate %d outer / %d evaluations\n", kept.size(), pts.size(), cs.outer_iterations, cs.cost_evaluations);
     return kept.empty() ? 11 : 0;
   } catch (const std::runtime_error& e) {
     std::printf("facade error: %s\n", e.what());
