@@ -139,11 +139,20 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
 void* pcp_accumulators_device(pcp_ctx* ctx);
 int pcp_reset_accumulators(pcp_ctx* ctx);
 
-/* Multi-GPU: frames are sharded across ranks; one NCCL all-reduce (sum, u32) of the accumulators at the end.
- * pcp_nccl_unique_id fills 128 bytes on rank 0; every rank then calls pcp_nccl_init with the same bytes. */
+/* Multi-GPU: frames are sharded across ranks (every rank holds the whole cloud); one exchange of the accumulators at the end.
+ * pcp_nccl_unique_id fills 128 bytes on rank 0; every rank then calls pcp_nccl_init with the same bytes.
+ * pcp_allreduce, called by every rank after its last frame, leaves the accumulators of the WHOLE job on every rank:
+ *   PCP_ACCUM_SUM   ncclAllReduce(u32, sum) — bit-identical for any rank count;
+ *   PCP_ACCUM_TOP5  ncclAllGather of the slot lists + a merge kernel (top_m best of the union, same order as the insertion);
+ *                   identical to the single-rank run when frames carry global numbers (pcp_set_frame_numbering);
+ *   mask accumulators {hits, max}: all-reduced with sum and max (allocated on ranks that saw no mask). */
 int pcp_nccl_unique_id(uint8_t id128[128]);
 int pcp_nccl_init(pcp_ctx* ctx, const uint8_t id128[128], int rank, int nranks);
 int pcp_allreduce(pcp_ctx* ctx);
+/* Global keyframe numbers of the frames this context submits (the tie-break of equal TOP5 scores, cpp:604-631 keeps the earlier
+ * observation): the next frame is number `next`, then next + stride, ...  Rank r of G with interleaved sharding: (r, G).
+ * Default (0, 1).  The numbering restarts from `next` at pcp_set_cloud / pcp_reset_accumulators. */
+int pcp_set_frame_numbering(pcp_ctx* ctx, int next, int stride);
 
 /* smoothColors + removePointsWithNoColor inputs (cpp:604-631, hpp:238-252): rgb_out = N x 3 (r,g,b) u8,
  * count_out = N u32 observations (either may be NULL).  SUM mode: integer mean; TOP5: the reference's top-M

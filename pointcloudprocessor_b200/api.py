@@ -264,6 +264,10 @@ class Colorizer:
         buf = (C.c_uint8 * 128).from_buffer_copy(id128)
         self._check(self._L.pcp_nccl_init(self._h, buf, rank, nranks), "pcp_nccl_init")
 
+    def set_frame_numbering(self, next_index: int, stride: int = 1):
+        """Global keyframe numbers of the frames submitted from now on (rank r of G, interleaved sharding: (r, G))."""
+        self._check(self._L.pcp_set_frame_numbering(self._h, int(next_index), int(stride)), "pcp_set_frame_numbering")
+
     def allreduce(self):
         self._check(self._L.pcp_allreduce(self._h), "pcp_allreduce")
 

@@ -270,7 +270,7 @@ int pcp_reset_accumulators(pcp_ctx* ctx) {
     CU(cudaMemsetAsync(ctx->d_top_score, 0, sizeof(float) * n1 * ctx->prm.top_m, ctx->stream));
     CU(cudaMemsetAsync(ctx->d_top_rgbf, 0, sizeof(uint32_t) * n1 * ctx->prm.top_m, ctx->stream));
   }
-  ctx->frame_index = 0;
+  ctx->frame_index = ctx->frame_first;
   return PCP_OK;
 }
 

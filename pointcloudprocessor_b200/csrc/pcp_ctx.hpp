@@ -69,6 +69,8 @@ struct pcp_ctx {
 
   int scan_grid = 148 * 4, resolve_grid = 148 * 4;
   int frame_index = 0;
+  int frame_first = 0;            // value frame_index restarts from at pcp_set_cloud / pcp_reset_accumulators
+  int frame_stride = 1;           // pcp_set_frame_numbering: global keyframe number of the next frame and its increment
   bool use_smz = false;   // shared-memory early-z scan kernel (PCP_SMZ=1 enables it when the grid fits)
   bool prefilter = true;  // FP32 pre-filter of the scan kernel (PCP_NO_PREFILTER=1 disables it: exact path for every point)
   uint64_t launches = 0;

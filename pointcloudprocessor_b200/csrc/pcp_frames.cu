@@ -209,7 +209,7 @@ static int submit_device(pcp_ctx* ctx, const double pose7[7], const double* T_op
   rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true,
                  out && !(out->flags & PCP_OUT_SKIP_CANDIDATES), img_ready, img_free);
   if (rc != PCP_OK) return rc;
-  ctx->frame_index++;
+  ctx->frame_index += ctx->frame_stride;
   if (out) return fetch_outputs(ctx, out);
   return PCP_OK;
 }
