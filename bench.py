@@ -189,6 +189,7 @@ def run_native(args):
         if world == 1 and args.gpus > 1:
             raise SystemExit("bench.py: --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
     torch.cuda.set_device(local)
+    numa = _bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -395,7 +396,8 @@ def run_native(args):
             "config": {"workload": f"{args.workload}: {n} points x {f} frames @ {W}x{H} per GPU, colorize + z-buffer culling, SUM accumulators",
                        "points": n, "frames_per_gpu": f, "image": [W, H], "parallelism": f"frames sharded x{world}, cloud replicated, NCCL allreduce u32",
                        "frames_in_flight": int(prm.frames_in_flight),
-                       "l2": "inputs larger than L2 (cloud 16 B x N + one image per frame); no explicit flush"},
+                       "l2": "inputs larger than L2 (cloud 16 B x N + one image per frame); no explicit flush",
+                       "host_affinity": (f"rank bound to the {numa} CPUs NVML lists for its GPU" if numa else "unbound")},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "colours_equal_device_path": e2e_matches_device},
@@ -409,6 +411,24 @@ def run_native(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def _bind_to_gpu_numa_node(local):
+    """Multi-rank runs: pin this process to the CPUs NVML names as closest to its GPU BEFORE the pinned staging buffers are
+    allocated, so that first touch puts them on the GPU's NUMA node (the end-to-end path is bound by the host link).  Best effort."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
 
 
 def main():

@@ -11,7 +11,8 @@
 #include "pcp_internal.cuh"
 
 struct pcp_ctx {
-  static constexpr int kSlots = 3;  // image staging slots: copy of frame f+1 overlaps the kernels of frame f
+  static constexpr int kSlots = 16;  // image staging slots (allocated on first use): uploads run up to 16 frames ahead of the kernels,
+                                    // so the host link stays busy while the cloud is still being pre-binned
 
   int device = 0;
   int sm_count = 148;

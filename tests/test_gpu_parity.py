@@ -125,6 +125,34 @@ def test_c1_shape_fast_variant(oracle, built_lib):
         assert np.array_equal(gc.accumulators()[0], oc.accumulators()[0])
 
 
+def test_c3_shape_masks_top5_and_nid_refinement(oracle, built_lib):
+    """BASELINE config 3: the C1 shape plus segmentation masks, the reference's TOP5 accumulation, and the NID cost / pose refinement over
+    the culled cloud of a keyframe (values against the oracle's doubles; the refinement must not leave the gate and must not raise the cost)."""
+    from pointcloudprocessor_b200 import api, synth
+    W, H = 1280, 720
+    sc = make_scene(1_000_000, 3, W, H, masks=True)
+    _run_pair(oracle, sc, accum="top5", masks=True)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    w2c, _ = oracle.pose_matrices(sc["poses"][0])
+    pts_cam = oracle.transform(sc["cloud"], w2c)
+    keep = oracle.view_culling(cam_o, W, H, pts_cam)
+    culled = np.concatenate([pts_cam[keep], sc["cloud"][keep, 3:]], 1)
+    grey = synth.grey_plane(sc["images"][0])
+    cands = synth.make_nid_candidates(4)
+    with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(W, H))) as gc:
+        cost = api.NIDCost(gc, grey, culled, 16)
+        val, grad, ok = cost.evaluate_with_gradient(cands)
+        for b in range(len(cands)):
+            rok, rv, rg = oracle.nid_grad(cam_o, grey, culled, cands[b])
+            assert ok[b] == rok and abs(val[b] - rv) <= 1e-5 * abs(rv)
+            assert np.abs(grad[b] - rg).max() <= 1e-5 * np.abs(rg).max()
+        T, s = api.calibrate([cost])
+        ident = np.array([0, 0, 0, 1, 0, 0, 0.0])
+        assert s["final_cost"] <= s["initial_cost"] and s["initial_cost"] == pytest.approx(oracle.nid(cam_o, grey, culled, ident)[0], rel=1e-5)
+        assert np.linalg.norm(T[:3, 3]) <= 0.2 * s["outer_iterations"] + 1e-9
+        cost.close()
+
+
 def test_reference_cull_size(oracle, built_lib):
     # the reference passes a hard-coded 4096x3000 to ViewCulling whatever the image (cpp:525)
     _run_pair(oracle, make_scene(100_000, 2, 640, 480), cull_size=(4096, 3000))
