@@ -111,6 +111,10 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   }
   const size_t cells = (size_t)ctx->Wc * ctx->Hc;
   if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
+  if ((e = cudaMalloc(&ctx->d_zprev, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zprev", e);
+  // index words 0xffffffff: no seed point before a slot's first frame
+  if ((e = cudaMemset(ctx->d_zgrid, 0xff, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMemset zgrid", e);
+  if ((e = cudaMemset(ctx->d_zprev, 0xff, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMemset zprev", e);
   if ((e = cudaMalloc(&ctx->d_counters, pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
   if ((e = cudaMemset(ctx->d_counters, 0, pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMemset counters", e);
   if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
@@ -120,6 +124,8 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   {
     const char* e_np = std::getenv("PCP_NO_PREFILTER");
     ctx->prefilter = !(e_np && e_np[0] == '1');
+    const char* e_sd = std::getenv("PCP_NO_SEED");
+    ctx->use_seed = !(e_sd && e_sd[0] == '1');
     const char* e_ns = std::getenv("PCP_SMZ");  // opt-in: measured 75-81 us vs 74.5 us for scan_kernel at C2
     ctx->use_smz = (e_ns && e_ns[0] == '1');
   }
@@ -145,6 +151,7 @@ void pcp_destroy(pcp_ctx* ctx) {
     if (ctx->ev_free[i]) cudaEventDestroy(ctx->ev_free[i]);
   }
   if (ctx->d_zgrid) cudaFree(ctx->d_zgrid);
+  if (ctx->d_zprev) cudaFree(ctx->d_zprev);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   if (ctx->d_total) cudaFree(ctx->d_total);

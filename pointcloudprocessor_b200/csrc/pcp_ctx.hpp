@@ -64,6 +64,7 @@ struct pcp_ctx {
   int last_slot = 0;              // slot of the last submitted frame
   cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
   unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys
+  unsigned long long* d_zprev = nullptr;       // kMaxFlight x Wc*Hc: the final z-grid of the slot's previous frame (seed points)
   pcp::FrameCounters* d_counters = nullptr;    // kMaxFlight entries
   pcp::FrameCounters* h_counters = nullptr;  // pinned
   uint32_t* d_total = nullptr;
@@ -73,6 +74,7 @@ struct pcp_ctx {
   int frame_first = 0;            // value frame_index restarts from at pcp_set_cloud / pcp_reset_accumulators
   int frame_stride = 1;           // pcp_set_frame_numbering: global keyframe number of the next frame and its increment
   bool use_smz = false;   // shared-memory early-z scan kernel (PCP_SMZ=1 enables it when the grid fits)
+  bool use_seed = true;   // last frame's nearest points go through the exact path first (PCP_NO_SEED=1 disables it)
   bool prefilter = true;  // FP32 pre-filter of the scan kernel (PCP_NO_PREFILTER=1 disables it: exact path for every point)
   uint64_t launches = 0;
   std::string err;

@@ -109,7 +109,8 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   unsigned long long* zg = ctx->d_zgrid + (size_t)si * (cells ? cells : 1);
   FrameCounters* ctr = ctx->d_counters + si;
   Record* recs = ctx->d_records + (size_t)si * ((ctx->n ? ctx->n : 1) + 64);
-  launch_zgrid_init(zg, cells, ctr, st);  // this slot's z-grid and counters (overlaps the other slots' kernels)
+  unsigned long long* zp = (ctx->use_seed && ctx->d_zprev) ? ctx->d_zprev + (size_t)si * (cells ? cells : 1) : nullptr;
+  launch_zgrid_init(zg, zp, cells, ctr, st);  // this slot's z-grid and counters (overlaps the other slots' kernels)
   if (pe) CU(cudaEventRecord(pe[1], st));
   ScanArgs sa;
   std::memset(&sa, 0, sizeof(sa));
@@ -120,6 +121,8 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.n_chunks = ctx->n_chunks;
   sa.chunk_mul = ctx->chunk_mul;
   sa.zgrid = zg;
+  sa.zprev = zp;
+  sa.cells = cells;
   sa.records = recs;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;

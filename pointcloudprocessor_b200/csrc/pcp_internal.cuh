@@ -76,6 +76,8 @@ struct ScanArgs {
   uint32_t n_chunks;                  // ceil(n / kChunk)
   uint32_t chunk_mul;                 // odd multiplier coprime with n_chunks: chunk visited at slot s is (s * chunk_mul) % n_chunks
   unsigned long long* zgrid;          // Wc*Hc packed keys
+  const unsigned long long* zprev;    // the slot's previous final z-grid (its index words name the seed points), or null
+  int cells;                          // Wc*Hc
   Record* records;
   FrameCounters* counters;
   uint32_t n;
@@ -101,7 +103,7 @@ struct ResolveArgs {
   int sample_mode;
 };
 
-void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s);
+void launch_zgrid_init(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters, cudaStream_t s);
 void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s);
 size_t scan_smz_smem_bytes(int cells);
 int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s);

@@ -26,15 +26,20 @@ static constexpr int kWarpsPerCta = kScanThreads / 32;
 static constexpr int kQueueCap = 64;  // per-warp record queue, flushed 32 at a time
 static constexpr int kCandCap = 32 * (PCP_UNROLL_CAP + 1); // per-warp candidate queue: < 32 left over + kUnroll x 32 new entries
 
-__global__ void zgrid_init_kernel(unsigned long long* zgrid, int cells, FrameCounters* counters) {
+// Also hands the grid the slot's previous frame ended with to `zprev`: its index words name that frame's nearest point of
+// every cell, which classify_kernel sends through the exact path before anything else (seed points).
+__global__ void zgrid_init_kernel(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < cells) zgrid[i] = kZInit;
+  if (i < cells) {
+    if (zprev) zprev[i] = zgrid[i];
+    zgrid[i] = kZInit;
+  }
   if (i < (int)(sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(counters)[i] = 0u;
 }
 
-void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s) {
+void launch_zgrid_init(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters, cudaStream_t s) {
   const int n = cells > 32 ? cells : 32;
-  zgrid_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(zgrid, cells, counters);
+  zgrid_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(zgrid, zprev, cells, counters);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -120,8 +125,8 @@ __device__ __forceinline__ unsigned int prefilter_b(const PreF& c, const PreA& a
 // ---------------------------------------------------------------------------------------------------------------------
 // Pass 1, stage B: the exact FP64 body for one camera-frame float point.  Returns true when a record must be emitted.
 // ---------------------------------------------------------------------------------------------------------------------
-// `idx` goes into the record (the accumulator slot: original index, or sorted position when pre-binned); `key_idx` is the
-// ORIGINAL point index and goes into the packed z-grid key, so that ties resolve identically whatever the storage order.
+// `idx` goes into the record (the accumulator slot: original index, or sorted position when pre-binned); `key_idx` goes
+// into the packed z-grid key (tie-break among equal fl32 distances; the position of the point in the device cloud).
 __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long long* __restrict__ zgrid, float x, float y, float z,
                                             uint32_t idx, uint32_t key_idx, Record& rec, bool& candidate, unsigned int* zs = nullptr) {
   candidate = false;
@@ -213,6 +218,25 @@ template <bool kCount>
 __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
   const int lane = threadIdx.x & 31;
   unsigned int ncand = 0;
+  // Seed points.  The point that was nearest in a cell of this slot's previous frame is very likely near the front of the
+  // new view too (consecutive keyframes are centimetres apart).  Sending those <= Wc*Hc points through the exact path FIRST
+  // is nothing but a different processing order (the final grid is min over all in-grid candidates whatever the order,
+  // SURVEY.md 3.4), but the scan kernel then starts against minima that are already close to final: more chunks fail the
+  // distance test without being loaded and fewer points reach the FP64 stage or leave a record.  Seeds emit no record and
+  // are not counted; the scan kernel meets the same points again in their chunks.  A stale or foreign index (first frame
+  // of a slot, new cloud) names some other point of the cloud, which is just as valid.
+  if (a.zprev && fp.depth_culling) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < a.cells; c += gridDim.x * blockDim.x) {
+      const uint32_t pos = (uint32_t)__ldg(a.zprev + c);  // index word = position in the (sorted) cloud
+      if (pos >= a.n) continue;
+      const float4 p = __ldg(a.cloud + pos);
+      float x = p.x, y = p.y, z = p.z;
+      if (fp.use_w2c) transform_point(fp.w2c, p.x, p.y, p.z, x, y, z);
+      Record rec;
+      bool cand;
+      (void)exact_point(fp, a.zgrid, x, y, z, pos, pos, rec, cand);
+    }
+  }
   for (unsigned long long s0 = (unsigned long long)(blockIdx.x * blockDim.x + threadIdx.x - lane); s0 < a.n_chunks;
        s0 += (unsigned long long)gridDim.x * blockDim.x) {
     const unsigned long long slot = s0 + lane;
@@ -407,7 +431,10 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
     if (lane < cnt) {
       const float4 c = q1[n1 + lane];
       const uint32_t slot = __float_as_uint(c.w);
-      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, __ldg(a.perm + slot), rec, cand);
+      // key index = sorted position: no look-up of the original index (a scattered 4-byte read per point, DRAM latency on the
+      // critical path of this stage); ties on fl32(dist) then go to the smallest sorted position, which is as deterministic,
+      // and nothing ever reads the index word of the grid except the seed pass (the reference never reads its index_map)
+      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, slot, rec, cand);
     }
     if (kCount) ncand += cand ? 1u : 0u;
     const unsigned int m = __ballot_sync(0xffffffffu, emit);
@@ -480,10 +507,10 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
   // the whole map, like a shuffled cloud at chunk granularity).  CTA c owns items c, c + G, c + 2G, ...; its warps take them
   // one at a time from a shared-memory ticket (chunk costs differ by orders of magnitude: skipped whole vs full of FP64
   // work).  The next item's list entry is loaded and its points are pulled into L2 while the current one is processed.
+  const uint32_t n_active = a.counters->n_active_blocks;
   __shared__ unsigned int s_ticket;
   if (threadIdx.x == 0) s_ticket = 0u;
   __syncthreads();
-  const uint32_t n_active = a.counters->n_active_blocks;
   auto take = [&]() -> uint32_t {
     uint32_t j = 0;
     if (lane == 0) j = atomicAdd(&s_ticket, 1u);
