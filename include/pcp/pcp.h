@@ -123,6 +123,15 @@ int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T
 int pcp_cull(pcp_ctx* ctx, const float* w2c16, const double* T16, int32_t* idx_out, size_t* m_out);
 /* Loop body of viewCullingAndSaveFilteredPcds (cpp:178-224): pose -> w2c -> cull. */
 int pcp_cull_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, int32_t* idx_out, size_t* m_out);
+/* Distance / 3-D point masks of one frame: generate_distance_masks of scripts/genNormAndDistanceMask.py:233-265 applied to the
+ * frame's culled cloud (the filtered_pcd/<ts>_beforeNID.pcd it reads, cpp:213-217), without the file round trip.  Every culled
+ * point whose truncated projection lies inside the image writes its range ||p|| (double norm of the float camera-frame point,
+ * stored as float32) and its camera-frame coordinates at that pixel; points later in the file overwrite earlier ones, i.e. the
+ * largest point index wins.  distance_out: H*W floats, 0 where no point landed; xyz_out: H*W*3 floats or NULL; index_out
+ * (extension): H*W int32 original index of the winning point, -1 where empty, or NULL; n_filled_out: pixels written, or NULL.
+ * Host buffers; synchronous; does not touch the accumulators or the frame numbering. */
+int pcp_splat_masks_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, float* distance_out, float* xyz_out,
+                         int32_t* index_out, size_t* n_filled_out);
 /* Host helper: the float matrices the reference derives from a pose (cpp:495-519). */
 int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[16], float c2w16[16]);
 

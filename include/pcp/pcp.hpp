@@ -91,6 +91,20 @@ class Colorizer {
     return p;  // cull size stays the reference's hard-coded 4096x3000 (cpp:525) unless the caller changes it
   }
 
+  // generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265) of the frame's culled cloud: H x W ranges (0 = empty),
+  // optional H x W x 3 camera-frame points and H x W winning point indices (-1 = empty).  Returns the number of pixels written.
+  size_t distance_masks(const Pose& pose, std::vector<float>& distance_mask, std::vector<float>* points_3d_mask = nullptr,
+                        std::vector<int32_t>* index_mask = nullptr, const Isometry3d* T_opt = nullptr) {
+    const double p7[7] = {pose.x, pose.y, pose.z, pose.qw, pose.qx, pose.qy, pose.qz};
+    const size_t npix = (size_t)params_.image_width * params_.image_height;
+    distance_mask.resize(npix);
+    if (points_3d_mask) points_3d_mask->resize(3 * npix);
+    if (index_mask) index_mask->resize(npix);
+    size_t filled = 0;
+    check(pcp_splat_masks_pose(ctx_, p7, T_opt ? T_opt->data() : nullptr, distance_mask.data(), points_3d_mask ? points_3d_mask->data() : nullptr,
+                               index_mask ? index_mask->data() : nullptr, &filled), ctx_, "pcp_splat_masks_pose");
+    return filled;
+  }
   pcp_ctx* handle() const { return ctx_; }
   size_t size() const { return pcp_num_points(ctx_); }
 

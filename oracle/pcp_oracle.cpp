@@ -692,6 +692,38 @@ void orc_color_pixels(const orc_camera* c, int W, int H, const float* pts_cam, s
   for (size_t i = 0; i < n; i++) pix[i] = color_pixel(cam, W, H, pts_cam[3 * i], pts_cam[3 * i + 1], pts_cam[3 * i + 2]);
 }
 
+// generate_distance_masks of scripts/genNormAndDistanceMask.py:233-265 on one frame's culled cloud (the file
+// filtered_pcd/<ts>_beforeNID.pcd the script reads, written at src/PointCloudProcessor.cpp:213-217): the points are visited
+// in file order (:252), projected with cv2.projectPoints(rvec = tvec = 0) (:245-246; the same plumb_bob model as
+// pinhole.hpp:12-51, pinned against cv2 in tests/test_oracle_cpu.py), truncated by astype(int) (:247), and every point
+// inside the mask (:258) overwrites distance_mask[y, x] = np.linalg.norm(xyz) stored as float32 (:251,:254,:259) and
+// points_3d_mask[y, x] = xyz (:260): the LAST point of the file that lands on a pixel wins.
+// Decisions: [M1] open3d holds the file's float32 coordinates as float64, so the norm is sqrt((x*x + y*y) + z*z) in double,
+// rounded once to float32 (numpy's dot may fuse the sum on some builds: third-party detail, invisible after the float32
+// rounding except on exact ties); [M2] astype(int) of a non-finite / out-of-range value is INT64_MIN in numpy: rejected.
+// index_out (extension): file position of the winning point, -1 where the pixel is empty.
+void orc_distance_masks(const orc_camera* c, int W, int H, const float* pts_cam /*n x 3*/, size_t n, float* dist /*H x W*/,
+                        float* xyz /*H x W x 3 or null*/, int32_t* index_out /*H x W or null*/) {
+  const Camera cam = to_cam(c);
+  const size_t np_ = (size_t)W * H;
+  for (size_t p = 0; p < np_; p++) dist[p] = 0.0f;                                     // np.zeros_like  :251
+  if (xyz) for (size_t p = 0; p < 3 * np_; p++) xyz[p] = 0.0f;                         // :252
+  if (index_out) for (size_t p = 0; p < np_; p++) index_out[p] = -1;
+  for (size_t i = 0; i < n; i++) {                                                     // zip(points_2d, points)  :255
+    const double X = pts_cam[3 * i], Y = pts_cam[3 * i + 1], Z = pts_cam[3 * i + 2];
+    double ud, vd;
+    project(cam, X, Y, Z, ud, vd);
+    if (!std::isfinite(ud) || !std::isfinite(vd)) continue;                            // [M2]
+    if (!(ud > -2147483648.0 && ud < 2147483648.0 && vd > -2147483648.0 && vd < 2147483648.0)) continue;
+    const long x = (long)ud, y = (long)vd;                                             // astype(int)  :247
+    if (!(0 <= x && x < W && 0 <= y && y < H)) continue;                               // :258
+    const size_t p = (size_t)y * W + (size_t)x;
+    dist[p] = (float)std::sqrt((X * X + Y * Y) + Z * Z);                               // :256,:259  [M1]
+    if (xyz) { xyz[3 * p] = pts_cam[3 * i]; xyz[3 * p + 1] = pts_cam[3 * i + 1]; xyz[3 * p + 2] = pts_cam[3 * i + 2]; }  // :260
+    if (index_out) index_out[p] = (int32_t)i;
+  }
+}
+
 void orc_scores(const float* pts_cam, size_t n, const double* pose7, float* out3 /*n x 3: orient, dist, final*/) {
   for (size_t i = 0; i < n; i++) {
     const float o = orientation_score(pts_cam[3 * i], pts_cam[3 * i + 1], pts_cam[3 * i + 2], pose7);

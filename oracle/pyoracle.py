@@ -106,6 +106,16 @@ def color_pixels(cam, W, H, pts_cam):
     return pix
 
 
+def distance_masks(cam, W, H, pts_cam):
+    """generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265) -> (distance HxW f32, xyz HxWx3 f32, index HxW i32)."""
+    pts_cam = np.ascontiguousarray(np.asarray(pts_cam, np.float32)[:, :3])
+    dist = np.empty((H, W), np.float32)
+    xyz = np.empty((H, W, 3), np.float32)
+    idx = np.empty((H, W), np.int32)
+    lib().orc_distance_masks(C.byref(cam), W, H, _p(pts_cam), C.c_size_t(pts_cam.shape[0]), _p(dist), _p(xyz), _p(idx))
+    return dist, xyz, idx
+
+
 def scores(pts_cam, pose7):
     pts_cam = np.ascontiguousarray(pts_cam, np.float32)
     pose7 = np.ascontiguousarray(pose7, np.float64)

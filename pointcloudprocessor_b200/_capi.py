@@ -63,7 +63,7 @@ SYMBOLS = [
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
-    "pcp_bfgs_default_options", "pcp_se3_bfgs", "pcp_calib_default_params", "pcp_calibrate", "pcp_set_frame_numbering",
+    "pcp_bfgs_default_options", "pcp_se3_bfgs", "pcp_calib_default_params", "pcp_calibrate", "pcp_set_frame_numbering", "pcp_splat_masks_pose",
 ]
 class BfgsOptions(C.Structure):
     _fields_ = [
@@ -127,6 +127,7 @@ def load():
     L.pcp_cull.argtypes = [vp, vp, vp, vp, C.POINTER(sz)]
     L.pcp_cull_pose.argtypes = [vp, vp, vp, vp, C.POINTER(sz)]
     L.pcp_pose_matrices.argtypes = [vp, vp, vp, vp]
+    L.pcp_splat_masks_pose.argtypes = [vp, vp, vp, vp, vp, vp, C.POINTER(sz)]
     L.pcp_get_accumulators.argtypes = [vp, vp, vp, vp]
     L.pcp_accumulators_device.argtypes = [vp]
     L.pcp_accumulators_device.restype = vp

@@ -222,6 +222,19 @@ class Colorizer:
         self._check(rc, "pcp_cull_pose")
         return idx[: m.value].copy()
 
+    def splat_masks_pose(self, pose7, T_opt=None, want_xyz=True, want_index=True):
+        """generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265) of the frame's culled cloud:
+        -> (distance HxW f32, xyz HxWx3 f32 | None, index HxW i32 | None, pixels filled)."""
+        pose = np.ascontiguousarray(pose7, np.float64)
+        W, H = int(self.params.image_width), int(self.params.image_height)
+        dist = np.empty((H, W), np.float32)
+        xyz = np.empty((H, W, 3), np.float32) if want_xyz else None
+        idx = np.empty((H, W), np.int32) if want_index else None
+        m = C.c_size_t(0)
+        rc = self._L.pcp_splat_masks_pose(self._h, _ptr(pose), _ptr(self._mat16(T_opt)), _ptr(dist), _ptr(xyz), _ptr(idx), C.byref(m))
+        self._check(rc, "pcp_splat_masks_pose")
+        return dist, xyz, idx, int(m.value)
+
     # -- accumulators / finalize -----------------------------------------------------------------------
     def accumulators(self):
         acc = np.empty((self.n, 4), np.uint32)

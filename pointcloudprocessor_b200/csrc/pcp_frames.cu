@@ -308,6 +308,45 @@ int pcp_cull_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, in
   return cull_common(ctx, fp, idx_out, m_out);
 }
 
+int pcp_splat_masks_pose(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, float* distance_out, float* xyz_out, int32_t* index_out,
+                         size_t* n_filled_out) {
+  if (!ctx) return PCP_EINVAL;
+  if (!distance_out) { ctx->fail("pcp_splat_masks_pose: null distance_out"); return PCP_EINVAL; }
+  CU(cudaSetDevice(ctx->device));
+  FrameParams fp;
+  int rc = frame_params_for_pose(ctx, pose7, T_opt16, fp);
+  if (rc != PCP_OK) return rc;
+  // the frame's culled cloud and its pixels: pass 1 + resolve without image (nothing is accumulated)
+  rc = run_frame(ctx, fp, nullptr, 0, nullptr, 0, false, true, false, false);
+  if (rc != PCP_OK) return rc;
+  CU(ctx->join());
+  const size_t npix = (size_t)fp.imgW * fp.imgH;
+  // one allocation: winner keys | distance | xyz | index | counter
+  const size_t off_dist = npix * 8, off_xyz = off_dist + npix * 4, off_idx = off_xyz + npix * 12, off_cnt = off_idx + npix * 4;
+  uint8_t* d = nullptr;
+  CU(cudaMalloc(&d, off_cnt + 16));
+  cudaError_t e = cudaMemsetAsync(d, 0, off_dist, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d + off_cnt, 0, 16, ctx->stream);
+  if (e == cudaSuccess) {
+    launch_splat(ctx->d_pix, ctx->d_perm, (uint32_t)ctx->n, ctx->d_cloud, fp, reinterpret_cast<unsigned long long*>(d),
+                 reinterpret_cast<float*>(d + off_dist), xyz_out ? reinterpret_cast<float*>(d + off_xyz) : nullptr,
+                 index_out ? reinterpret_cast<int32_t*>(d + off_idx) : nullptr, reinterpret_cast<unsigned int*>(d + off_cnt), ctx->sm_count,
+                 ctx->stream);
+    ctx->launches += ctx->n ? 2 : 1;
+    e = cudaGetLastError();
+  }
+  unsigned int filled = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(distance_out, d + off_dist, npix * 4, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && xyz_out) e = cudaMemcpyAsync(xyz_out, d + off_xyz, npix * 12, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && index_out) e = cudaMemcpyAsync(index_out, d + off_idx, npix * 4, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&filled, d + off_cnt, sizeof(filled), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) { ctx->fail("pcp_splat_masks_pose: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+  if (n_filled_out) *n_filled_out = filled;
+  return PCP_OK;
+}
+
 int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint32_t* mask_max) {
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));

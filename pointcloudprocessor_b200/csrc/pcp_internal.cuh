@@ -123,5 +123,8 @@ void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,
                          uint32_t* d_total, cudaStream_t s);
 size_t compact_scratch_words(uint32_t n);
+// distance / 3-D point masks of a frame from the resolve kernel's pixel indices (pcp_splat.cu); `winner` = imgW*imgH zeroed u64 words
+void launch_splat(const int32_t* pix, const uint32_t* perm, uint32_t n, const float4* cloud, const FrameParams& fp, unsigned long long* winner,
+                  float* dist, float* xyz, int32_t* index, unsigned int* n_filled, int sm_count, cudaStream_t s);
 
 }  // namespace pcp

@@ -358,3 +358,35 @@ def test_hsv_adjust_in_pipeline(oracle, built_lib):
             oc.frame(pose, oracle.hsv_roundtrip(raw[i]))
         assert np.array_equal(gc.accumulators()[0], oc.accumulators()[0])
         assert oc.accumulators()[0][:, 3].sum() > 0
+
+
+@pytest.mark.parametrize("shape", [(60_000, 640, 480, True), (20_000, 160, 120, False), (200_000, 320, 240, True)])
+def test_distance_masks_equal_oracle(oracle, built_lib, shape):
+    """pcp_splat_masks_pose (scripts/genNormAndDistanceMask.py:233-265): distance, 3-D point and winner-index masks of
+    the frame's culled cloud, bit for bit the oracle's file-order loop (the last point on a pixel wins = the largest index)."""
+    from pointcloudprocessor_b200 import api
+    n, W, H, depth_culling = shape
+    sc = make_scene(n, 3, W, H)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam_g = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    p = api.default_params(image_size=(W, H))
+    p.enable_depth_buffer_culling = 1 if depth_culling else 0
+    with api.Colorizer(cam_g, p) as gc:
+        gc.set_cloud(sc["cloud"])
+        for pose in sc["poses"]:
+            w2c, _ = oracle.pose_matrices(pose)
+            pts = oracle.transform(sc["cloud"][:, :3], w2c)
+            keep = oracle.view_culling(cam_o, W, H, pts, depth_culling=depth_culling)
+            d_o, xyz_o, idx_o = oracle.distance_masks(cam_o, W, H, pts[keep])
+            idx_o = np.where(idx_o >= 0, keep[np.maximum(idx_o, 0)], -1).astype(np.int32)  # file position -> map index
+            d_g, xyz_g, idx_g, filled = gc.splat_masks_pose(pose)
+            assert filled == int((idx_o >= 0).sum()) and filled > 50
+            assert np.array_equal(idx_g, idx_o)
+            assert np.array_equal(d_g.view(np.uint32), d_o.view(np.uint32))
+            assert np.array_equal(xyz_g.view(np.uint32), xyz_o.view(np.uint32))
+            # optional outputs may be left out
+            d2, x2, i2, f2 = gc.splat_masks_pose(pose, want_xyz=False, want_index=False)
+            assert x2 is None and i2 is None and f2 == filled and np.array_equal(d2, d_g)
+        # the masks are read-only products: nothing was accumulated
+        acc, _, _ = gc.accumulators()
+        assert acc.sum() == 0

@@ -404,3 +404,57 @@ def test_nid_jet_gradient_matches_finite_differences(oracle):
         a[k] += 1e-6; b[k] -= 1e-6
         fd[k] = (oracle.nid(cam, img, pts, a)[0] - oracle.nid(cam, img, pts, b)[0]) / 2e-6
     assert np.abs(g - fd).max() <= 1e-5 * np.abs(g).max()
+
+
+@pytest.mark.parametrize("shape", [(60_000, 640, 480, True, 700), (20_000, 160, 120, False, 2500)])
+def test_distance_masks_vs_script_transcription(oracle, shape):
+    """orc_distance_masks against a literal transcription of generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265):
+    cv2.projectPoints with zero rvec / tvec, astype(int), the zip loop in file order (last point on a pixel wins), np.linalg.norm
+    stored into a float32 mask.  The pixel a point lands on must agree everywhere cv2's projection is not within 1e-6 of an
+    integer boundary (cv2 evaluates the same model with its own operation order); ranges to one float32 ulp."""
+    cv2 = pytest.importorskip("cv2")
+    n, W, H, depth_culling, least = shape  # without depth culling many points share a pixel: the overwrite order is exercised
+    sc = make_scene(n, 2, W, H)
+    cam = oracle.camera(sc["intr"], sc["dist"])
+    w2c, _ = oracle.pose_matrices(sc["poses"][1])
+    pts = oracle.transform(sc["cloud"][:, :3], w2c)
+    keep = oracle.view_culling(cam, W, H, pts, depth_culling=depth_culling)
+    pts = pts[keep]
+    assert len(pts) > least
+    dist, xyz, idx = oracle.distance_masks(cam, W, H, pts)
+    # --- the script, line by line -----------------------------------------------------------------------------------
+    points = pts.astype(np.float64)  # np.asarray(pcd.points)
+    K = np.array([[sc["intr"][0], 0, sc["intr"][2]], [0, sc["intr"][1], sc["intr"][3]], [0, 0, 1]], np.float64)
+    p2d, _ = cv2.projectPoints(points, rvec=np.zeros((3, 1)), tvec=np.zeros((3, 1)), cameraMatrix=K, distCoeffs=np.array(sc["dist"], np.float64))
+    uv = p2d.squeeze()
+    points_2d = uv.astype(int)
+    distance_mask = np.zeros((H, W), np.float32)
+    points_3d_mask = np.zeros((H, W, 3), np.float32)
+    winner = np.full((H, W), -1, np.int32)
+    for i, (point, p) in enumerate(zip(points_2d, points)):
+        x, y = point
+        if 0 <= x < W and 0 <= y < H:
+            distance_mask[y, x] = np.linalg.norm(p)
+            points_3d_mask[y, x] = (p[0], p[1], p[2])
+            winner[y, x] = i
+    # ------------------------------------------------------------------------------------------------------------------
+    near_edge = np.abs(uv - np.round(uv)).min(axis=1) < 1e-6
+    assert not near_edge.any(), "scene has a projection on a pixel boundary: pick another seed"
+    assert (winner >= 0).sum() > 0.8 * least
+    if not depth_culling:
+        assert (winner >= 0).sum() < 0.98 * len(pts)  # collisions happened
+    assert np.array_equal(idx, winner)
+    assert np.array_equal(xyz, points_3d_mask)
+    assert np.allclose(dist, distance_mask, rtol=1.2e-7, atol=0)
+    assert (dist != distance_mask).mean() < 1e-3  # a fused dot product in numpy's BLAS can move a tie by one ulp, rarely
+
+
+def test_distance_masks_last_point_wins_and_rejects(oracle):
+    cam = oracle.camera([100.0, 100.0, 32.0, 24.0], [0, 0, 0, 0, 0])
+    pts = np.array([[0, 0, -1], [0, 0, 2], [0.001, 0, 2], [0, 0, 0], [1e9, 0, 1], [-0.005, -0.005, 1], [np.nan, 0, 1]], np.float32)
+    dist, xyz, idx = oracle.distance_masks(cam, 64, 48, pts)
+    assert idx[24, 32] == 2 and dist[24, 32] == np.float32(np.sqrt(np.float64(np.float32(0.001)) ** 2 + 4.0))  # later point overwrites
+    # point 0 lies behind the camera and lands on (32, 24) through x/z, y/z as in cv2.projectPoints: the script has no z gate (a
+    # culled cloud never holds such a point, view_culling.cpp:80); here it is simply overwritten by the later points
+    assert idx[23, 31] == 5  # u = 31.5, v = 23.5
+    assert (idx >= 0).sum() == 2 and dist[idx < 0].max() == 0.0
