@@ -402,9 +402,19 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_kernel(const
 #define PCP_A1W 2
 #endif
 static constexpr int kA1 = PCP_A1W;
+#ifndef PCP_ENT_DIST
+#define PCP_ENT_DIST 8
+#endif
+static constexpr int kEntDist = PCP_ENT_DIST;  // prefetch distance in tickets (one round of the CTA's warps)
+static constexpr int kEntCap = 320;  // list entries staged per CTA (PCP_ENT_SMEM): 5 KB; C2 has <= 264 per CTA
 static constexpr int kQ0Cap = 32 * (kGroups + 1);  // < 32 left over + one chunk
 static constexpr int kQ1Cap = 32 * (kA1 + 1);      // < 32 left over + one A1 batch
-static constexpr size_t kBinnedSmem = (size_t)kWarpsPerCta * ((kQ0Cap + kQ1Cap) * sizeof(float4) + kQueueCap * sizeof(Record));
+#ifndef PCP_RQ_FLUSH
+#define PCP_RQ_FLUSH 32
+#endif
+static constexpr int kRqFlush = PCP_RQ_FLUSH;   // records per global atomicAdd on n_records (same-address atomics serialise in L2)
+static constexpr int kRqCap = kRqFlush + 32;    // < kRqFlush left over + one stage-B batch
+static constexpr size_t kBinnedSmem = (size_t)kWarpsPerCta * ((kQ0Cap + kQ1Cap) * sizeof(float4) + kRqCap * sizeof(Record));
 
 template <bool kCount>
 __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
@@ -414,7 +424,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
   const unsigned int lt_mask = (1u << lane) - 1u;
   float4* q0 = reinterpret_cast<float4*>(binned_smem) + (size_t)warp * kQ0Cap;
   float4* q1 = reinterpret_cast<float4*>(binned_smem) + (size_t)kWarpsPerCta * kQ0Cap + (size_t)warp * kQ1Cap;
-  Record* rq = reinterpret_cast<Record*>(binned_smem + (size_t)kWarpsPerCta * (kQ0Cap + kQ1Cap) * sizeof(float4)) + (size_t)warp * kQueueCap;
+  Record* rq = reinterpret_cast<Record*>(binned_smem + (size_t)kWarpsPerCta * (kQ0Cap + kQ1Cap) * sizeof(float4)) + (size_t)warp * kRqCap;
   int n0 = 0, n1 = 0, rn = 0;
   unsigned int ncand = 0;
 #ifdef PCP_STATS
@@ -442,15 +452,15 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
       if (emit) rq[rn + __popc(m & lt_mask)] = rec;
       rn += __popc(m);
       __syncwarp();
-      if (rn >= 32) {
+      if (rn >= kRqFlush) {
         unsigned int base = 0;
-        if (lane == 0) base = atomicAdd(&a.counters->n_records, 32u);
+        if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)kRqFlush);
         base = __shfl_sync(0xffffffffu, base, 0);
-        rn -= 32;
+        rn -= kRqFlush;
         const uint4* src = reinterpret_cast<const uint4*>(rq + rn);
         uint4* dst = reinterpret_cast<uint4*>(a.records + base);
-        dst[lane] = src[lane];
-        dst[lane + 32] = src[lane + 32];
+#pragma unroll
+        for (int t = 0; t < kRqFlush / 16; t++) dst[lane + 32 * t] = src[lane + 32 * t];
         __syncwarp();
       }
     }
@@ -509,6 +519,22 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
   // work).  The next item's list entry is loaded and its points are pulled into L2 while the current one is processed.
   const uint32_t n_active = a.counters->n_active_blocks;
   __shared__ unsigned int s_ticket;
+#ifndef PCP_NO_ENT_SMEM
+  // The CTA's share of the list (items c, c + G, ...) is staged in shared memory by one bulk load, so that taking an item is
+  // one shared-memory atomic plus one broadcast LDS (it was ATOMS -> LDG of the entry from L2 -> prefetch address, a chain of
+  // ~1 us per chunk on the warp's critical path).  The points of item j + 8 are pulled into L2 by the warp that takes item j:
+  // the prefetch distance is one round of the CTA's warps (~2 us at C2, DRAM latency is < 1 us) and costs no registers.
+  __shared__ uint4 s_ent[kEntCap];
+  const uint32_t n_mine = n_active > blockIdx.x ? (n_active - blockIdx.x + gridDim.x - 1u) / gridDim.x : 0u;
+  for (uint32_t j = threadIdx.x; j < n_mine && j < (uint32_t)kEntCap; j += blockDim.x) s_ent[j] = __ldg(a.active + blockIdx.x + gridDim.x * j);
+  if (threadIdx.x == 0) s_ticket = 0u;
+  __syncthreads();
+  auto entry = [&](uint32_t j) -> uint4 { return j < (uint32_t)kEntCap ? s_ent[j] : __ldg(a.active + blockIdx.x + gridDim.x * j); };
+  auto pull = [&](uint32_t j) {
+    if (j < n_mine && lane < kChunk / 8) prefetch_l2(a.cloud + (size_t)entry(j).x * kChunk + lane * 8);  // the chunk in lines of 128 B
+  };
+  for (uint32_t j = (uint32_t)warp; j < (uint32_t)kEntDist; j += kWarpsPerCta) pull(j);
+#else
   if (threadIdx.x == 0) s_ticket = 0u;
   __syncthreads();
   auto take = [&]() -> uint32_t {
@@ -517,6 +543,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
     j = __shfl_sync(0xffffffffu, j, 0);
     return blockIdx.x + gridDim.x * j;
   };
+#endif
   const uint4 kNoEnt = make_uint4(0u, 0u, 0u, 0u);
   // one lane per cell of the entry's rectangle: (minimum + tol)^2 rounded up, as bits (0 for the other lanes / no rectangle)
   auto rect_bits = [&](const uint4& e) -> unsigned int {
@@ -533,6 +560,16 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
   // The next item's list entry is loaded (and its points pulled into L2) while the current one is processed.  Deeper
   // pipelining (z-grid cells of the next item, record blocks reserved ahead, stage A1's z word reused by stage B) was
   // measured slower: the kernel sits at its 64-register budget and every extra live value costs more than the latency it hides.
+#ifndef PCP_NO_ENT_SMEM
+  (void)kNoEnt;
+  for (;;) {
+    uint32_t tj = 0;
+    if (lane == 0) tj = atomicAdd(&s_ticket, 1u);
+    tj = __shfl_sync(0xffffffffu, tj, 0);
+    if (tj >= n_mine) break;
+    pull(tj + (uint32_t)kEntDist);
+    const uint4 ent = entry(tj);
+#else
   uint32_t item = take();
   uint4 ent = item < n_active ? __ldg(a.active + item) : kNoEnt;
   while (item < n_active) {
@@ -542,8 +579,9 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
       nent = __ldg(a.active + nitem);
       if (lane < kChunk / 8) prefetch_l2(a.cloud + (size_t)nent.x * kChunk + lane * 8);  // the chunk in lines of 128 B
     }
-    const unsigned int zb = rect_bits(ent);
+#endif
     const uint32_t base = ent.x * kChunk;
+    const unsigned int zb = rect_bits(ent);
     float lim2 = __int_as_float(0x7f800000);  // +inf: nothing is dropped by the distance test
     bool skip = false;
     if (ent.y != 0u) {
@@ -584,8 +622,10 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
 #pragma unroll 1
       while (n0 >= 32) stage_a1();
     }
+#ifdef PCP_NO_ENT_SMEM
     item = nitem;
     ent = nent;
+#endif
   }
 
   __syncwarp();
@@ -602,7 +642,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
     unsigned int base = 0;
     if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)rn);
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (lane < rn) a.records[base + lane] = rq[lane];
+    for (int i = lane; i < rn; i += 32) a.records[base + i] = rq[i];
   }
   if (kCount) {
     for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
