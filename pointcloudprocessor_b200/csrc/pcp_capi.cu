@@ -216,7 +216,7 @@ cudaError_t pcp_ctx::drain() {
 
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
-  F(d_cloud); F(d_perm); F(d_aabb); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
+  F(d_cloud); F(d_perm); F(d_inv); F(d_aabb); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
   F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt);
   if (d_prebin_scratch) { cudaFree(d_prebin_scratch); d_prebin_scratch = nullptr; prebin_scratch_bytes = 0; }
   out_points = 0;
@@ -229,6 +229,7 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   const bool on = ctx->prm.prebin != 0 && !(e_np && e_np[0] == '1') && n > 0;
   if (!on) {
     if (ctx->d_perm) { cudaFree(ctx->d_perm); ctx->d_perm = nullptr; }
+    if (ctx->d_inv) { cudaFree(ctx->d_inv); ctx->d_inv = nullptr; }
     if (ctx->d_aabb) { cudaFree(ctx->d_aabb); ctx->d_aabb = nullptr; }
     if (ctx->d_active) { cudaFree(ctx->d_active); ctx->d_active = nullptr; }
     ctx->n_chunks = 0;
@@ -236,9 +237,11 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   }
   const uint32_t n_chunks = (uint32_t)((n + kChunk - 1) / kChunk);
   if (!ctx->d_perm) CU(cudaMalloc(&ctx->d_perm, sizeof(uint32_t) * n));
+  if (!ctx->d_inv) CU(cudaMalloc(&ctx->d_inv, sizeof(uint32_t) * n));
   if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
   if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks * pcp_ctx::kMaxFlight));
   CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, &ctx->d_prebin_scratch, &ctx->prebin_scratch_bytes, ctx->sm_count, ctx->stream));
+  launch_invert_perm(ctx->d_perm, (uint32_t)n, ctx->d_inv, ctx->stream);
   ctx->n_chunks = n_chunks;
   // odd multiplier coprime with n_chunks: the visiting order (slot * mul) % n_chunks is a permutation of the chunks
   auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };
@@ -246,7 +249,7 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   for (uint32_t cand : {40503u, 7919u, 7907u, 6007u, 5003u, 4001u, 3001u, 2003u, 1009u, 509u, 251u, 127u, 61u, 31u, 13u, 7u, 3u})
     if (cand < n_chunks && gcd(cand, n_chunks) == 1) { mul = cand; break; }
   ctx->chunk_mul = mul;
-  ctx->launches += 5;
+  ctx->launches += 6;
   return PCP_OK;
 }
 

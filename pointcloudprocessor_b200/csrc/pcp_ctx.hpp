@@ -31,6 +31,7 @@ struct pcp_ctx {
   size_t n = 0;
   float4* d_cloud = nullptr;      // N x 16 B  {x,y,z,intensity}
   uint32_t* d_perm = nullptr;     // N x 4 B   sorted position -> original index (pre-binned mode; null otherwise)
+  uint32_t* d_inv = nullptr;      // N x 4 B   original index -> sorted position (pre-binned mode): finalize gathers through it
   float4* d_aabb = nullptr;       // 2 float4 per chunk of 128 sorted points (pre-binned mode)
   uint4* d_active = nullptr;      // per-frame list of chunks to scan + their cell rectangle / distance bound (pre-binned mode)
   uint32_t n_chunks = 0, chunk_mul = 1;

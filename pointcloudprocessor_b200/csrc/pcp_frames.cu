@@ -420,7 +420,7 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
   CU(ctx->join());
-  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm ? ctx->d_inv : nullptr, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
   else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
   ctx->launches++;
   CU(cudaGetLastError());
@@ -443,7 +443,7 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
   }
   uint8_t* d_rgb = rgb_out ? ctx->d_out_rgb : nullptr;
   uint32_t* d_cnt = count_out ? ctx->d_out_cnt : nullptr;
-  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm, (uint32_t)n, d_rgb, d_cnt, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm ? ctx->d_inv : nullptr, (uint32_t)n, d_rgb, d_cnt, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
   else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
   ctx->launches++;
   if (rgb_out) CU(cudaMemcpyAsync(rgb_out, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream));

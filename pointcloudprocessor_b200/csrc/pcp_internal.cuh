@@ -109,7 +109,7 @@ size_t scan_smz_smem_bytes(int cells);
 int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
-void launch_finalize_sum(const uint4* acc, const uint32_t* perm, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
+void launch_finalize_sum(const uint4* acc, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
 // generateColorMap's 8-bit HSV round trip (pcp_image.cu); src and dst may alias
@@ -118,6 +118,7 @@ void launch_hsv_roundtrip(const uint8_t* src, size_t spitch, uint8_t* dst, size_
 // pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)
 cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, void** scratch, size_t* scratch_bytes, int sm_count,
                          cudaStream_t s);
+void launch_invert_perm(const uint32_t* perm, uint32_t n, uint32_t* inv, cudaStream_t s);
 void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s);
 // ascending index list from a visibility bitmask; returns through d_total the number of set bits
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,

@@ -160,4 +160,15 @@ cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* 
   return cudaGetLastError();
 }
 
+// inv[perm[j]] = j: lets the finalize kernels walk the outputs in the caller's order (coalesced writes) and gather the per-point
+// state, instead of scattering 3-byte colours through perm.
+__global__ void invert_perm_kernel(const uint32_t* __restrict__ perm, uint32_t n, uint32_t* __restrict__ inv) {
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) inv[perm[j]] = j;
+}
+void launch_invert_perm(const uint32_t* perm, uint32_t n, uint32_t* inv, cudaStream_t s) {
+  if (n == 0) return;
+  const uint32_t blocks = (n + 255u) / 256u;
+  invert_perm_kernel<<<blocks < 148u * 16u ? blocks : 148u * 16u, 256, 0, s>>>(perm, n, inv);
+}
+
 }  // namespace pcp
