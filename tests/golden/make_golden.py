@@ -13,6 +13,7 @@ so that a generator drift is reported as such, plus the outputs:
                    SUM colours and TOP5 colours
   edge_*.npz     : hand-made edge-case cloud (stored explicitly) with its outputs
   nid_*.npz      : NID values, ok flags and joint histograms for a set of candidate poses
+  distmask_*.npz : per frame the filled pixels of the distance / 3-D point masks with winner index, range and point
 """
 from __future__ import annotations
 
@@ -122,8 +123,33 @@ def nid_case():
     print("nid:", np.array(vals)[:4], "ok", np.array(oks).astype(int))
 
 
+def distmask_case():
+    """generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265) on the culled cloud of each frame; stored sparse."""
+    n, f, W, H = 60_000, 3, 640, 480
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(f)
+    cam = O.camera(intr, dist)
+    out = {"n": n, "f": f, "W": W, "H": H, "sha_cloud": sha(cloud), "sha_poses": sha(poses)}
+    for i in range(f):
+        w2c, _ = O.pose_matrices(poses[i])
+        pts = O.transform(cloud[:, :3], w2c)
+        keep = O.view_culling(cam, W, H, pts)
+        d, xyz, idx = O.distance_masks(cam, W, H, pts[keep])
+        pix = np.flatnonzero(idx.reshape(-1) >= 0).astype(np.int32)
+        out[f"pix_{i}"] = pix                                            # filled pixels, ascending
+        out[f"index_{i}"] = keep[idx.reshape(-1)[pix]].astype(np.int32)  # winning point, as map index
+        out[f"dist_{i}"] = d.reshape(-1)[pix]
+        out[f"xyz_{i}"] = xyz.reshape(-1, 3)[pix]
+        print("distmask frame", i, "culled", len(keep), "pixels filled", len(pix))
+    np.savez_compressed(os.path.join(HERE, "distmask_tiny.npz"), **out)
+
+
 if __name__ == "__main__":
     O.build()
+    if "--only-distmask" in sys.argv:
+        distmask_case()
+        sys.exit(0)
     colorize_case("tiny", 20_000, 3, 320, 240)
     colorize_case("tiny_masks", 20_000, 3, 320, 240, masks=True)
     T = np.eye(4)
@@ -134,3 +160,4 @@ if __name__ == "__main__":
     colorize_case("refcull", 30_000, 2, 640, 480, cull_size=(4096, 3000))
     edge_case()
     nid_case()
+    distmask_case()

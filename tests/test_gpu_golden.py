@@ -120,3 +120,22 @@ def test_nid_golden(built_lib):
             if ok[b]:
                 assert abs(got[b] - g["nid"][b]) <= 1e-5 * abs(g["nid"][b])  # north_star: relative NID error <= 1e-5
         cost.close()
+
+
+def test_distance_masks_golden(built_lib):
+    """pcp_splat_masks_pose against tests/golden/distmask_tiny.npz (scripts/genNormAndDistanceMask.py:233-265), bit for bit."""
+    from pointcloudprocessor_b200 import api, synth
+    from test_oracle_cpu import _dense_distmask
+    g = np.load(os.path.join(GOLD, "distmask_tiny.npz"))
+    n, f, W, H = int(g["n"]), int(g["f"]), int(g["W"]), int(g["H"])
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(f)
+    assert sha(cloud) == str(g["sha_cloud"]) and sha(poses) == str(g["sha_poses"])
+    with api.Colorizer(api.create_camera("pinhole", intr, dist), api.default_params(image_size=(W, H))) as gc:
+        gc.set_cloud(cloud)
+        for i in range(f):
+            d, xyz, idx, filled = gc.splat_masks_pose(poses[i])
+            gd, gx, gi = _dense_distmask(g, i)
+            assert filled == len(g[f"pix_{i}"]) and np.array_equal(idx, gi)
+            assert np.array_equal(d.view(np.uint32), gd.view(np.uint32)) and np.array_equal(xyz.view(np.uint32), gx.view(np.uint32))

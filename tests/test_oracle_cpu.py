@@ -458,3 +458,30 @@ def test_distance_masks_last_point_wins_and_rejects(oracle):
     # culled cloud never holds such a point, view_culling.cpp:80); here it is simply overwritten by the later points
     assert idx[23, 31] == 5  # u = 31.5, v = 23.5
     assert (idx >= 0).sum() == 2 and dist[idx < 0].max() == 0.0
+
+
+def _dense_distmask(g, i):
+    W, H = int(g["W"]), int(g["H"])
+    d = np.zeros(W * H, np.float32); xyz = np.zeros((W * H, 3), np.float32); idx = np.full(W * H, -1, np.int32)
+    pix = g[f"pix_{i}"]
+    d[pix] = g[f"dist_{i}"]; xyz[pix] = g[f"xyz_{i}"]; idx[pix] = g[f"index_{i}"]
+    return d.reshape(H, W), xyz.reshape(H, W, 3), idx.reshape(H, W)
+
+
+def test_oracle_distmask_golden(oracle):
+    from pointcloudprocessor_b200 import synth
+    g = np.load(os.path.join(GOLD, "distmask_tiny.npz"))
+    n, f, W, H = int(g["n"]), int(g["f"]), int(g["W"]), int(g["H"])
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(f)
+    assert sha(cloud) == str(g["sha_cloud"]) and sha(poses) == str(g["sha_poses"])
+    cam = oracle.camera(intr, dist)
+    for i in range(f):
+        w2c, _ = oracle.pose_matrices(poses[i])
+        pts = oracle.transform(cloud[:, :3], w2c)
+        keep = oracle.view_culling(cam, W, H, pts)
+        d, xyz, idx = oracle.distance_masks(cam, W, H, pts[keep])
+        gd, gx, gi = _dense_distmask(g, i)
+        assert np.array_equal(np.where(idx >= 0, keep[np.maximum(idx, 0)], -1), gi)
+        assert np.array_equal(d.view(np.uint32), gd.view(np.uint32)) and np.array_equal(xyz.view(np.uint32), gx.view(np.uint32))
