@@ -62,15 +62,40 @@ __device__ __forceinline__ void bspline(double s, double b[4]) {
 }
 
 __global__ void __launch_bounds__(kNidThreads) nid_hist_kernel(const NidArgs a) {
+#ifndef PCP_NID_DOUBLE_ATOMICS
+  // Joint-histogram weights accumulate in shared memory as 2^-31 fixed point in (hi, lo) 32-bit pairs: a shared-memory
+  // atomicAdd(double) is an ATOMS.CAST.SPIN loop on this architecture (so is a 64-bit integer add), and the 32 lanes of a
+  // warp collide on the 256 bins all the time; ATOMS.ADD on 32 bits is native.  `lo` takes the weight, the lane whose add
+  // wraps carries one into `hi`: exact, and independent of the order of the adds.  A flush holds <= 16 taps whose weights sum
+  // to <= 1, so it fits in 32 bits; the quantisation is 2^-32 per flush against sums normalised by the point count
+  // (relative error of the NID ~1e-9; the tolerance is 1e-5).
+  __shared__ unsigned int sh_lo[kNidSmemDoubles], sh_hi[kNidSmemDoubles];
+#else
   __shared__ double sh[kNidSmemDoubles];
+#endif
   __shared__ unsigned int sh_pts[8 * 32];
   const int bins = a.bins, nb2 = bins * bins;
   const int pose = blockIdx.y;
+#ifndef PCP_NID_DOUBLE_ATOMICS
+  for (int i = threadIdx.x; i < a.copies * nb2; i += blockDim.x) { sh_lo[i] = 0u; sh_hi[i] = 0u; }
+#else
   for (int i = threadIdx.x; i < a.copies * nb2; i += blockDim.x) sh[i] = 0.0;
+#endif
   for (int i = threadIdx.x; i < 8 * 32; i += blockDim.x) sh_pts[i] = 0u;
   __syncthreads();
   const int warp = threadIdx.x >> 5;
+#ifndef PCP_NID_DOUBLE_ATOMICS
+  unsigned int* mylo = sh_lo + (warp % a.copies) * nb2;
+  unsigned int* myhi = sh_hi + (warp % a.copies) * nb2;
+  auto flush = [&](int key, double acc) {
+    const unsigned int q = __double2uint_rn(acc * 2147483648.0);
+    const unsigned int old = atomicAdd(&mylo[key], q);
+    if (old + q < old) atomicAdd(&myhi[key], 1u);
+  };
+#else
   double* myh = sh + (warp % a.copies) * nb2;
+  auto flush = [&](int key, double acc) { atomicAdd(&myh[key], acc); };
+#endif
   unsigned int* myp = sh_pts + warp * 32;
 
   const double* q = a.se3 + (size_t)pose * 7;
@@ -109,20 +134,26 @@ __global__ void __launch_bounds__(kNidThreads) nid_hist_kernel(const NidArgs a) 
         const int bi = __ldg(a.binimg + (size_t)y * a.W + x);      // :87-88
         const double w = bx[ia] * by[jb];                          // :86
         if (bi != cur) {
-          if (cur >= 0) atomicAdd(&myh[cur * bins + bin_p], acc);  // :89
+          if (cur >= 0) flush(cur * bins + bin_p, acc);  // :89
           cur = bi;
           acc = 0.0;
         }
         acc += w;
       }
     }
-    if (cur >= 0) atomicAdd(&myh[cur * bins + bin_p], acc);
+    if (cur >= 0) flush(cur * bins + bin_p, acc);
   }
   __syncthreads();
   double* gh = a.hist + (size_t)pose * (nb2 + bins);
   for (int i = threadIdx.x; i < nb2; i += blockDim.x) {
+#ifndef PCP_NID_DOUBLE_ATOMICS
+    unsigned long long t = 0ull;
+    for (int c = 0; c < a.copies; c++) t += ((unsigned long long)sh_hi[c * nb2 + i] << 32) | (unsigned long long)sh_lo[c * nb2 + i];
+    const double s = (double)t * (1.0 / 2147483648.0);
+#else
     double s = 0.0;
     for (int c = 0; c < a.copies; c++) s += sh[c * nb2 + i];
+#endif
     if (s != 0.0) atomicAdd(&gh[i], s);
   }
   for (int i = threadIdx.x; i < bins; i += blockDim.x) {

@@ -310,7 +310,9 @@ def test_nid_gradient(oracle, built_lib):
         cost = api.NIDCost(gc, grey, culled, 16)
         val, grad, ok = cost.evaluate_with_gradient(cands)
         val0, ok0 = cost(cands)
-        assert np.allclose(val, val0, rtol=1e-12, atol=0) and np.array_equal(ok, ok0)
+        # the value kernel accumulates its histogram in 2^-31 fixed point (order-independent), the gradient kernel in doubles: they
+        # agree far inside the 1e-5 of north_star, not to the last bits
+        assert np.allclose(val, val0, rtol=1e-8, atol=0) and np.array_equal(ok, ok0)
         for b in range(cands.shape[0]):
             rok, rv, rg = oracle.nid_grad(cam_o, grey, culled, cands[b])
             assert ok[b] == rok
