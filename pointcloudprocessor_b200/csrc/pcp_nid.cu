@@ -518,8 +518,8 @@ int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_
   return PCP_OK;
 }
 
-int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, double* grad_out, uint8_t* ok_out) {
-  if (!nid || !se3 || B <= 0 || !nid_out || !grad_out) return PCP_EINVAL;
+// Enqueues the upload of the poses, the histogram / entropy kernels of one cost on the context's stream; no host synchronisation.
+static int nid_grad_enqueue(pcp_nid* nid, const double* se3, int B) {
   pcp_ctx* ctx = nid->ctx;
   CUN(cudaSetDevice(ctx->device));
   const int nb2 = nid->bins * nid->bins, nb = 8 * nb2 + nid->bins;
@@ -543,7 +543,9 @@ int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, d
   a.cam = CamD{c.fx, c.fy, c.cx, c.cy, c.dist[0], c.dist[1], c.dist[2], c.dist[3], c.dist[4]};
   const size_t smem = sizeof(double) * 8 * nb2;
   CUN(cudaFuncSetAttribute(nid_hist_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_pose = (int)((nid->m + 2047) / 2048);
+  // a line-search evaluation is ONE pose over one keyframe's culled cloud (~4e4 points): down to one point per thread so that it
+  // still spreads over the GPU (2048 points per CTA left 22 CTAs on 148 SMs)
+  int per_pose = (int)((nid->m + kNidThreads - 1) / kNidThreads);
   const int want = (ctx->sm_count * 4 + B - 1) / B;
   if (per_pose > want) per_pose = want;
   if (per_pose < 1) per_pose = 1;
@@ -557,6 +559,14 @@ int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, d
   }
   nid_entropy_grad_kernel<<<B, 32, 0, s>>>(nid->d_hist_g, nid->bins, B, nid->d_out_g);
   ctx->launches++;
+  CUN(cudaGetLastError());
+  return PCP_OK;
+}
+
+// Reads the B x {NID, ok, 7 partials} of an enqueued evaluation back (synchronises the stream).
+static int nid_grad_collect(pcp_nid* nid, int B, double* nid_out, double* grad_out, uint8_t* ok_out) {
+  pcp_ctx* ctx = nid->ctx;
+  cudaStream_t s = ctx->stream;
   std::vector<double> h(9 * (size_t)B);
   CUN(cudaMemcpyAsync(h.data(), nid->d_out_g, sizeof(double) * 9 * B, cudaMemcpyDeviceToHost, s));
   CUN(cudaStreamSynchronize(s));
@@ -567,6 +577,13 @@ int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, d
     for (int k = 0; k < 7; k++) grad_out[7 * (size_t)b + k] = h[9 * b + 2 + k];
   }
   return PCP_OK;
+}
+
+int pcp_nid_eval_grad(pcp_nid* nid, const double* se3, int B, double* nid_out, double* grad_out, uint8_t* ok_out) {
+  if (!nid || !se3 || B <= 0 || !nid_out || !grad_out) return PCP_EINVAL;
+  const int rc = nid_grad_enqueue(nid, se3, B);
+  if (rc != PCP_OK) return rc;
+  return nid_grad_collect(nid, B, nid_out, grad_out, ok_out);
 }
 
 // Pose gate of MultiNIDCost (visual_camera_calibration.cpp:99-105): delta = init^-1 * T.
@@ -617,8 +634,15 @@ int pcp_nid_eval_multi_grad(pcp_nid* const* costs, int n_costs, const double ini
     sum_out[b] = 0.0;
     for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] = 0.0;
   }
+  // every cost's kernels are enqueued before the first read-back: one host synchronisation per evaluation instead of one per keyframe
+  // (the costs own their pose / histogram / output buffers); the sums below keep the reference's order of the keyframes
   for (int c = 0; c < n_costs; c++) {
-    const int rc = pcp_nid_eval_grad(costs[c], se3, B, vals.data(), grads.data(), oks.data());
+    if (!costs[c]) return PCP_EINVAL;
+    const int rc = nid_grad_enqueue(costs[c], se3, B);
+    if (rc != PCP_OK) return rc;
+  }
+  for (int c = 0; c < n_costs; c++) {
+    const int rc = nid_grad_collect(costs[c], B, vals.data(), grads.data(), oks.data());
     if (rc != PCP_OK) return rc;
     for (int b = 0; b < B; b++) {
       sum_out[b] += vals[b];  // residuals[0] += residuals[i] on Jets: values and dual parts add (visual_camera_calibration.cpp:116-119)

@@ -1,0 +1,108 @@
+#!/usr/bin/env python
+"""BASELINE config C3 on one GPU: the C1 shape (1e6 points, 20 poses, 1280x720) plus segmentation masks, the reference's TOP5
+accumulation, and the NID pose refinement over the culled clouds of all keyframes (VisualCameraCalibration::calibrate).
+
+    python tools/bench_c3.py [--reps 5] > profiles/<name>.json
+
+Stages, each through the public calls with host buffers (wall clock between synchronisations):
+  cull      pcp_cull_pose per keyframe -> the per-keyframe culled clouds (viewCullingAndSaveFilteredPcds, cpp:178-224)
+  nid_build NIDCost objects: upload of the culled cloud and the grey plane, image binning
+  refine    pcp_calibrate: outer loop + BFGS, every cost / gradient evaluation on the device (MultiNIDCost over 20 keyframes)
+  colorize  20 x pcp_submit_frame with image + mask + the refined extrinsic, TOP5 accumulators, pcp_finalize
+The oracle checks ride along: the culled index lists and the mask / SUM-count accumulators of the colour pass are compared bit
+for bit with the oracle driven by the same extrinsic, and the initial NID cost within 1e-5 relative.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--frames", type=int, default=0)
+    args = ap.parse_args()
+    import torch
+    from oracle import pyoracle as O
+    from pointcloudprocessor_b200 import api, synth
+
+    n, f, W, H = synth.CONFIGS["C3"]
+    if args.frames:
+        f = args.frames
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(f)
+    images = [synth.make_image(i, W, H) for i in range(f)]
+    masks = [synth.make_mask(i, W, H) for i in range(f)]
+    greys = [synth.grey_plane(im) for im in images]
+    cam_o = O.camera(intr, dist)
+    sync = torch.cuda.synchronize
+    t = {k: [] for k in ("cull", "nid_build", "refine", "colorize")}
+    summary = None
+    p = api.default_params(image_size=(W, H), accum_mode=api.ACCUM_TOP5)
+    with api.Colorizer(api.create_camera("pinhole", intr, dist), p) as gc:
+        gc.set_cloud(cloud)
+        for rep in range(args.reps + 1):  # the first repetition is the warm-up
+            sync(); t0 = time.perf_counter()
+            idx = [gc.cull_pose(poses[i]) for i in range(f)]
+            sync(); t1 = time.perf_counter()
+            if rep == 0:  # host-side gather of the culled clouds (camera frame + intensity), as the reference's PCD round trip hands them over
+                w2cs = [O.pose_matrices(poses[i])[0] for i in range(f)]
+                pts = [np.ascontiguousarray(np.concatenate([O.transform(cloud[idx[i]], w2cs[i]), cloud[idx[i], 3:]], 1)) for i in range(f)]
+            sync(); t1b = time.perf_counter()
+            costs = [api.NIDCost(gc, greys[i], pts[i], 16) for i in range(f)]
+            sync(); t2 = time.perf_counter()
+            T, s = api.calibrate(costs)
+            sync(); t3 = time.perf_counter()
+            gc.reset_accumulators()
+            for i in range(f):
+                gc.submit_frame(poses[i], images[i], mask=masks[i], T_opt=T)
+            rgb, cnt = gc.finalize()
+            sync(); t4 = time.perf_counter()
+            for c in costs:
+                c.close()
+            if rep:
+                t["cull"].append(t1 - t0); t["nid_build"].append(t2 - t1b); t["refine"].append(t3 - t2); t["colorize"].append(t4 - t3)
+            summary = s
+        acc_g, mh_g, mm_g = gc.accumulators()
+    # oracle checks (outside the timed regions)
+    k = min(f, 3)
+    for i in range(k):
+        keep = O.view_culling(cam_o, W, H, O.transform(cloud, w2cs[i]))
+        assert np.array_equal(keep, idx[i]), f"culled cloud of keyframe {i} differs from the oracle"
+    ident = np.array([0, 0, 0, 1, 0, 0, 0.0])
+    ref0 = sum(O.nid(cam_o, greys[i], pts[i], ident)[0] for i in range(f))
+    assert abs(summary["initial_cost"] - ref0) <= 1e-5 * abs(ref0), (summary["initial_cost"], ref0)
+    oc = O.Colorizer(cam_o, W, H, cloud)
+    for i in range(f):
+        oc.frame(poses[i], images[i], mask=masks[i], T_opt=T)
+    acc_o, mh_o, mm_o = oc.accumulators()
+    assert np.array_equal(acc_g, acc_o) and np.array_equal(mh_g, mh_o) and np.array_equal(mm_g, mm_o)
+    med = {k: float(np.median(v)) for k, v in t.items()}
+    total = sum(med.values())
+    m_tot = int(sum(len(i) for i in idx))
+    out = {"metric": "c3_pipeline_seconds", "unit": "s", "higher_is_better": False, "value": total, "n_gpus": 1, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": f"C3: {n} points x {f} keyframes @ {W}x{H}, masks, TOP5 accumulators, NID refinement over all keyframes",
+                      "culled_points_total": m_tot, "reps": args.reps},
+           "stages_ms": {k: v * 1e3 for k, v in med.items()},
+           "point_frames_per_sec_colorize": n * f / med["colorize"], "point_frames_per_sec_cull": n * f / med["cull"],
+           "refine": {k: summary[k] for k in ("outer_iterations", "inner_iterations", "cost_evaluations", "initial_cost", "final_cost", "converged")
+                      if k in summary},
+           "parity": {"culled_lists_bit_exact": k, "mask_and_count_accumulators_bit_exact_frames": f, "initial_cost_rel_tol": 1e-5}}
+    if "cost_evaluations" in summary and summary["cost_evaluations"]:
+        out["refine"]["ms_per_cost_evaluation"] = med["refine"] * 1e3 / summary["cost_evaluations"]
+        out["refine"]["point_poses_per_s"] = m_tot * summary["cost_evaluations"] / med["refine"]
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
