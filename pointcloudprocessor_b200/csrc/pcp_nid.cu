@@ -492,8 +492,8 @@ int pcp_nid_eval(pcp_nid* nid, const double* se3, int B, double* nid_out, uint8_
   a.copies = kNidSmemDoubles / nb2 >= 8 ? 8 : (kNidSmemDoubles / nb2 >= 2 ? 2 : 1);
   const pcp_camera& c = ctx->cam;
   a.cam = CamD{c.fx, c.fy, c.cx, c.cy, c.dist[0], c.dist[1], c.dist[2], c.dist[3], c.dist[4]};
-  // enough CTAs per pose to fill the GPU, at least ~2048 points per CTA
-  int per_pose = (int)((nid->m + 2047) / 2048);
+  // enough CTAs per pose to fill the GPU: down to one point per thread when few poses are evaluated
+  int per_pose = (int)((nid->m + kNidThreads - 1) / kNidThreads);
   const int want = (ctx->sm_count * 4 + B - 1) / B;
   if (per_pose > want) per_pose = want;
   if (per_pose < 1) per_pose = 1;
