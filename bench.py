@@ -2,14 +2,20 @@
 """bench.py — point-frames/sec of the colorization hot path on N B200s (+ roofline, CPU baseline, end-to-end).
 
 A "step" is one pass of the hot path over one batch: every keyframe of the workload projected, culled, sampled and
-accumulated over the whole map cloud, the per-point accumulators all-reduced across ranks (N>1) and finalized.
+accumulated over the whole map cloud, the per-point accumulators exchanged across ranks (N>1) and finalized.
   value : whole-job point-frames/s with the cloud and all images already resident in HBM (CUDA events on the stream the
           kernels are launched on, max over ranks)
   e2e   : the same metric through the C ABI with HOST buffers: cloud upload, one image upload per frame and the
           read-back of the colours are inside the timed region
-  roofline / cpu_baseline : see DESIGN.md "Measurement"
+  roofline / cpu_baseline / parity : see DESIGN.md "Measurement"
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload C2]
+Workloads (BASELINE.json configs):
+  N = 1 : C2 (1e7 points x 200 frames @ 1920x1080), the configuration the metric is quoted on.
+  N > 1 : C4 (1e8 points x 2000 frames @ 1920x1080) with the FRAMES SHARDED over the ranks ("scaling": "strong"), as
+          BASELINE.json config 4 names it; `--scaling weak` keeps round 1's mode (C2 per rank).  In strong mode rank 0 also
+          times the WHOLE frame set on its own GPU (`single_gpu_same_workload`) so that the line carries its own N=1 point.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload C2] [--sample bilinear]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 """
 from __future__ import annotations
@@ -31,6 +37,7 @@ if ROOT not in sys.path:
 
 METRIC = "point_frames_per_sec_colorized"
 UNIT = "point-frames/s"
+FRAME_BLOCK = 25     # strong scaling: frames are dealt to the ranks in blocks of 25 consecutive keyframes (pose locality + balance)
 
 
 def _peaks():
@@ -43,14 +50,57 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def _workload(args):
+def _host_threads() -> int:
+    """All the host threads this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU
+    arm ignores it (it is the only thing running on the host when it runs) and passes this count to the oracle explicitly."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def _plan(args, world):
+    """Workload of this run: (name, points, frames of the whole job, W, H, scaling, image period)."""
     from pointcloudprocessor_b200 import synth
-    n, f, w, h = synth.CONFIGS[args.workload]
+    scaling = args.scaling or ("strong" if world > 1 else "single")
+    name = args.workload or ("C4" if scaling == "strong" else "C2")
+    n, f, w, h = synth.CONFIGS[name]
     if args.points:
         n = args.points
     if args.frames:
         f = args.frames
-    return n, f, w, h
+    if scaling == "weak":
+        total = f * world
+        period = f
+    else:
+        total = f
+        period = args.image_period or (40 if f > 400 else f)
+        period = min(period, f)
+    return dict(name=name, n=n, frames_total=total, frames_per_rank_weak=f, W=w, H=h, scaling=scaling, period=period)
+
+
+def _frames_of_rank(plan, rank, world):
+    """Global keyframe numbers of one rank."""
+    F = plan["frames_total"]
+    if plan["scaling"] == "weak":
+        f = plan["frames_per_rank_weak"]
+        return list(range(rank * f, (rank + 1) * f))
+    from pointcloudprocessor_b200.shard import frames_of_rank
+    return frames_of_rank(F, rank, world, "dealt", FRAME_BLOCK)
+
+
+def _config(plan, world, sample):
+    """The `config` object: identical in the native and the reference arm of the same launch."""
+    n, F, W, H = plan["n"], plan["frames_total"], plan["W"], plan["H"]
+    mode = {"single": "one GPU", "strong": f"frames sharded over {world} GPUs in blocks of {FRAME_BLOCK} (fixed total work)",
+            "weak": f"{plan['frames_per_rank_weak']} frames per GPU x {world} GPUs (work grows with N)"}[plan["scaling"]]
+    return {
+        "workload": f"{plan['name']}: {n} points x {F} frames @ {W}x{H}, colorize + z-buffer culling, SUM accumulators, {sample} sampling",
+        "points": n, "frames": F, "image": [W, H], "n_gpus": world,
+        "parallelism": f"{mode}; cloud replicated; accumulators exchanged once per step (NCCL over NVLink)" if world > 1 else mode,
+        "images": f"{plan['period']} distinct synthetic images, frame g reads image g mod {plan['period']}" if plan["period"] < F else "one synthetic image per frame",
+        "l2": "inputs larger than L2 (cloud 16 B x N + one image per frame); no explicit flush",
+    }
 
 
 class ClockSampler:
@@ -99,54 +149,50 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# reference arm: the CPU oracle (the reference itself cannot be compiled on this box) on all host cores
+# CPU legs: the oracle (the reference itself cannot be compiled on this box) on all host cores.
+# These two functions and the parity checks below are the only places where bench.py touches oracle/.
 # ---------------------------------------------------------------------------------------------------------------------
-def _cpu_sample(cloud, poses, images, W, H, intr, dist, threads, budget_s, max_frames):
-    """Times the OpenMP oracle on the first k frames of the workload (k sized from a one-frame calibration)."""
+def _oracle_accumulate(cloud, poses, images_of, frames, W, H, intr, dist, threads, bilinear):
+    """Runs the oracle over the given global frames; returns (seconds, u32 accumulators)."""
     from oracle import pyoracle as O
-    cam = O.camera(intr, dist)
-    oc = O.Colorizer(cam, W, H, cloud)
+    oc = O.Colorizer(O.camera(intr, dist), W, H, cloud, bilinear=bilinear)
     t0 = time.perf_counter()
-    oc.frame(poses[0], images[0], threads=threads)
-    t1 = time.perf_counter() - t0
-    k = int(max(1, min(max_frames, budget_s / max(t1, 1e-6))))
-    oc.close()
-    oc = O.Colorizer(cam, W, H, cloud)
-    t0 = time.perf_counter()
-    for i in range(k):
-        oc.frame(poses[i % len(poses)], images[i % len(images)], threads=threads)
-    oc.finalize_sum()
+    for g in frames:
+        oc.frame(poses[g], images_of(g), threads=threads)
     dt = time.perf_counter() - t0
     acc = oc.accumulators()[0]
     oc.close()
-    return k, dt, acc
+    return dt, acc
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
-        return 0
+        return 0  # the CPU arm is one process on the host's cores; the other ranks of a torchrun launch have nothing to do
     from oracle import pyoracle as O
     from pointcloudprocessor_b200 import synth
     O.build()
-    n, f, W, H = _workload(args)
+    plan = _plan(args, max(world, args.gpus))
+    n, F, W, H = plan["n"], plan["frames_total"], plan["W"], plan["H"]
     intr, dist = synth.make_camera(W, H)
     cloud = synth.make_cloud(n)
-    poses, _ = synth.make_poses(f)
-    threads = O.max_threads()
+    poses, _ = synth.make_poses(F)
+    threads = _host_threads()
+    bilinear = args.sample == "bilinear"
     cam = O.camera(intr, dist)
-    oc = O.Colorizer(cam, W, H, cloud)
+    oc = O.Colorizer(cam, W, H, cloud, bilinear=bilinear)
     img0 = synth.make_image(0, W, H)
     t0 = time.perf_counter()
     oc.frame(poses[0], img0, threads=threads)
     t1 = time.perf_counter() - t0
     total_steps = args.steps + args.warmup
-    k = int(max(1, min(f, (150.0 / total_steps) / max(t1, 1e-6))))  # whole run <= ~2.5 min
+    k = int(max(1, min(F, plan["period"], (150.0 / total_steps) / max(t1, 1e-6))))  # whole run <= ~2.5 min
     images = [synth.make_image(i, W, H) for i in range(k)]
     times = []
     for s in range(total_steps):
         oc.close()
-        oc = O.Colorizer(cam, W, H, cloud)
+        oc = O.Colorizer(cam, W, H, cloud, bilinear=bilinear)
         t0 = time.perf_counter()
         for i in range(k):
             oc.frame(poses[i], images[i], threads=threads)
@@ -157,15 +203,15 @@ def run_reference(args):
     oc.close()
     total = sum(times)
     value = n * k * len(times) / total
-    sample = f"first {k} of {f} frames over the full {n}-point cloud per step, OpenMP over points"
+    sample = f"first {k} of {F} frames over the full {n}-point cloud per step, OpenMP over points on {threads} threads"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {n} points x {f} frames @ {W}x{H}, colorize + z-buffer culling", "sample_frames_per_step": k},
+        "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak" if plan["scaling"] == "weak" else "strong" if world > 1 else "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": _config(plan, max(world, args.gpus), args.sample),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "sample_frames_per_step": k,
     }
     print(json.dumps(line))
     return 0
@@ -198,27 +244,49 @@ def run_native(args):
         if world > 1:
             dist.barrier()
 
-    n, f, W, H = _workload(args)
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    plan = _plan(args, world)
+    n, F, W, H, P = plan["n"], plan["frames_total"], plan["W"], plan["H"], plan["period"]
+    strong = plan["scaling"] == "strong"
     intr, dcoef = synth.make_camera(W, H)
     cam = api.create_camera("pinhole", intr, dcoef)
-    prm = api.default_params(image_size=(W, H))
-    # weak scaling: every rank colours its own f frames (a different stretch of the path) of the same replicated map
-    poses_all, _ = synth.make_poses(f * world)
-    poses = poses_all[rank * f:(rank + 1) * f]
+    sample_mode = api.SAMPLE_BILINEAR if args.sample == "bilinear" else api.SAMPLE_NEAREST
+    prm = api.default_params(image_size=(W, H), sample_mode=sample_mode)
+    poses_all, _ = synth.make_poses(F)
+    mine = _frames_of_rank(plan, rank, world)
+    f = len(mine)
     cloud_np = synth.make_cloud(n)
 
-    # pinned host staging (e2e) and device-resident copies (value)
+    # images: frame g reads image g mod P.  Rank 0 of a strong run also times the whole frame set alone, so it holds all P.
+    need = sorted({g % P for g in (range(F) if (strong and rank == 0) else mine)})
+    slot_of = {im: k for k, im in enumerate(need)}
+    img_bytes = H * W * 3
     h_cloud = torch.empty((n, 4), dtype=torch.float32).pin_memory()
     h_cloud.numpy()[...] = cloud_np
-    h_imgs = torch.empty((f, H, W, 3), dtype=torch.uint8).pin_memory()
-    for i in range(f):
-        synth.make_image(rank * f + i, W, H, out=h_imgs.numpy()[i])
+    h_imgs = torch.empty((len(need), H, W, 3), dtype=torch.uint8).pin_memory()
+    for k, im in enumerate(need):
+        synth.make_image(im, W, H, out=h_imgs.numpy()[k])
     h_rgb = torch.empty((n, 3), dtype=torch.uint8).pin_memory()
     h_cnt = torch.empty((n,), dtype=torch.int32).pin_memory()
     d_cloud = h_cloud.cuda()
     d_imgs = h_imgs.cuda()
     d_rgb = torch.empty((n, 3), dtype=torch.uint8, device="cuda")
     d_cnt = torch.empty((n,), dtype=torch.int32, device="cuda")
+
+    def dimg(g):
+        return d_imgs.data_ptr() + slot_of[g % P] * img_bytes
+
+    def himg(g):
+        return h_imgs.data_ptr() + slot_of[g % P] * img_bytes
+
+    def himg_np(g):
+        return h_imgs.numpy()[slot_of[g % P]]
 
     stream = torch.cuda.Stream()
     gc = api.Colorizer(cam, prm, device=local)
@@ -228,34 +296,46 @@ def run_native(args):
         ids = [gc.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         gc.nccl_init(ids[0], rank, world)
-    img_bytes = H * W * 3
-    img_ptrs = [d_imgs.data_ptr() + i * img_bytes for i in range(f)]
-    himg_ptrs = [h_imgs.data_ptr() + i * img_bytes for i in range(f)]
 
-    def step_device():
+    ex0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ex1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+
+    def step_device(frames=mine, timed_step=None):
         gc.reset_accumulators()
-        for i in range(f):
-            gc.submit_frame_device(poses[i], img_ptrs[i], W * 3)
+        for g in frames:
+            gc.submit_frame_device(poses_all[g], dimg(g), W * 3)
         if world > 1:
-            gc.allreduce()
-        gc.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+            if timed_step is not None:
+                gc.join()                      # the exchange interval starts when the last frame's kernels are done
+                ex0[timed_step].record(stream)
+            gc.exchange_finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+            if timed_step is not None:
+                ex1[timed_step].record(stream)
+        else:
+            gc.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
 
     def step_e2e():
         gc.set_cloud_ptr(h_cloud.data_ptr(), n)          # H2D cloud (resets the accumulators)
-        for i in range(f):
-            gc.submit_frame_ptr(poses[i], himg_ptrs[i], W * 3)  # H2D image per frame, overlapped on the copy stream
+        for g in mine:
+            gc.submit_frame_ptr(poses_all[g], himg(g), W * 3)  # H2D image per frame, overlapped on the copy stream
         if world > 1:
-            gc.allreduce()
-        gc.finalize_ptr(h_rgb.data_ptr(), h_cnt.data_ptr())  # D2H colours + observation counts (synchronises)
+            gc.exchange_finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+            if rank == 0:                                 # the job's output is read back once, by rank 0 (it writes the PCD)
+                with torch.cuda.stream(stream):           # the stream the exchange was enqueued on
+                    h_rgb.copy_(d_rgb, non_blocking=True)
+                    h_cnt.copy_(d_cnt, non_blocking=True)
+            gc.synchronize()
+        else:
+            gc.finalize_ptr(h_rgb.data_ptr(), h_cnt.data_ptr())  # D2H colours + observation counts (synchronises)
 
     # ---- statistics pass (untimed): visible fraction for the algorithmic-byte count --------------------------------
     gc.reset_accumulators()
     nvis = 0
-    stat_frames = min(f, 16)
-    for i in range(stat_frames):
-        r = gc.submit_frame_device(poses[i], img_ptrs[i], W * 3, want_counts=True)
+    stat_frames = mine[:16]
+    for g in stat_frames:
+        r = gc.submit_frame_device(poses_all[g], dimg(g), W * 3, want_counts=True)
         nvis += r["n_visible"]
-    f_vis = nvis / (stat_frames * n)
+    f_vis = nvis / (max(len(stat_frames), 1) * n)
 
     # ---- value: HBM-resident ------------------------------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):
@@ -270,8 +350,8 @@ def run_native(args):
     barrier()
     torch.cuda.synchronize()
     ev0.record(stream)
-    for _ in range(args.steps):
-        step_device()
+    for s in range(args.steps):
+        step_device(timed_step=s)
     ev1.record(stream)
     gc.synchronize()
     torch.cuda.synchronize()
@@ -281,14 +361,14 @@ def run_native(args):
     prof = gc.profile_read()
     gc.profile_enable(False)
     clocks = sampler.stop() if sampler else None
+    ms = max_over_ranks(ms)
+    value = n * F * args.steps / (ms * 1e-3)
+    exchange_ms = None
     if world > 1:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = n * f * world * args.steps / (ms * 1e-3)
+        exchange_ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in zip(ex0, ex1)) / args.steps)
 
     # ---- e2e: host buffers through the C ABI --------------------------------------------------------------------------
-    e2e_steps = max(1, min(args.steps, 10))
+    e2e_steps = max(1, min(args.steps, 10 if n <= 20_000_000 else 3))
     step_e2e()
     barrier()
     torch.cuda.synchronize()
@@ -297,112 +377,184 @@ def run_native(args):
         step_e2e()
     gc.synchronize()
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
-    e2e_value = n * f * world * e2e_steps / e2e_s
-    h2d = n * 16 + f * img_bytes
-    d2h = n * 3 + n * 4
-    rgb_e2e = h_rgb.numpy().copy()
-    rgb_dev = d_rgb.cpu().numpy()
-    e2e_matches_device = bool(np.array_equal(rgb_e2e, rgb_dev))
+    e2e_value = n * F * e2e_steps / e2e_s
+    h2d = world * n * 16 + F * img_bytes       # every rank uploads the cloud; every frame's image goes up once
+    d2h = n * 3 + n * 4                        # colours + counts, read back once (rank 0 when N > 1)
+    e2e_matches_device = None
+    if rank == 0:
+        rgb_e2e = h_rgb.numpy().copy()
+        e2e_matches_device = bool(np.array_equal(rgb_e2e, d_rgb.cpu().numpy()))
+
+    # ---- parity against the oracle (every N) --------------------------------------------------------------------------
+    # N = 1: the frames the cpu_baseline sample timed.  N > 1: the first --parity-frames frames of EVERY rank go through the
+    # sharded path and the exchange; rank 0 compares the exchanged accumulators with the oracle run over the same global frames.
+    cpu = None
+    parity = None
+    bilinear = args.sample == "bilinear"
+    threads = _host_threads()
+    if not args.no_cpu:
+        if world == 1:
+            from oracle import pyoracle as O
+            img0 = himg_np(mine[0])
+            oc = O.Colorizer(O.camera(intr, dcoef), W, H, cloud_np, bilinear=bilinear)
+            t0 = time.perf_counter()
+            oc.frame(poses_all[mine[0]], img0, threads=threads)
+            t1 = time.perf_counter() - t0
+            oc.close()
+            k = int(max(1, min(f, args.cpu_budget / max(t1, 1e-6))))
+            frames_chk = mine[:k]
+            dt, acc_o = _oracle_accumulate(cloud_np, poses_all, himg_np, frames_chk, W, H, intr, dcoef, threads, bilinear)
+            cpu = {"value": n * k / dt, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": f"first {k} of {F} frames over the full {n}-point cloud, OpenMP over points, {dt:.1f} s"}
+            gc.reset_accumulators()
+            for g in frames_chk:
+                gc.submit_frame_device(poses_all[g], dimg(g), W * 3)
+            acc_g, _, _ = gc.accumulators()
+            parity = {"frames": k, "accumulators_bit_exact_vs_oracle": bool(np.array_equal(acc_g, acc_o))}
+        else:
+            kp = max(1, args.parity_frames)
+            gc.reset_accumulators()
+            for g in mine[:kp]:
+                gc.submit_frame_device(poses_all[g], dimg(g), W * 3)
+            gc.allreduce()
+            gc.synchronize()
+            if rank == 0:
+                acc_g, _, _ = gc.accumulators()
+                frames_chk = sorted(g for r in range(world) for g in _frames_of_rank(plan, r, world)[:kp])
+                imgs_chk = {}
+
+                def img_of(g):
+                    im = g % P
+                    if im not in imgs_chk:
+                        imgs_chk[im] = himg_np(g) if im in slot_of else synth.make_image(im, W, H)
+                    return imgs_chk[im]
+
+                dt, acc_o = _oracle_accumulate(cloud_np, poses_all, img_of, frames_chk, W, H, intr, dcoef, threads, bilinear)
+                parity = {"frames": len(frames_chk), "frames_per_rank": kp, "ranks": world, "oracle_threads": threads, "oracle_seconds": round(dt, 1),
+                          "what": "exchanged accumulators of the first frames of every rank vs the oracle over the same global frames",
+                          "accumulators_bit_exact_vs_oracle": bool(np.array_equal(acc_g, acc_o))}
+            barrier()
+
+    # ---- strong scaling: the same frame set on ONE GPU (rank 0; the other ranks wait) ---------------------------------
+    single = None
+    if strong and world > 1:
+        if rank == 0:
+            g1 = api.Colorizer(cam, prm, device=local)
+            g1.set_stream(stream.cuda_stream)
+            g1.set_cloud_device(d_cloud.data_ptr(), n)
+            allf = list(range(F))
+
+            def step_single():
+                g1.reset_accumulators()
+                for g in allf:
+                    g1.submit_frame_device(poses_all[g], dimg(g), W * 3)
+                g1.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+
+            step_single()
+            g1.synchronize()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ss = 2
+            s0.record(stream)
+            for _ in range(ss):
+                step_single()
+            s1.record(stream)
+            g1.synchronize()
+            torch.cuda.synchronize()
+            sms = s0.elapsed_time(s1) / ss
+            single = {"n_gpus": 1, "value": n * F / (sms * 1e-3), "ms_per_step": sms, "steps": ss,
+                      "note": "the whole frame set of this run on rank 0's GPU alone (no exchange), timed after the N-GPU region"}
+            g1.close()
+        barrier()
 
     # ---- roofline of the dominant kernel ------------------------------------------------------------------------------
     # The timed region above runs frames_in_flight frames concurrently (kernels of neighbouring frames overlap), so the
     # per-kernel durations recorded there include time shared with other kernels.  The roofline numbers come from a second
-    # timed pass over the same workload with frames_in_flight = 1 (one kernel at a time), CUDA events on the launching stream.
-    peak, peak_src = _peaks()
-    frames_prof = max(prof["frames"], 1)
-    kern_ms_pipelined = {"scan": prof["scan_ms"] / frames_prof, "resolve": prof["resolve_ms"] / frames_prof}
-    prm1 = api.default_params(image_size=(W, H), frames_in_flight=1)
-    gc1 = api.Colorizer(cam, prm1, device=local)
-    gc1.set_stream(stream.cuda_stream)
-    gc1.set_cloud_device(d_cloud.data_ptr(), n)
-    serial_steps = max(1, min(args.steps, 5))
+    # timed pass over the same frames with frames_in_flight = 1 (one kernel at a time), CUDA events on the launching stream.
+    roofline = None
+    if rank == 0:
+        peak, peak_src = _peaks()
+        frames_prof = max(prof["frames"], 1)
+        kern_ms_pipelined = {"scan": prof["scan_ms"] / frames_prof, "resolve": prof["resolve_ms"] / frames_prof}
+        prm1 = api.default_params(image_size=(W, H), frames_in_flight=1, sample_mode=sample_mode)
+        gc1 = api.Colorizer(cam, prm1, device=local)
+        gc1.set_stream(stream.cuda_stream)
+        gc1.set_cloud_device(d_cloud.data_ptr(), n)
+        serial_steps = max(1, min(args.steps, 5 if n <= 20_000_000 else 1))
 
-    def step_serial():
-        gc1.reset_accumulators()
-        for i in range(f):
-            gc1.submit_frame_device(poses[i], img_ptrs[i], W * 3)
-        gc1.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+        def step_serial():
+            gc1.reset_accumulators()
+            for g in mine:
+                gc1.submit_frame_device(poses_all[g], dimg(g), W * 3)
+            gc1.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
 
-    for _ in range(2):
-        step_serial()
-    gc1.synchronize()
-    gc1.profile_enable(True)
-    evs0, evs1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    evs0.record(stream)
-    for _ in range(serial_steps):
-        step_serial()
-    evs1.record(stream)
-    gc1.synchronize()
-    torch.cuda.synchronize()
-    serial_ms_per_step = evs0.elapsed_time(evs1) / serial_steps
-    prof1 = gc1.profile_read()
-    gc1.close()
-    frames_prof1 = max(prof1["frames"], 1)
-    kern_ms = {"scan": prof1["scan_ms"] / frames_prof1, "resolve": prof1["resolve_ms"] / frames_prof1}
-    dominant = max(kern_ms, key=kern_ms.get)
-    Wc, Hc = W // prm.downsample, H // prm.downsample
-    scan_bytes = 16.0 * n                                    # pass 1 reads every point once as float4
-    pipe_bytes = n * (32.0 + 32.0 * f_vis) + 3.0 * W * H + 16.0 * Wc * Hc   # whole per-frame pipeline, §8d formula
-    scan_gbs = scan_bytes / (kern_ms["scan"] * 1e-3) / 1e9 if kern_ms["scan"] > 0 else 0.0
-    frame_ms = sum(kern_ms.values())
-    pipe_gbs = pipe_bytes / (frame_ms * 1e-3) / 1e9 if frame_ms > 0 else 0.0
-    roofline = {
-        "bound": "hbm", "kernel": "classify_kernel + scan_binned_kernel (pass 1)" if dominant == "scan" else dominant, "achieved": scan_gbs, "peak": peak, "unit": "GB/s",
-        "frac": scan_gbs / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": scan_bytes,
-        "kernel_ms_per_frame": kern_ms, "kernel_share_of_frame": {k: v / frame_ms for k, v in kern_ms.items()} if frame_ms > 0 else None,
-        "pipeline": {"algorithmic_bytes_per_frame": pipe_bytes, "f_vis": f_vis, "achieved": pipe_gbs, "frac": pipe_gbs / peak},
-        "note": "achieved = ALGORITHMIC bytes (every point of the cloud, SURVEY.md 8d) / time; the pre-binned scan never reads chunks that are "
-                "certainly culled, so DRAM traffic (`traffic`, ncu) is below the algorithmic bytes and frac is not capped at 1",
-        "measured_on": f"second timed pass, {serial_steps} steps with frames_in_flight=1 (kernels not overlapped): {serial_ms_per_step:.3f} ms/step",
-        "kernel_ms_per_frame_in_timed_region": kern_ms_pipelined,
-        "pipeline_in_timed_region": {"achieved": pipe_bytes * f / (ms / args.steps * 1e-3) / 1e9, "frac": pipe_bytes * f / (ms / args.steps * 1e-3) / 1e9 / peak,
-                                     "note": "algorithmic bytes of all frames / ms_per_step of the headline (overlapped) run"},
-    }
-    tr = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tr):
-        try:
-            roofline["traffic"] = json.load(open(tr)).get("scan_kernel_dram_bytes_per_launch")
-        except Exception:
-            pass
-
-    # ---- CPU baseline (rank 0, N=1 only) + parity of the sample -------------------------------------------------------
-    cpu = None
-    parity = None
-    if world == 1 and not args.no_cpu:
-        from oracle import pyoracle as O
-        threads = O.max_threads()
-        images_np = h_imgs.numpy()
-        k, dt, acc_o = _cpu_sample(cloud_np, poses, images_np, W, H, intr, dcoef, threads, args.cpu_budget, f)
-        cpu = {"value": n * k / dt, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"first {k} of {f} frames over the full {n}-point cloud, OpenMP over points, {dt:.1f} s"}
-        gc.reset_accumulators()
-        for i in range(k):
-            gc.submit_frame_device(poses[i], img_ptrs[i], W * 3)
-        acc_g, _, _ = gc.accumulators()
-        parity = {"frames": k, "accumulators_bit_exact_vs_oracle": bool(np.array_equal(acc_g, acc_o))}
+        for _ in range(2 if n <= 20_000_000 else 1):
+            step_serial()
+        gc1.synchronize()
+        gc1.profile_enable(True)
+        evs0, evs1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evs0.record(stream)
+        for _ in range(serial_steps):
+            step_serial()
+        evs1.record(stream)
+        gc1.synchronize()
+        torch.cuda.synchronize()
+        serial_ms_per_step = evs0.elapsed_time(evs1) / serial_steps
+        prof1 = gc1.profile_read()
+        gc1.close()
+        frames_prof1 = max(prof1["frames"], 1)
+        kern_ms = {"scan": prof1["scan_ms"] / frames_prof1, "resolve": prof1["resolve_ms"] / frames_prof1}
+        dominant = max(kern_ms, key=kern_ms.get)
+        Wc, Hc = W // prm.downsample, H // prm.downsample
+        scan_bytes = 16.0 * n                                    # pass 1 reads every point once as float4
+        pipe_bytes = n * (32.0 + 32.0 * f_vis) + 3.0 * W * H + 16.0 * Wc * Hc   # whole per-frame pipeline, §8d formula
+        scan_gbs = scan_bytes / (kern_ms["scan"] * 1e-3) / 1e9 if kern_ms["scan"] > 0 else 0.0
+        frame_ms = sum(kern_ms.values())
+        pipe_gbs = pipe_bytes / (frame_ms * 1e-3) / 1e9 if frame_ms > 0 else 0.0
+        ms_step_rank = ms / args.steps
+        roofline = {
+            "bound": "hbm", "kernel": "classify_kernel + scan_binned_kernel (pass 1)" if dominant == "scan" else dominant, "achieved": scan_gbs, "peak": peak,
+            "unit": "GB/s", "frac": scan_gbs / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": scan_bytes,
+            "kernel_ms_per_frame": kern_ms, "kernel_share_of_frame": {k: v / frame_ms for k, v in kern_ms.items()} if frame_ms > 0 else None,
+            "pipeline": {"algorithmic_bytes_per_frame": pipe_bytes, "f_vis": f_vis, "achieved": pipe_gbs, "frac": pipe_gbs / peak},
+            "note": "achieved = ALGORITHMIC bytes (every point of the cloud, SURVEY.md 8d) / time; the pre-binned scan never reads chunks that are "
+                    "certainly culled, so DRAM traffic (`traffic`, ncu) is below the algorithmic bytes and frac is not capped at 1",
+            "measured_on": f"second timed pass on rank 0, {serial_steps} steps with frames_in_flight=1 (kernels not overlapped): {serial_ms_per_step:.3f} ms/step",
+            "kernel_ms_per_frame_in_timed_region": kern_ms_pipelined,
+            "pipeline_in_timed_region": {"achieved": pipe_bytes * f / (ms_step_rank * 1e-3) / 1e9, "frac": pipe_bytes * f / (ms_step_rank * 1e-3) / 1e9 / peak,
+                                         "note": "algorithmic bytes of this rank's frames / ms_per_step of the headline (overlapped) run"},
+        }
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr):
+            try:
+                tj = json.load(open(tr))
+                roofline["traffic"] = tj.get("scan_kernel_dram_bytes_per_launch")
+                roofline["traffic_source"] = tj.get("source_note", "profiles/traffic.json: ncu --set full capture of this command at C2 (dram__bytes_read.sum + dram__bytes_write.sum per launch)")
+                if roofline["traffic"] and kern_ms["scan"] > 0 and plan["name"] == "C2":
+                    roofline["dram_frac"] = roofline["traffic"] / (kern_ms["scan"] * 1e-3) / 1e9 / peak
+            except Exception:
+                pass
 
     gc.close()
     if rank == 0:
+        cfg = _config(plan, world, args.sample)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {n} points x {f} frames @ {W}x{H} per GPU, colorize + z-buffer culling, SUM accumulators",
-                       "points": n, "frames_per_gpu": f, "image": [W, H], "parallelism": f"frames sharded x{world}, cloud replicated, NCCL allreduce u32",
-                       "frames_in_flight": int(prm.frames_in_flight),
-                       "l2": "inputs larger than L2 (cloud 16 B x N + one image per frame); no explicit flush",
-                       "host_affinity": (f"rank bound to the {numa} CPUs NVML lists for its GPU" if numa else "unbound")},
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if strong and world > 1 else "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": cfg,
+            "host": {"affinity": (f"rank bound to the {numa} CPUs NVML lists for its GPU" if numa else "unbound"), "threads": threads},
+            "frames_in_flight": int(prm.frames_in_flight), "frames_per_rank": f,
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "colours_equal_device_path": e2e_matches_device},
             "roofline": roofline,
         }
+        if exchange_ms is not None:
+            line["exchange"] = {"ms_per_step": exchange_ms, "what": "reduce-scatter of the u32 sums (16 B/point), finalize of the rank's slice, all-gather of colours + counts (8 B/point); "
+                                "CUDA events around it on the launching stream, max over ranks", "share_of_step": exchange_ms / (ms / args.steps)}
+        if single is not None:
+            line["single_gpu_same_workload"] = single
         if cpu is not None:
             line["cpu_baseline"] = cpu
         if parity is not None:
@@ -434,12 +586,16 @@ def _bind_to_gpu_numa_node(local):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--workload", default="", help="C1..C5 (default: C2 on one GPU, C4 sharded on several)")
+    ap.add_argument("--scaling", default="", choices=["", "strong", "weak"], help="N>1: strong = C4 frames sharded (default), weak = C2 per rank")
     ap.add_argument("--points", type=int, default=0)
     ap.add_argument("--frames", type=int, default=0)
+    ap.add_argument("--image-period", type=int, default=0)
+    ap.add_argument("--sample", default="nearest", choices=["nearest", "bilinear"])
+    ap.add_argument("--parity-frames", type=int, default=2, help="N>1: frames per rank of the oracle check of the exchanged accumulators")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

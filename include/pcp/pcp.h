@@ -60,8 +60,12 @@ typedef struct {
   float brightness_scale;          /* 1.0 (cpp:727) */
   int hsv_vector_block;            /* pixels per vector iteration of the OpenCV build to reproduce (its scalar row tail rounds
                                     * differently from its vector body): 32 = cv2 4.13 AVX2 build; 0 = whole row is vector body */
-  int reserved[2];
+  int debug_flags;                 /* PCP_DEBUG_*: 0 in production.  Test hooks that select a slower path with identical results. */
+  int reserved;
 } pcp_params;
+/* PCP_DEBUG_NO_PREFILTER: every point takes the exact FP64 path of pass 1 (no FP32 pre-filter, no chunk skipping by distance).
+ * PCP_DEBUG_NO_SEED: the previous frame's nearest points are not sent through pass 1 first. */
+enum { PCP_DEBUG_NO_PREFILTER = 1, PCP_DEBUG_NO_SEED = 2 };
 
 /* Optional per-frame outputs (host buffers, caller-owned; any pointer may be NULL). */
 typedef struct {
@@ -90,6 +94,8 @@ const char* pcp_last_error(const pcp_ctx* ctx); /* ctx may be NULL: message of t
 int pcp_set_stream(pcp_ctx* ctx, void* cuda_stream);
 void* pcp_get_stream(pcp_ctx* ctx);
 int pcp_synchronize(pcp_ctx* ctx);
+/* The context's stream waits (asynchronously, on the device) for every frame submitted so far; nothing blocks on the host. */
+int pcp_join(pcp_ctx* ctx);
 
 /* Pinned host memory for images/clouds, so that submit_frame's copies are asynchronous. */
 int pcp_host_alloc(void** out, size_t bytes);
@@ -158,6 +164,16 @@ int pcp_reset_accumulators(pcp_ctx* ctx);
 int pcp_nccl_unique_id(uint8_t id128[128]);
 int pcp_nccl_init(pcp_ctx* ctx, const uint8_t id128[128], int rank, int nranks);
 int pcp_allreduce(pcp_ctx* ctx);
+/* The exchange fused with finalize (SUM accumulators): ncclReduceScatter of the u32 sums (every rank then owns the whole job's sums
+ * of 1/G of the points), finalize of that slice only, ncclAllGather of the packed colour + count (8 B per point instead of 16 B of
+ * sums), outputs in the caller's point order on EVERY rank.  21 instead of 28 bytes per point cross NVLink and the finalize
+ * arithmetic is done once per point instead of G times; the results equal pcp_allreduce + pcp_finalize bit for bit.  TOP5 mode
+ * falls back to exactly that pair.  Afterwards the accumulators count as consumed: pcp_get_accumulators / pcp_finalize /
+ * pcp_submit_frame return PCP_EINVAL until pcp_reset_accumulators or pcp_set_cloud.  One exchange per pass: a second
+ * pcp_allreduce / pcp_exchange_finalize without a reset in between returns PCP_EINVAL on every rank (it would double-count).
+ * Replaces: smoothColors over the union of all keyframes' observations (src/PointCloudProcessor.cpp:604-631). */
+int pcp_exchange_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out);                 /* host outputs; synchronises */
+int pcp_exchange_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out);      /* device outputs; asynchronous */
 /* Global keyframe numbers of the frames this context submits (the tie-break of equal TOP5 scores, cpp:604-631 keeps the earlier
  * observation): the next frame is number `next`, then next + stride, ...  Rank r of G with interleaved sharding: (r, G).
  * Default (0, 1).  The numbering restarts from `next` at pcp_set_cloud / pcp_reset_accumulators. */

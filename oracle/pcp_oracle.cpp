@@ -34,7 +34,23 @@
 //  D12 cv::cvtColor BGR<->HSV 8-bit: restated from OpenCV 4.x and pinned against cv2 4.13.0 over all 2^24 inputs; the
 //      backward conversion differs between OpenCV's vector body and its scalar row tail (see hsv_roundtrip).
 //  D11 kd-tree re-indexing (PointCloudProcessor.cpp:557-593) is replaced by carrying the point index
-//      ("reindex=carry"); scores are computed from the camera-frame float point directly.
+//      ("reindex=carry", the default and what the CUDA path does); scores are computed from the camera-frame float point
+//      directly.  "reindex=radius" (orc_colorizer_set_reindex, small clouds only: brute force) restates the reference
+//      literally: float c2w' of the coloured camera-frame point, every map point within 1e-5 m of it receives the
+//      observation (none if the float round trip drifted further; coincident points all do), scores from the point taken
+//      back through Affine3f::inverse() [D4].  tests/test_oracle_cpu.py and tools/reindex_divergence.py measure the difference.
+//  D13 view_culling.cpp:88 `pt_2d_f / downsample_factor` is Eigen::Vector2f / int: Eigen promotes the int to float and
+//      evaluates scalar_quotient_op, a TRUE binary32 division per component (Eigen 3.2 and 3.3 alike; ROS noetic ships
+//      3.3.7) — not a multiplication by the reciprocal, which would move cell borders by one ulp for some u.
+//  D14 nid_cost.hpp:95-103 Eigen .sum(): `hist_points` holds integers, so `sum` is exact whatever the order.  The three
+//      entropy sums reduce `x * log(x + 1e-6)`: Eigen 3.3.7 (ROS noetic) has no packet log for double (packet_traits<double>::
+//      HasLog == 0 on SSE), and ceres::Jet is never vectorised, so for both T = double and T = Jet the reduction takes
+//      DefaultTraversal: std::log per coefficient, summed one coefficient at a time in storage order — i = 0..bins-1 for the two
+//      marginals, and COLUMN-major for `hist` (rows = image bin, columns = point bin): the oracle walks its row-major copy in
+//      that order.  (Eigen >= 3.4 vectorises log for doubles and would differ in the last bits; tolerance 1e-5 covers it.)
+//  D15 pcl::KdTreeFLANN::radiusSearch (cpp:571): squared distances accumulated in binary32 in x,y,z order (FLANN L2_Simple),
+//      compared against float(radius * radius) with radius = double(1e-5f); a neighbour is kept when dist2 < radius2... the
+//      boundary case cannot be pinned without FLANN; the oracle uses <=, which differs only for a point EXACTLY at 1e-5 m.
 
 #include <algorithm>
 #include <cfloat>
@@ -308,6 +324,7 @@ struct Colorizer {
   bool keep_obs = false;
   int sample_mode = 0;                 // 0 nearest (reference), 1 bilinear (extension, see bilinear_q)
   std::vector<std::vector<Obs>> obs;   // per-point observation lists (include/RGBCloud.hpp:29-41)
+  int reindex = 0;                     // 0 carry the point index [D11]; 1 radius: the reference's kd-tree re-indexing, brute force
   int frame_counter = 0;
 };
 
@@ -362,6 +379,8 @@ FrameResult colorize_frame(Colorizer& S, const double pose[7], const double* T_o
   // merge per-thread grids: the final map is min over fl32(dist) whatever the order
   for (int t = 0; t < T; t++) for (size_t c = 0; c < zmin.size(); c++) zmin[c] = std::min(zmin[c], zl[t][c]);
 
+  struct Colored { float x, y, z; uint8_t r, g, b; };
+  std::vector<std::vector<Colored>> colored(T);
   int n_cand = 0, n_vis = 0, n_col = 0;
 #pragma omp parallel for num_threads(T) reduction(+ : n_cand, n_vis, n_col) schedule(static, 1)
   for (int t = 0; t < T; t++) {
@@ -396,13 +415,38 @@ FrameResult colorize_frame(Colorizer& S, const double pose[7], const double* T_o
         if (mv == 255) S.mask_hits[c.idx] += 1;
         S.mask_max[c.idx] = std::max<uint32_t>(S.mask_max[c.idx], mv);
       }
-      if (S.keep_obs) {                                       // cpp:586-591
+      if (S.keep_obs && S.reindex == 1) {
+        colored[t].push_back({c.x, c.y, c.z, r, g, b});      // re-indexed below, serially (observations land on OTHER points' lists)
+      } else if (S.keep_obs) {                                // cpp:586-591
         const float o = orientation_score(c.x, c.y, c.z, pose);
         const float d = distance_score(c.x, c.y, c.z);
         const float f = (float)((double)(o + d) / 2.0);
         S.obs[c.idx].push_back({(float)r, (float)g, (float)b, f, S.frame_counter});
       }
     }
+  }
+  if (S.keep_obs && S.reindex == 1) {
+    // src/PointCloudProcessor.cpp:554-594, literally: coloredCloud -> world with c2w' in float (:555), radiusSearch(eps = 1e-5f)
+    // over the map cloud (:571) [D15], and for EVERY index found the scores of the point taken back through
+    // transformation_c2w_optimized.inverse() (:579, Affine3f::inverse() [D4], Matrix4f * Vector4f as column sums left to right).
+    const Mat4f inv = affine_inverse_f(c2w);
+    const float r2 = (float)((double)1e-5f * (double)1e-5f);
+    for (int t = 0; t < T; t++)
+      for (const Colored& c : colored[t]) {
+        float wx, wy, wz;
+        transform_point(c2w, c.x, c.y, c.z, wx, wy, wz);                                  // :555 [D1]
+        const float cx = ((inv(0, 0) * wx + inv(0, 1) * wy) + inv(0, 2) * wz) + inv(0, 3) * 1.0f;   // :579
+        const float cy = ((inv(1, 0) * wx + inv(1, 1) * wy) + inv(1, 2) * wz) + inv(1, 3) * 1.0f;
+        const float cz = ((inv(2, 0) * wx + inv(2, 1) * wy) + inv(2, 2) * wz) + inv(2, 3) * 1.0f;
+        const float o = orientation_score(cx, cy, cz, pose);                              // :586
+        const float d = distance_score(cx, cy, cz);                                       // :587
+        const float f = (float)((double)(o + d) / 2.0);                                   // :588
+        for (size_t j = 0; j < n; j++) {                                                  // :571, brute force
+          const float dx = S.xyzi[4 * j] - wx, dy = S.xyzi[4 * j + 1] - wy, dz = S.xyzi[4 * j + 2] - wz;
+          float d2 = dx * dx; d2 += dy * dy; d2 += dz * dz;
+          if (d2 <= r2) S.obs[j].push_back({(float)c.r, (float)c.g, (float)c.b, f, S.frame_counter});   // :590-591
+        }
+      }
   }
   R.n_candidates = n_cand; R.n_visible = n_vis; R.n_colored = n_col;
   S.frame_counter++;
@@ -466,7 +510,8 @@ bool nid_eval(const Camera& cam, const double* image, int W, int H, const float*
   double Hi = 0.0, Hp = 0.0, Hj = 0.0;
   for (int i = 0; i < bins; i++) { const double p = hist_image[i] / sum; Hi += p * std::log(p + 1e-6); }
   for (int i = 0; i < bins; i++) { const double p = hist_points[i] / sum; Hp += p * std::log(p + 1e-6); }
-  for (int i = 0; i < bins * bins; i++) { const double p = hist[i] / sum; Hj += p * std::log(p + 1e-6); }
+  for (int c = 0; c < bins; c++)          // Eigen's column-major walk of hist(row = image bin, column = point bin)  [D14]
+    for (int r = 0; r < bins; r++) { const double p = hist[(size_t)r * bins + c] / sum; Hj += p * std::log(p + 1e-6); }
   Hi = -Hi; Hp = -Hp; Hj = -Hj;                                                        // :101-103
   const double MI = Hi + Hp - Hj;                                                      // :104
   const double NID = (Hj - MI) / Hj;                                                   // :105
@@ -561,7 +606,8 @@ bool nid_eval_grad(const Camera& cam, const double* image, int W, int H, const f
   double Hp = 0.0;
   for (int i = 0; i < bins; i++) { const Jet7 p = hist_image[i] / Jet7(sum); Hi += p * jlog(p + Jet7(1e-6)); }
   for (int i = 0; i < bins; i++) { const double p = hist_points[i] / sum; Hp += p * std::log(p + 1e-6); }
-  for (int i = 0; i < bins * bins; i++) { const Jet7 p = hist[i] / Jet7(sum); Hj += p * jlog(p + Jet7(1e-6)); }
+  for (int c = 0; c < bins; c++)          // column-major, as in nid_eval  [D14]
+    for (int r = 0; r < bins; r++) { const Jet7 p = hist[(size_t)r * bins + c] / Jet7(sum); Hj += p * jlog(p + Jet7(1e-6)); }
   Hi = -Hi; Hp = -Hp; Hj = -Hj;
   const Jet7 MI = (Hi + Jet7(Hp)) - Hj;
   const Jet7 NID = (Hj - MI) / Hj;
@@ -752,6 +798,14 @@ void orc_colorizer_frame(void* h, const double* pose7, const double* T_opt16, co
                          size_t mask_pitch, uint8_t* vis, int32_t* pix, int threads, int* counts3) {
   const FrameResult r = colorize_frame(*(Colorizer*)h, pose7, T_opt16, bgr, pitch, mask, mask_pitch, vis, pix, threads);
   if (counts3) { counts3[0] = r.n_candidates; counts3[1] = r.n_visible; counts3[2] = r.n_colored; }
+}
+
+// reindex = 0: carry the index (default, D11); 1: the reference's kd-tree re-indexing by brute force (needs keep_obs; small clouds)
+void orc_colorizer_set_reindex(void* h, int mode) { ((Colorizer*)h)->reindex = mode; }
+// number of observations every point's list holds (RGBCloud::getPointData(i).rgbScores.size())
+void orc_colorizer_obs_counts(void* h, uint32_t* counts) {
+  Colorizer* S = (Colorizer*)h;
+  for (size_t i = 0; i < S->n; i++) counts[i] = S->keep_obs ? (uint32_t)S->obs[i].size() : 0u;
 }
 
 void orc_colorizer_get_acc(void* h, uint32_t* acc4, uint32_t* mask_hits, uint32_t* mask_max) {

@@ -127,7 +127,7 @@ def scores(pts_cam, pose7):
 class Colorizer:
     """The loop body of pcdColorizationAndSmooth (src/PointCloudProcessor.cpp:488-595) on the CPU."""
 
-    def __init__(self, cam, W, H, xyzi, cull_size=None, ds=14, tol=0.05, keep_obs=False, bilinear=False):
+    def __init__(self, cam, W, H, xyzi, cull_size=None, ds=14, tol=0.05, keep_obs=False, bilinear=False, reindex="carry"):
         self.cam, self.W, self.H = cam, W, H
         self.xyzi = np.ascontiguousarray(xyzi, np.float32)
         assert self.xyzi.ndim == 2 and self.xyzi.shape[1] == 4
@@ -137,6 +137,11 @@ class Colorizer:
                                                         C.c_size_t(self.n), int(keep_obs)))
         if bilinear:
             lib().orc_colorizer_set_sample_mode(self._h, 1)
+        if reindex not in ("carry", "radius"):
+            raise ValueError("reindex must be 'carry' or 'radius'")
+        if reindex == "radius":  # src/PointCloudProcessor.cpp:557-593 literally (brute force: small clouds only); decision D11
+            assert keep_obs, "reindex='radius' re-indexes the observation lists: keep_obs=True"
+            lib().orc_colorizer_set_reindex(self._h, 1)
 
     def close(self):
         if self._h:
@@ -167,6 +172,12 @@ class Colorizer:
         mm = np.empty(self.n, np.uint32)
         lib().orc_colorizer_get_acc(self._h, _p(acc), _p(mh), _p(mm))
         return acc, mh, mm
+
+    def obs_counts(self):
+        """Observations per point (RGBCloud::getPointData(i).rgbScores.size()); needs keep_obs."""
+        c = np.empty(self.n, np.uint32)
+        lib().orc_colorizer_obs_counts(self._h, _p(c))
+        return c
 
     def finalize_sum(self):
         rgb = np.empty((self.n, 3), np.uint8)

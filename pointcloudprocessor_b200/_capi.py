@@ -25,7 +25,7 @@ class Params(C.Structure):
         ("image_width", C.c_int), ("image_height", C.c_int), ("cull_width", C.c_int), ("cull_height", C.c_int),
         ("downsample", C.c_int), ("depth_tolerance", C.c_double), ("enable_depth_buffer_culling", C.c_int),
         ("accum_mode", C.c_int), ("sample_mode", C.c_int), ("top_m", C.c_int), ("prebin", C.c_int), ("frames_in_flight", C.c_int), ("hsv_adjust", C.c_int), ("saturation_scale", C.c_float),
-        ("brightness_scale", C.c_float), ("hsv_vector_block", C.c_int), ("reserved", C.c_int * 2),
+        ("brightness_scale", C.c_float), ("hsv_vector_block", C.c_int), ("debug_flags", C.c_int), ("reserved", C.c_int),
     ]
 
 
@@ -35,6 +35,7 @@ class FrameOut(C.Structure):
 
 
 OUT_SKIP_CANDIDATES = 1
+DEBUG_NO_PREFILTER, DEBUG_NO_SEED = 1, 2
 
 
 # every symbol include/pcp/pcp.h declares
@@ -64,6 +65,7 @@ SYMBOLS = [
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
     "pcp_bfgs_default_options", "pcp_se3_bfgs", "pcp_calib_default_params", "pcp_calibrate", "pcp_set_frame_numbering", "pcp_splat_masks_pose",
+    "pcp_join", "pcp_exchange_finalize", "pcp_exchange_finalize_device",
 ]
 class BfgsOptions(C.Structure):
     _fields_ = [
@@ -116,6 +118,9 @@ def load():
     L.pcp_get_stream.argtypes = [vp]
     L.pcp_get_stream.restype = vp
     L.pcp_synchronize.argtypes = [vp]
+    L.pcp_join.argtypes = [vp]
+    L.pcp_exchange_finalize.argtypes = [vp, vp, vp]
+    L.pcp_exchange_finalize_device.argtypes = [vp, vp, vp]
     L.pcp_host_alloc.argtypes = [C.POINTER(vp), sz]
     L.pcp_host_free.argtypes = [vp]
     L.pcp_set_cloud.argtypes = [vp, vp, sz, sz, sz]

@@ -243,6 +243,13 @@ class Colorizer:
         self._check(self._L.pcp_get_accumulators(self._h, _ptr(acc), _ptr(mh), _ptr(mm)), "pcp_get_accumulators")
         return acc, mh, mm
 
+    def mask_accumulators(self):
+        """(hits of mask == 255, max mask value) per point; also available after exchange_finalize."""
+        mh = np.empty(self.n, np.uint32)
+        mm = np.empty(self.n, np.uint32)
+        self._check(self._L.pcp_get_accumulators(self._h, None, _ptr(mh), _ptr(mm)), "pcp_get_accumulators")
+        return mh, mm
+
     def accumulators_device(self) -> int:
         return int(self._L.pcp_accumulators_device(self._h) or 0)
 
@@ -283,6 +290,20 @@ class Colorizer:
 
     def allreduce(self):
         self._check(self._L.pcp_allreduce(self._h), "pcp_allreduce")
+
+    def exchange_finalize(self, want_count=True):
+        """Reduce-scatter of the sums + finalize of the rank's slice + all-gather of the colours: (rgb, count) of the whole job."""
+        rgb = np.empty((self.n, 3), np.uint8)
+        cnt = np.empty(self.n, np.uint32) if want_count else None
+        self._check(self._L.pcp_exchange_finalize(self._h, _ptr(rgb), _ptr(cnt)), "pcp_exchange_finalize")
+        return (rgb, cnt) if want_count else rgb
+
+    def exchange_finalize_device(self, d_rgb: int, d_count: int = 0):
+        self._check(self._L.pcp_exchange_finalize_device(self._h, C.c_void_p(d_rgb or 0), C.c_void_p(d_count or 0)), "pcp_exchange_finalize_device")
+
+    def join(self):
+        """The context's stream waits (on the device) for every frame submitted so far."""
+        self._check(self._L.pcp_join(self._h), "pcp_join")
 
 
 def load_pcd_xyzi(path) -> np.ndarray:

@@ -52,7 +52,7 @@ void pcp_default_params(pcp_params* p) {
   p->saturation_scale = 1.0f;  // cpp:726-727
   p->brightness_scale = 1.0f;
   p->hsv_vector_block = 32;
-  p->prebin = 1;  // Morton-sorted chunks with AABBs; PCP_NO_PREBIN=1 or prebin = 0 keeps the caller's order on the device
+  p->prebin = 1;  // Morton-sorted chunks with AABBs; prebin = 0 keeps the caller's order on the device
 }
 
 int pcp_abi_version(void) { return PCP_ABI_VERSION; }
@@ -100,10 +100,6 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
     if ((e = cudaEventCreateWithFlags(&ctx->ev_free[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
   }
   ctx->flight = params->frames_in_flight > 0 ? params->frames_in_flight : 3;
-  {
-    const char* e_fl = std::getenv("PCP_FLIGHT");
-    if (e_fl && e_fl[0] >= '1' && e_fl[0] <= '0' + pcp_ctx::kMaxFlight) ctx->flight = e_fl[0] - '0';
-  }
   for (int i = 0; i < pcp_ctx::kMaxFlight; i++) {
     if ((e = cudaStreamCreateWithFlags(&ctx->fs[i].stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     if ((e = cudaEventCreateWithFlags(&ctx->fs[i].ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
@@ -121,14 +117,8 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
   ctx->resolve_grid = ctx->sm_count * 6;
-  {
-    const char* e_np = std::getenv("PCP_NO_PREFILTER");
-    ctx->prefilter = !(e_np && e_np[0] == '1');
-    const char* e_sd = std::getenv("PCP_NO_SEED");
-    ctx->use_seed = !(e_sd && e_sd[0] == '1');
-    const char* e_ns = std::getenv("PCP_SMZ");  // opt-in: measured 75-81 us vs 74.5 us for scan_kernel at C2
-    ctx->use_smz = (e_ns && e_ns[0] == '1');
-  }
+  ctx->prefilter = !(params->debug_flags & PCP_DEBUG_NO_PREFILTER);
+  ctx->use_seed = !(params->debug_flags & PCP_DEBUG_NO_SEED);
   *out = ctx;
   return PCP_OK;
 }
@@ -216,8 +206,9 @@ cudaError_t pcp_ctx::drain() {
 
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
-  F(d_cloud); F(d_perm); F(d_inv); F(d_aabb); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
-  F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt);
+  F(d_cloud); F(d_perm); F(d_inv); F(d_aabb); F(d_order); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
+  F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt); F(d_xchg);
+  xchg_points = 0;
   if (d_prebin_scratch) { cudaFree(d_prebin_scratch); d_prebin_scratch = nullptr; prebin_scratch_bytes = 0; }
   out_points = 0;
   n = 0;
@@ -225,12 +216,12 @@ void pcp_ctx::free_cloud() {
 
 // Sort the uploaded cloud into Morton chunks (pcp_prebin.cu).  Called after every upload, before the accumulators are reset.
 static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
-  const char* e_np = std::getenv("PCP_NO_PREBIN");
-  const bool on = ctx->prm.prebin != 0 && !(e_np && e_np[0] == '1') && n > 0;
+  const bool on = ctx->prm.prebin != 0 && n > 0;
   if (!on) {
     if (ctx->d_perm) { cudaFree(ctx->d_perm); ctx->d_perm = nullptr; }
     if (ctx->d_inv) { cudaFree(ctx->d_inv); ctx->d_inv = nullptr; }
     if (ctx->d_aabb) { cudaFree(ctx->d_aabb); ctx->d_aabb = nullptr; }
+    if (ctx->d_order) { cudaFree(ctx->d_order); ctx->d_order = nullptr; }
     if (ctx->d_active) { cudaFree(ctx->d_active); ctx->d_active = nullptr; }
     ctx->n_chunks = 0;
     return PCP_OK;
@@ -239,23 +230,19 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   if (!ctx->d_perm) CU(cudaMalloc(&ctx->d_perm, sizeof(uint32_t) * n));
   if (!ctx->d_inv) CU(cudaMalloc(&ctx->d_inv, sizeof(uint32_t) * n));
   if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
+  if (!ctx->d_order) CU(cudaMalloc(&ctx->d_order, sizeof(uint32_t) * n_chunks));
   if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks * pcp_ctx::kMaxFlight));
-  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, &ctx->d_prebin_scratch, &ctx->prebin_scratch_bytes, ctx->sm_count, ctx->stream));
+  CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->d_order, &ctx->d_prebin_scratch, &ctx->prebin_scratch_bytes, ctx->sm_count,
+                  ctx->stream));
   launch_invert_perm(ctx->d_perm, (uint32_t)n, ctx->d_inv, ctx->stream);
   ctx->n_chunks = n_chunks;
-  // odd multiplier coprime with n_chunks: the visiting order (slot * mul) % n_chunks is a permutation of the chunks
-  auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };
-  uint32_t mul = 1;
-  for (uint32_t cand : {40503u, 7919u, 7907u, 6007u, 5003u, 4001u, 3001u, 2003u, 1009u, 509u, 251u, 127u, 61u, 31u, 13u, 7u, 3u})
-    if (cand < n_chunks && gcd(cand, n_chunks) == 1) { mul = cand; break; }
-  ctx->chunk_mul = mul;
   ctx->launches += 6;
   return PCP_OK;
 }
 
 static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
   const size_t n1 = n ? n : 1;
-  CU(cudaMalloc(&ctx->d_acc, sizeof(uint4) * n1));
+  CU(cudaMalloc(&ctx->d_acc, sizeof(uint4) * (n1 + pcp_ctx::kAccPad)));
   CU(cudaMalloc(&ctx->d_records, sizeof(Record) * (n1 + 64) * ctx->flight));
   if (ctx->prm.accum_mode == PCP_ACCUM_TOP5) {
     CU(cudaMalloc(&ctx->d_top_score, sizeof(float) * n1 * ctx->prm.top_m));
@@ -268,12 +255,22 @@ static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
 
 extern "C" {
 
+/* The context's stream waits (asynchronously) for every frame submitted so far: work enqueued on it afterwards, e.g. an event
+ * recorded by the caller, follows the frames' kernels. */
+int pcp_join(pcp_ctx* ctx) {
+  if (!ctx) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  CU(ctx->join());
+  return PCP_OK;
+}
+
 int pcp_reset_accumulators(pcp_ctx* ctx) {
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   const size_t n1 = ctx->n ? ctx->n : 1;
   CU(ctx->join());  // frames in flight still update the accumulators
-  if (ctx->d_acc) CU(cudaMemsetAsync(ctx->d_acc, 0, sizeof(uint4) * n1, ctx->stream));
+  if (ctx->d_acc) CU(cudaMemsetAsync(ctx->d_acc, 0, sizeof(uint4) * (n1 + pcp_ctx::kAccPad), ctx->stream));
+  ctx->reduced = ctx->acc_scattered = false;
   if (ctx->d_mask_acc) CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * n1, ctx->stream));
   if (ctx->d_top_frame) {
     CU(cudaMemsetAsync(ctx->d_top_frame, 0xff, sizeof(uint32_t) * n1 * ctx->prm.top_m, ctx->stream));

@@ -32,15 +32,21 @@ struct pcp_ctx {
   float4* d_cloud = nullptr;      // N x 16 B  {x,y,z,intensity}
   uint32_t* d_perm = nullptr;     // N x 4 B   sorted position -> original index (pre-binned mode; null otherwise)
   uint32_t* d_inv = nullptr;      // N x 4 B   original index -> sorted position (pre-binned mode): finalize gathers through it
-  float4* d_aabb = nullptr;       // 2 float4 per chunk of 128 sorted points (pre-binned mode)
+  float4* d_aabb = nullptr;       // 2 float4 per chunk of 64 sorted points, stored in visiting order (pre-binned mode)
+  uint32_t* d_order = nullptr;    // visit slot -> chunk id (pre-binned mode)
   uint4* d_active = nullptr;      // per-frame list of chunks to scan + their cell rectangle / distance bound (pre-binned mode)
-  uint32_t n_chunks = 0, chunk_mul = 1;
+  uint32_t n_chunks = 0;
   void* d_prebin_scratch = nullptr;  // sort keys / temporaries of the pre-binning, kept across uploads
   size_t prebin_scratch_bytes = 0;
   uint8_t* d_out_rgb = nullptr;      // staging of pcp_finalize's host outputs, kept across calls
   uint32_t* d_out_cnt = nullptr;
   size_t out_points = 0;
+  static constexpr size_t kAccPad = 64;  // d_acc holds N + kAccPad entries: the reduce-scatter of pcp_exchange_finalize works on G equal slices
   uint4* d_acc = nullptr;         // N x 16 B  {sum_r,sum_g,sum_b,count}
+  uint2* d_xchg = nullptr;        // pcp_exchange_finalize: packed {rgb, count} of every point in sorted order (all-gather buffer)
+  size_t xchg_points = 0;
+  bool reduced = false;           // the accumulators were exchanged since the last reset (a second exchange would double-count)
+  bool acc_scattered = false;     // ... by pcp_exchange_finalize: only this rank's slice of d_acc is meaningful until the next reset
   uint2* d_mask_acc = nullptr;    // N x 8 B   {hits, max}; allocated at the first frame that carries a mask
   float* d_top_score = nullptr;   // top_m x N
   uint32_t* d_top_rgbf = nullptr;
@@ -60,7 +66,7 @@ struct pcp_ctx {
     cudaEvent_t ev_fork = nullptr, ev_done = nullptr;
   };
   FrameSlot fs[kMaxFlight];
-  int flight = 3;                 // frames in flight (pcp_params.frames_in_flight; PCP_FLIGHT=1..3 overrides)
+  int flight = 3;                 // frames in flight (pcp_params.frames_in_flight)
   uint64_t frames_run = 0;        // frames submitted since creation (slot = frames_run % flight)
   int last_slot = 0;              // slot of the last submitted frame
   cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
@@ -74,9 +80,8 @@ struct pcp_ctx {
   int frame_index = 0;
   int frame_first = 0;            // value frame_index restarts from at pcp_set_cloud / pcp_reset_accumulators
   int frame_stride = 1;           // pcp_set_frame_numbering: global keyframe number of the next frame and its increment
-  bool use_smz = false;   // shared-memory early-z scan kernel (PCP_SMZ=1 enables it when the grid fits)
-  bool use_seed = true;   // last frame's nearest points go through the exact path first (PCP_NO_SEED=1 disables it)
-  bool prefilter = true;  // FP32 pre-filter of the scan kernel (PCP_NO_PREFILTER=1 disables it: exact path for every point)
+  bool use_seed = true;   // last frame's nearest points go through the exact path first (pcp_params.debug_flags & PCP_DEBUG_NO_SEED disables it)
+  bool prefilter = true;  // FP32 pre-filter of the scan kernel (PCP_DEBUG_NO_PREFILTER disables it: exact path for every point)
   uint64_t launches = 0;
   std::string err;
 

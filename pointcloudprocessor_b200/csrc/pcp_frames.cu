@@ -79,6 +79,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
               bool want_vis, bool want_pix, bool accumulate, bool count_candidates, cudaEvent_t img_ready = nullptr,
               cudaEvent_t img_free = nullptr) {
   if (!ctx->d_cloud) { ctx->fail("no cloud: call pcp_set_cloud first"); return PCP_EINVAL; }
+  if (accumulate && ctx->acc_scattered) { ctx->fail("the accumulators were consumed by pcp_exchange_finalize: call pcp_reset_accumulators first"); return PCP_EINVAL; }
   int rc = ensure_outputs(ctx, want_vis, want_pix);
   if (rc != PCP_OK) return rc;
   if (d_mask && !ctx->d_mask_acc) {
@@ -119,20 +120,15 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.aabb = ctx->d_perm ? ctx->d_aabb : nullptr;
   sa.active = ctx->d_active ? ctx->d_active + (size_t)si * ctx->n_chunks : nullptr;
   sa.n_chunks = ctx->n_chunks;
-  sa.chunk_mul = ctx->chunk_mul;
+  sa.order = ctx->d_order;
+  sa.seed_blocks = (zp && fp.depth_culling && ctx->d_perm) ? (cells + 255) / 256 : 0;
   sa.zgrid = zg;
   sa.zprev = zp;
   sa.cells = cells;
   sa.records = recs;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
-  // shared-memory early-z variant when the z-grid's high words fit beside the queues (see scan_smz_kernel)
-  const bool smz = ctx->use_smz && !ctx->d_perm && fp.use_prefilter && fp.depth_culling && !fp.use_T && scan_smz_smem_bytes(cells) <= 232448;
-  if (smz) {
-    if (launch_scan_smz(sa, fp, ctx->sm_count, count_candidates, st) != 0) { ctx->fail("scan_smz_kernel: cannot reserve shared memory"); return PCP_ECUDA; }
-  } else {
-    launch_scan(sa, fp, ctx->scan_grid, count_candidates, st);
-  }
+  if (launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->device, st) != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
   if (pe) CU(cudaEventRecord(pe[2], st));
   // the resolve kernels update the accumulators without atomics: they run in frame order
   if (ctx->last_done && ctx->flight > 1) CU(cudaStreamWaitEvent(st, ctx->last_done, 0));
@@ -351,6 +347,7 @@ int pcp_get_accumulators(pcp_ctx* ctx, uint32_t* acc4, uint32_t* mask_hits, uint
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  if (acc4 && ctx->acc_scattered) { ctx->fail("pcp_get_accumulators: the colour sums were consumed by pcp_exchange_finalize (the mask accumulators are still available)"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
   CU(ctx->join());
   // per-point state lives in sorted order when the cloud is pre-binned: hand it back in the caller's order
@@ -418,6 +415,7 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
   if (!ctx) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  if (ctx->acc_scattered) { ctx->fail("pcp_finalize: the accumulators were consumed by pcp_exchange_finalize"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
   CU(ctx->join());
   if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm ? ctx->d_inv : nullptr, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
@@ -432,6 +430,7 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
   CU(cudaSetDevice(ctx->device));
   if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
   const size_t n = ctx->n;
+  if (ctx->acc_scattered) { ctx->fail("pcp_finalize: the accumulators were consumed by pcp_exchange_finalize"); return PCP_EINVAL; }
   if (n == 0) return PCP_OK;
   CU(ctx->join());
   if (ctx->out_points < n) {

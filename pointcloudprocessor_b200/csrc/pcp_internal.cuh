@@ -33,7 +33,8 @@ struct FrameCounters {
   unsigned int n_colored;     // generateColorMap pushes (cpp:763)
   unsigned int n_active_blocks;
   unsigned int stats[3];      // PCP_STATS builds: chunks skipped whole, points kept by stage A0, points kept by stage A1
-  unsigned int pad[8];
+  unsigned int pool_next;     // scan_ring_kernel: next entry of the common pool of the active list (relative to its start)
+  unsigned int pad[7];
 };
 static_assert(sizeof(FrameCounters) == 64, "FrameCounters layout");
 
@@ -71,10 +72,11 @@ struct FrameParams {
 struct ScanArgs {
   const float4* __restrict__ cloud;   // N x {x,y,z,intensity}, possibly block-sorted
   const uint32_t* __restrict__ perm;  // sorted position -> original index (null when not pre-binned)
-  const float4* __restrict__ aabb;    // pre-binned: 2 float4 per chunk {lo.xyz, nonfinite}, {hi.xyz, count}; null otherwise
+  const float4* __restrict__ aabb;    // pre-binned: 2 float4 per VISIT SLOT {lo.xyz, nonfinite}, {hi.xyz, count} (boxes stored in visiting order); null otherwise
+  const uint32_t* __restrict__ order; // pre-binned: visit slot -> chunk id (a fixed pseudo-random permutation of the chunks)
+  int seed_blocks;                    // classify_kernel: its first seed_blocks CTAs run the seed points, the others classify chunks
   uint4* active;                      // pre-binned: {chunk id, ChunkInfo rect, org, d2lo bits} of the chunks worth processing this frame
   uint32_t n_chunks;                  // ceil(n / kChunk)
-  uint32_t chunk_mul;                 // odd multiplier coprime with n_chunks: chunk visited at slot s is (s * chunk_mul) % n_chunks
   unsigned long long* zgrid;          // Wc*Hc packed keys
   const unsigned long long* zprev;    // the slot's previous final z-grid (its index words name the seed points), or null
   int cells;                          // Wc*Hc
@@ -104,9 +106,7 @@ struct ResolveArgs {
 };
 
 void launch_zgrid_init(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters, cudaStream_t s);
-void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s);
-size_t scan_smz_smem_bytes(int cells);
-int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s);
+int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, int device, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
 void launch_finalize_sum(const uint4* acc, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
@@ -116,8 +116,8 @@ void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_
 void launch_hsv_roundtrip(const uint8_t* src, size_t spitch, uint8_t* dst, size_t dpitch, int W, int H, float sat_scale, float val_scale, int block,
                           int sm_count, cudaStream_t s);
 // pre-binning (pcp_prebin.cu) and the un-permuting copy of per-point arrays (elem_words u32 words per point)
-cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, void** scratch, size_t* scratch_bytes, int sm_count,
-                         cudaStream_t s);
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, uint32_t* d_order, void** scratch, size_t* scratch_bytes,
+                         int sm_count, cudaStream_t s);
 void launch_invert_perm(const uint32_t* perm, uint32_t n, uint32_t* inv, cudaStream_t s);
 void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s);
 // ascending index list from a visibility bitmask; returns through d_total the number of set bits

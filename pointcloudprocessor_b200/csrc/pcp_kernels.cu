@@ -9,10 +9,11 @@
 //   finalize_*      smoothColors (src/PointCloudProcessor.cpp:604-631) as an integer mean or the top-M weighted mean.
 //
 // Compiled with -fmad=false; every decision-making operation additionally uses explicit _rn intrinsics (pcp_math.cuh).
+#include <type_traits>
+#include <utility>
+
 #include "pcp_internal.cuh"
 #include "pcp_chunk.cuh"
-
-#define PCP_SMZ_LOCALB 1  // scan_smz_kernel: stage B consults the shared-memory bound before talking to L2
 
 namespace pcp {
 
@@ -26,10 +27,43 @@ static constexpr int kWarpsPerCta = kScanThreads / 32;
 static constexpr int kQueueCap = 64;  // per-warp record queue, flushed 32 at a time
 static constexpr int kCandCap = 32 * (PCP_UNROLL_CAP + 1); // per-warp candidate queue: < 32 left over + kUnroll x 32 new entries
 
+// ---- PTX wrappers: mbarrier, 1-D bulk asynchronous copy (TMA engine), programmatic dependent launch ------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+// 1-D bulk asynchronous copy global -> shared (TMA engine, SASS UBLKCP); `bytes` a multiple of 16, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes),
+               "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Also hands the grid the slot's previous frame ended with to `zprev`: its index words name that frame's nearest point of
 // every cell, which classify_kernel sends through the exact path before anything else (seed points).
 __global__ void zgrid_init_kernel(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  pdl_launch_dependents();
   if (i < cells) {
     if (zprev) zprev[i] = zgrid[i];
     zgrid[i] = kZInit;
@@ -128,7 +162,7 @@ __device__ __forceinline__ unsigned int prefilter_b(const PreF& c, const PreA& a
 // `idx` goes into the record (the accumulator slot: original index, or sorted position when pre-binned); `key_idx` goes
 // into the packed z-grid key (tie-break among equal fl32 distances; the position of the point in the device cloud).
 __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long long* __restrict__ zgrid, float x, float y, float z,
-                                            uint32_t idx, uint32_t key_idx, Record& rec, bool& candidate, unsigned int* zs = nullptr) {
+                                            uint32_t idx, uint32_t key_idx, Record& rec, bool& candidate) {
   candidate = false;
   double X = (double)x, Y = (double)y, Z = (double)z;                // view_culling.cpp:33
   if (fp.use_T) transform_point_d(fp.T, (double)x, (double)y, (double)z, X, Y, Z);  // :37
@@ -152,26 +186,10 @@ __device__ __forceinline__ bool exact_point(const FrameParams& fp, unsigned long
   const int cell = py * fp.Wc + px;
   const float df = __double2float_rn(dist);                           // :123
   const unsigned long long key = ((unsigned long long)__float_as_uint(df) << 32) | (unsigned long long)key_idx;
-  unsigned long long cur;
-#ifdef PCP_SMZ_LOCALB
-  if (zs) {
-    // shared-memory copy first: only a point that can lower (or tie) the SM's bound talks to L2 at all
-    const unsigned int local = zs[cell];
-    cur = ((unsigned long long)local << 32) | 0xffffffffull;
-    if (__float_as_uint(df) <= local && dist <= 3.4028234663852886e+38) {
-      const unsigned long long old = atomicMin(zgrid + cell, key);
-      cur = old < key ? old : key;
-      atomicMin(zs + cell, (unsigned int)(cur >> 32));
-    }
-  } else
-#endif
-  {
-    cur = __ldcg(zgrid + cell);                                       // L2-coherent read: an upper bound of the final minimum
-    if (key < cur && dist <= 3.4028234663852886e+38) {                // :118 (dist > FLT_MAX never enters the map)
-      const unsigned long long old = atomicMin(zgrid + cell, key);
-      cur = old < key ? old : key;
-    }
-    if (zs) atomicMin(zs + cell, (unsigned int)(cur >> 32));         // the SM's shared-memory copy learns what L2 knows
+  unsigned long long cur = __ldcg(zgrid + cell);                      // L2-coherent read: an upper bound of the final minimum
+  if (key < cur && dist <= 3.4028234663852886e+38) {                  // :118 (dist > FLT_MAX never enters the map)
+    const unsigned long long old = atomicMin(zgrid + cell, key);
+    cur = old < key ? old : key;
   }
   const float minf = __uint_as_float((unsigned int)(cur >> 32));
   if (dist > __dadd_rn((double)minf, fp.tol)) return false;           // :157 can only get stricter as the minimum decreases
@@ -218,48 +236,51 @@ template <bool kCount>
 __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
   const int lane = threadIdx.x & 31;
   unsigned int ncand = 0;
+  pdl_launch_dependents();  // the scan kernel's CTAs may take their places (they wait for this grid before reading its list)
+  pdl_wait();               // zgrid_init_kernel's grid, counters and seed copy
   // Seed points.  The point that was nearest in a cell of this slot's previous frame is very likely near the front of the
   // new view too (consecutive keyframes are centimetres apart).  Sending those <= Wc*Hc points through the exact path FIRST
   // is nothing but a different processing order (the final grid is min over all in-grid candidates whatever the order,
   // SURVEY.md 3.4), but the scan kernel then starts against minima that are already close to final: more chunks fail the
   // distance test without being loaded and fewer points reach the FP64 stage or leave a record.  Seeds emit no record and
   // are not counted; the scan kernel meets the same points again in their chunks.  A stale or foreign index (first frame
-  // of a slot, new cloud) names some other point of the cloud, which is just as valid.
-  if (a.zprev && fp.depth_culling) {
-    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < a.cells; c += gridDim.x * blockDim.x) {
-      const uint32_t pos = (uint32_t)__ldg(a.zprev + c);  // index word = position in the (sorted) cloud
-      if (pos >= a.n) continue;
-      const float4 p = __ldg(a.cloud + pos);
-      float x = p.x, y = p.y, z = p.z;
-      if (fp.use_w2c) transform_point(fp.w2c, p.x, p.y, p.z, x, y, z);
-      Record rec;
-      bool cand;
-      (void)exact_point(fp, a.zgrid, x, y, z, pos, pos, rec, cand);
-    }
-  }
-  for (unsigned long long s0 = (unsigned long long)(blockIdx.x * blockDim.x + threadIdx.x - lane); s0 < a.n_chunks;
-       s0 += (unsigned long long)gridDim.x * blockDim.x) {
-    const unsigned long long slot = s0 + lane;
-    uint32_t chunk = 0;
-    int cls = kChunkSkip;
-    ChunkInfo info{0u, 0u, 0.0f};
-    if (slot < a.n_chunks) {
-      chunk = (uint32_t)((slot * a.chunk_mul) % a.n_chunks);
-      cls = kChunkProcess;
-      if (fp.use_prefilter) {  // with a double T (pcp_cull) the gate is taken after T: no chunk culling
-        const float4 a0 = __ldg(a.aabb + 2 * chunk), a1 = __ldg(a.aabb + 2 * chunk + 1);
-        cls = classify_chunk(fp, a0, a1, kCount, info);
-        if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
+  // of a slot, new cloud) names some other point of the cloud, which is just as valid.  The seeds have their own CTAs (the
+  // first seed_blocks of the grid), so that their chain of dependent accesses runs beside the chunk classification.
+  if ((int)blockIdx.x < a.seed_blocks) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < a.cells) {
+      const uint32_t pos = (uint32_t)__ldcg(a.zprev + c);  // index word = position in the (sorted) cloud (written by zgrid_init_kernel while this CTA may already have been resident: L2 load)
+      if (pos < a.n) {
+        const float4 p = __ldg(a.cloud + pos);
+        float x = p.x, y = p.y, z = p.z;
+        if (fp.use_w2c) transform_point(fp.w2c, p.x, p.y, p.z, x, y, z);
+        Record rec;
+        bool cand;
+        (void)exact_point(fp, a.zgrid, x, y, z, pos, pos, rec, cand);
       }
     }
-    const unsigned int m = __ballot_sync(0xffffffffu, cls == kChunkProcess);
-    if (m) {
-      unsigned int base = 0;
-      if (lane == 0) base = atomicAdd(&a.counters->n_active_blocks, (unsigned int)__popc(m));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (cls == kChunkProcess)
-        a.active[base + __popc(m & ((1u << lane) - 1u))] = make_uint4(chunk, info.rect, info.org, __float_as_uint(info.d2lo));
+    return;
+  }
+  const uint32_t slot = (blockIdx.x - a.seed_blocks) * blockDim.x + threadIdx.x;  // one lane per visit slot; whole warps take the same path
+  uint32_t chunk = 0;
+  int cls = kChunkSkip;
+  ChunkInfo info{0u, 0u, 0.0f};
+  if (slot < a.n_chunks) {
+    chunk = __ldg(a.order + slot);
+    cls = kChunkProcess;
+    if (fp.use_prefilter) {  // with a double T (pcp_cull) the gate is taken after T: no chunk culling
+      const float4 a0 = __ldg(a.aabb + 2 * slot), a1 = __ldg(a.aabb + 2 * slot + 1);
+      cls = classify_chunk(fp, a0, a1, kCount, info);
+      if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
     }
+  }
+  const unsigned int m = __ballot_sync(0xffffffffu, cls == kChunkProcess);
+  if (m) {
+    unsigned int base = 0;
+    if (lane == 0) base = atomicAdd(&a.counters->n_active_blocks, (unsigned int)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (cls == kChunkProcess)
+      a.active[base + __popc(m & ((1u << lane) - 1u))] = make_uint4(chunk, info.rect, info.org, __float_as_uint(info.d2lo));
   }
   if (kCount) {
     for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
@@ -414,6 +435,7 @@ static constexpr int kQ1Cap = 32 * (kA1 + 1);      // < 32 left over + one A1 ba
 #endif
 static constexpr int kRqFlush = PCP_RQ_FLUSH;   // records per global atomicAdd on n_records (same-address atomics serialise in L2)
 static constexpr int kRqCap = kRqFlush + 32;    // < kRqFlush left over + one stage-B batch
+#ifdef PCP_SCAN_V1  // the round-1 kernel, kept for one A/B measurement against scan_ring_kernel
 static constexpr size_t kBinnedSmem = (size_t)kWarpsPerCta * ((kQ0Cap + kQ1Cap) * sizeof(float4) + kRqCap * sizeof(Record));
 
 template <bool kCount>
@@ -652,137 +674,290 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
   }
 }
 
+#endif  // PCP_SCAN_V1
+
 // ---------------------------------------------------------------------------------------------------------------------
-// scan_smz_kernel: the same two stages with the early-z reads served from SHARED MEMORY.  One CTA of 32 warps per SM keeps
-// a private copy zs[cell] of the z-grid's high words (FP32 bit patterns, upper bounds of the final minima):
-//   * stage A reads it with LDS instead of a scattered global load (the L1/L2 latency of those reads was the top stall);
-//   * stage B, which talks to the authoritative 64-bit grid in L2 anyway, lowers zs[cell] to what it saw there;
-//   * after iterations 1, 2, 4, 8, ... the whole CTA re-reads the global grid (coalesced, ~8 B x cells) so that every SM
-//     learns the minima found by the others.  All warps run the same number of iterations, so the barriers are uniform.
-// Used when 144 KB of queues + 4 B x cells fit in the 227 KB of shared memory (<= ~21 k cells: every BASELINE config; the
-// reference's hard-coded 4096x3000 cull size has 62 k cells and takes scan_kernel).
+// scan_ring_kernel (pre-binned cloud): pass 1 as a warp-specialised pipeline.
+//
+//   scout warp (the CTA's last warp)
+//     walks the CTA's share of the active-chunk list 32 entries at a time, ONE LANE PER ENTRY: the lane reads the current
+//     minima of the entry's z-grid cell rectangle (ld.cg, L2) and decides whether the whole chunk can be skipped (its
+//     distance bound exceeds (minimum + tol)^2 of every cell it can fall into: the reference's pass 2, view_culling.cpp:157,
+//     rejects all of its points and none can lower a minimum).  The ids of the chunks that survive go, in one store for the
+//     whole batch, into a small shared-memory work ring {chunk, ticket number}.  The scout stays at most kAhead chunks ahead
+//     of the workers, so that it tests against minima that are as fresh as the old one-chunk-at-a-time kernel saw.
+//   worker warps (the other seven)
+//     take the ring's entries in order (one shared-memory ticket per chunk) and fetch the chunk THEMSELVES with one bulk
+//     asynchronous copy (cp.async.bulk.shared.global, 1 KB = 64 float4, completion on the warp's own mbarrier) into one of the
+//     warp's two buffers; the copy of the warp's next chunk is in flight while it works on the current one.  A skipped chunk
+//     is never read from HBM and nothing is prefetched on speculation.  Then the stages that decide: exact float transform
+//     (PCL order), FP32 projection pre-filter against the point's own cell (prefilter_a/b), compaction, and the exact FP64
+//     body (exact_point) 32 dense entries at a time; records leave through a warp-private queue, 32 records (1 KB, coalesced)
+//     per global atomicAdd.
+//
+// The split takes the per-entry work (ticket, list entry, rectangle test: a chain of dependent shared / L2 accesses that cost
+// a whole warp ~100 instructions per entry, 47 % of them for chunks that are then skipped) off the warps that do the
+// arithmetic and runs it 32 entries wide.  Every mbarrier is waited on only by the warp that armed it, which also tracks its
+// phase: no cross-warp phase bookkeeping (bulk copies complete out of order; a shared ring of slots whose consumers wait by
+// parity alone can be passed by a consumer that is a whole lap ahead).  Work distribution between CTAs: entries c, c + G, ...
+// of the first (100 - kPoolPct) % of the list are CTA c's own; the rest is a common pool the scouts draw from in batches with
+// one global atomic each, which evens out the end of the launch (chunk costs differ by orders of magnitude).
 // ---------------------------------------------------------------------------------------------------------------------
-#ifndef PCP_SMZ_THREADS
-#define PCP_SMZ_THREADS 1024
+#ifndef PCP_AHEAD
+#define PCP_AHEAD 24
 #endif
-static constexpr int kSmzThreads = PCP_SMZ_THREADS;
-static constexpr int kSmzWarps = kSmzThreads / 32;
-static constexpr size_t kSmzQueueBytes = (size_t)kSmzWarps * kCandCap * sizeof(float4) + (size_t)kSmzWarps * kQueueCap * sizeof(Record);
+#ifndef PCP_POOL_PCT
+#define PCP_POOL_PCT 30
+#endif
+#ifndef PCP_POOL_BATCH
+#define PCP_POOL_BATCH 16
+#endif
+static constexpr int kWorkers = kWarpsPerCta - 1;       // warps 0 .. kWorkers-1 work, warp kWorkers scouts
+static constexpr int kWorkCap = 128;                    // work-ring entries (power of two, >= kAhead + 32 + kWorkers)
+static constexpr int kAhead = PCP_AHEAD;                // the scout tests at most this many chunks ahead of the tickets taken
+static constexpr int kPoolPct = PCP_POOL_PCT;           // share of the active list handed out dynamically
+static constexpr int kPoolBatch = PCP_POOL_BATCH;       // pool entries per global atomic (<= 32)
+static constexpr uint32_t kWorkFree = 0xffffffffu;
+static constexpr size_t kBufBytes = (size_t)kWorkers * 2 * kChunk * sizeof(float4);  // two chunk buffers per worker warp
+static constexpr size_t kRingSmem = kBufBytes + (size_t)kWorkers * (kQ1Cap * sizeof(float4) + kRqCap * sizeof(Record));
+static_assert(kChunk == 64, "scan_ring_kernel: two points per worker lane");
+static_assert(kPoolBatch >= 1 && kPoolBatch <= 32, "pool batch: one lane per entry");
+static_assert((kWorkCap & (kWorkCap - 1)) == 0 && kWorkCap >= kAhead + 32 + kWorkers, "work ring too small");
+
+__device__ __forceinline__ uint2 lds_volatile_v2(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_volatile_v2(uint2* p, uint2 v) {
+  asm volatile("st.volatile.shared.v2.u32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "r"(v.x), "r"(v.y) : "memory");
+}
 
 template <bool kCount>
-__global__ void __launch_bounds__(kSmzThreads, 1) scan_smz_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
-  extern __shared__ __align__(16) unsigned char smz_smem[];
+__global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_ring_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+  extern __shared__ __align__(128) unsigned char ring_smem[];
+  __shared__ __align__(8) uint64_t s_bar[kWorkers][2];  // completion of the bulk copy into buffer b of worker w
+  __shared__ __align__(8) uint2 s_work[kWorkCap];       // {chunk id, ticket number} or {_, kWorkFree}
+  __shared__ volatile unsigned int s_total;             // number of work entries of this CTA, 0xffffffff until the scout is done
+  __shared__ unsigned int s_ticket;
+  __shared__ uint4 s_ent[kEntCap];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const unsigned int lt_mask = (1u << lane) - 1u;
-  float4* cq = reinterpret_cast<float4*>(smz_smem) + (size_t)warp * kCandCap;
-  Record* rq = reinterpret_cast<Record*>(smz_smem + (size_t)kSmzWarps * kCandCap * sizeof(float4)) + (size_t)warp * kQueueCap;
-  unsigned int* zs = reinterpret_cast<unsigned int*>(smz_smem + kSmzQueueBytes);
-  const int cells = fp.Wc * fp.Hc;
-  for (int i = threadIdx.x; i < cells; i += kSmzThreads) zs[i] = kZBoundInit;
-  __syncthreads();
-  int cn = 0, rn = 0;
   unsigned int ncand = 0;
+  const bool prefilter_on = fp.use_prefilter != 0;
+  const bool depth_culling = fp.depth_culling != 0;
+  const unsigned int* zhi = reinterpret_cast<const unsigned int*>(a.zgrid) + 1;
 
-  auto stage_b = [&](int cnt) {
-    Record rec;
-    bool cand = false, emit = false;
-    cn -= cnt;
-    if (lane < cnt) {
-      const float4 c = cq[cn + lane];
-      emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, __float_as_uint(c.w), __float_as_uint(c.w), rec, cand, zs);
-    }
-    if (kCount) ncand += cand ? 1u : 0u;
-    const unsigned int m = __ballot_sync(0xffffffffu, emit);
-    if (m) {
-      if (emit) rq[rn + __popc(m & lt_mask)] = rec;
-      rn += __popc(m);
-      __syncwarp();
-      if (rn >= 32) {
-        unsigned int base = 0;
-        if (lane == 0) base = atomicAdd(&a.counters->n_records, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        rn -= 32;
-        const uint4* src = reinterpret_cast<const uint4*>(rq + rn);
-        uint4* dst = reinterpret_cast<uint4*>(a.records + base);
-        dst[lane] = src[lane];
-        dst[lane + 32] = src[lane + 32];
-        __syncwarp();
+  if (threadIdx.x < kWorkCap) s_work[threadIdx.x] = make_uint2(0u, kWorkFree);
+  if (threadIdx.x == 0) {
+    for (int w = 0; w < kWorkers; w++) { mbar_init(&s_bar[w][0], 1u); mbar_init(&s_bar[w][1], 1u); }
+    s_ticket = 0u;
+    s_total = 0xffffffffu;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  pdl_wait();  // everything above overlaps the tail of classify_kernel (programmatic dependent launch); its list is read from here on
+  // this CTA may have been resident since before classify_kernel wrote its list: read that data from L2, never through L1 / the
+  // read-only path (ld.global.nc promises data that is constant for the lifetime of THIS kernel, which started earlier)
+  const uint32_t n_active = __ldcg(&a.counters->n_active_blocks);
+  const uint32_t G = gridDim.x;
+  // static share: entries c + G j, j < n_static (the same count for every CTA); pool: entries [n_static * G, n_active)
+  const uint32_t n_static = (uint32_t)(((unsigned long long)n_active * (100 - kPoolPct) / 100) / G);
+  const uint32_t pool0 = n_static * G;
+  for (uint32_t j = threadIdx.x; j < n_static && j < (uint32_t)kEntCap; j += blockDim.x) s_ent[j] = __ldcg(a.active + blockIdx.x + G * j);
+  __syncthreads();
+
+  if (warp == kWorkers) {
+    // ------------------------------------------------------------ scout ---------------------------------------------------
+    uint32_t count = 0;  // work entries published so far
+    auto offer = [&](bool valid, const uint4& ent) {
+      // stay close to the workers: a test against minima that are kAhead chunks old skips less
+      while ((int)(count - *(volatile unsigned int*)&s_ticket) > kAhead) __nanosleep(64);
+      bool skip = false;
+      if (valid && ent.y != 0u) {
+        const int w = (int)(ent.y & 63u), h = (int)((ent.y >> 6) & 63u);
+        const unsigned int* row = zhi + 2 * ((int)(ent.z >> 16) * fp.Wc + (int)(ent.z & 0xffffu));
+        unsigned int m = 0u;  // max over the rectangle of (minimum + tol)^2 rounded up, as bits (non-negative floats order like their bits)
+        for (int cy = 0; cy < h; cy++, row += 2 * fp.Wc) {
+#pragma unroll 4
+          for (int cx = 0; cx < w; cx++) {
+            const float lim = __fadd_ru(__uint_as_float(PCP_ZLOAD0(row + 2 * cx)), fp.pre.tol_up);
+            m = max(m, __float_as_uint(__fmul_ru(lim, lim)));
+          }
+        }
+        skip = __uint_as_float(ent.w) > __uint_as_float(m);  // the whole chunk is farther than every cell it can fall into
+        if (kCount && skip) ncand += ent.y >> 12;             // offered only for all-candidate chunks (classify_chunk)
       }
+      const bool go = valid && !skip;
+      const unsigned int gm = __ballot_sync(0xffffffffu, go);
+      if (go) {
+        const uint32_t t = count + __popc(gm & lt_mask);
+        uint2* e = &s_work[t & (kWorkCap - 1)];
+        while (lds_volatile_v2(e).y != kWorkFree) __nanosleep(32);  // the worker that held the entry's previous ticket hands it back
+        sts_volatile_v2(e, make_uint2(ent.x, t));
+#ifndef PCP_NO_SCOUT_PREFETCH
+        // the chunk WILL be read (it passed the test): start it on its way from HBM to L2 now, so that the worker's bulk copy, a few
+        // tickets later, finds it there.  One instruction covers one 128-byte line of every surviving lane's chunk.
+        const float4* src = a.cloud + (size_t)ent.x * kChunk;
+#pragma unroll
+        for (int k = 0; k < kChunk / 8; k++)
+          if ((uint32_t)(k * 8) < a.n - ent.x * (uint32_t)kChunk) prefetch_l2(src + k * 8);  // not beyond the cloud's last point
+#endif
+      }
+      count += __popc(gm);
+      __syncwarp();
+    };
+    for (uint32_t j0 = 0; j0 < n_static; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      const bool valid = j < n_static;
+      uint4 ent = make_uint4(0u, 0u, 0u, 0u);
+      if (valid) ent = j < (uint32_t)kEntCap ? s_ent[j] : __ldcg(a.active + blockIdx.x + G * j);
+      offer(valid, ent);
     }
-  };
+    for (;;) {  // the common pool
+      uint32_t i0 = 0;
+      if (lane == 0) i0 = pool0 + atomicAdd(&a.counters->pool_next, (unsigned int)kPoolBatch);
+      i0 = __shfl_sync(0xffffffffu, i0, 0);
+      if (i0 >= n_active) break;
+      const uint32_t i = i0 + lane;
+      const bool valid = lane < kPoolBatch && i < n_active;
+      uint4 ent = make_uint4(0u, 0u, 0u, 0u);
+      if (valid) ent = __ldcg(a.active + i);
+      offer(valid, ent);
+    }
+    if (lane == 0) s_total = count;  // tickets >= count find no work
+  } else {
+    // ------------------------------------------------------------ workers -------------------------------------------------
+    float4* buf = reinterpret_cast<float4*>(ring_smem) + (size_t)warp * 2 * kChunk;
+    float4* q1 = reinterpret_cast<float4*>(ring_smem + kBufBytes) + (size_t)warp * kQ1Cap;
+    Record* rq = reinterpret_cast<Record*>(ring_smem + kBufBytes + (size_t)kWorkers * kQ1Cap * sizeof(float4)) + (size_t)warp * kRqCap;
+    int n1 = 0, rn = 0;
 
-  const unsigned long long per_iter = (unsigned long long)gridDim.x * kSmzThreads * kUnroll;
-  const uint32_t iters = (uint32_t)(((unsigned long long)a.n + per_iter - 1) / per_iter);
-  float4 p[kUnroll];
-  auto load_chunk = [&](uint32_t it) {
-    const unsigned long long b = ((unsigned long long)it * gridDim.x + blockIdx.x) * (kSmzThreads * kUnroll) + (unsigned long long)warp * (32 * kUnroll);
+    auto stage_b = [&](int cnt) {
+      Record rec;
+      bool cand = false, emit = false;
+      n1 -= cnt;
+      if (lane < cnt) {
+        const float4 c = q1[n1 + lane];
+        const uint32_t slot = __float_as_uint(c.w);
+        // key index = sorted position: ties on fl32(dist) go to the smallest sorted position (deterministic; nothing reads the
+        // index word of the grid except the seed pass, and the reference never reads its index_map)
+        emit = exact_point(fp, a.zgrid, c.x, c.y, c.z, slot, slot, rec, cand);
+      }
+      if (kCount) ncand += cand ? 1u : 0u;
+      const unsigned int m = __ballot_sync(0xffffffffu, emit);
+      if (m) {
+        if (emit) rq[rn + __popc(m & lt_mask)] = rec;
+        rn += __popc(m);
+        __syncwarp();
+        if (rn >= kRqFlush) {
+          unsigned int base = 0;
+          if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)kRqFlush);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          rn -= kRqFlush;
+          const uint4* src = reinterpret_cast<const uint4*>(rq + rn);
+          uint4* dst = reinterpret_cast<uint4*>(a.records + base);
 #pragma unroll
-    for (int k = 0; k < kUnroll; k++) {
-      const unsigned long long i = b + k * 32 + lane;
-      p[k] = i < a.n ? __ldcs(a.cloud + i) : make_float4(0.f, 0.f, -1.f, 0.f);
-    }
-  };
-#ifdef PCP_SMZ_PIPE
-  load_chunk(0);
-#endif
-  for (uint32_t it = 0; it < iters; it++) {
-    const unsigned long long base64 = ((unsigned long long)it * gridDim.x + blockIdx.x) * (kSmzThreads * kUnroll) + (unsigned long long)warp * (32 * kUnroll);
-    bool valid[kUnroll];
-    uint32_t idx[kUnroll];
-#ifndef PCP_SMZ_PIPE
-    load_chunk(it);
-#endif
+          for (int t = 0; t < kRqFlush / 16; t++) dst[lane + 32 * t] = src[lane + 32 * t];
+          __syncwarp();
+        }
+      }
+    };
+
+    // Takes the next ticket, waits for its work entry and starts the bulk copy of that chunk into buffer b.
+    // `base` / `cnt`: the chunk's first point (sorted position) and point count; returns false when no work is left.
+    auto fetch = [&](int b, uint32_t& base, uint32_t& cnt) -> bool {
+      uint32_t chunk = kWorkFree;
+      if (lane == 0) {
+        const uint32_t t = atomicAdd(&s_ticket, 1u);
+        uint2* e = &s_work[t & (kWorkCap - 1)];
+        for (;;) {
+          const uint2 v = lds_volatile_v2(e);
+          if (v.y == t) { chunk = v.x; sts_volatile_v2(e, make_uint2(0u, kWorkFree)); break; }
+          if (t >= s_total) break;  // the scout is done and never issued this ticket
+          __nanosleep(32);
+        }
+        if (chunk != kWorkFree) {
+          const uint32_t b0 = chunk * kChunk;
+          const uint32_t c = a.n - b0 < (uint32_t)kChunk ? a.n - b0 : (uint32_t)kChunk;
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the warp's reads of this buffer precede the async-proxy write
+          mbar_arrive_expect_tx(&s_bar[warp][b], c * 16u);
+          bulk_g2s(buf + (size_t)b * kChunk, a.cloud + b0, c * 16u, &s_bar[warp][b]);
+        }
+      }
+      chunk = __shfl_sync(0xffffffffu, chunk, 0);
+      if (chunk == kWorkFree) return false;
+      base = chunk * kChunk;
+      cnt = a.n - base < (uint32_t)kChunk ? a.n - base : (uint32_t)kChunk;
+      return true;
+    };
+
+    uint32_t base[2] = {0u, 0u}, cnt[2] = {0u, 0u}, phase[2] = {0u, 0u};
+    bool have[2];
+    have[0] = fetch(0, base[0], cnt[0]);
+    have[1] = have[0] ? fetch(1, base[1], cnt[1]) : false;
+    // one chunk out of buffer B (a compile-time index: base / cnt / phase / have stay in registers)
+    auto step = [&](auto B) {
+      constexpr int b = decltype(B)::value;
+      mbar_wait(&s_bar[warp][b], phase[b]);
+      phase[b] ^= 1u;
+      float4 p[2];
+      p[0] = buf[(size_t)b * kChunk + lane];
+      p[1] = buf[(size_t)b * kChunk + 32 + lane];
+      const uint32_t cbase = base[b], ccnt = cnt[b];
+      __syncwarp();  // every lane has its points: the buffer can take the warp's next chunk while this one is processed
+      have[b] = fetch(b, base[b], cnt[b]);
+      float x[2], y[2], z[2];
+      bool ok[2], push[2];
+      unsigned int cur[2];
 #pragma unroll
-    for (int k = 0; k < kUnroll; k++) {
-      const unsigned long long i = base64 + k * 32 + lane;
-      valid[k] = i < a.n;
-      idx[k] = (uint32_t)i;
-    }
-    float x[kUnroll], y[kUnroll], z[kUnroll];
-    bool push[kUnroll];
+      for (int k = 0; k < 2; k++) {
+        x[k] = p[k].x; y[k] = p[k].y; z[k] = p[k].z;
+        if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x[k], y[k], z[k]);  // pcl::transformPointCloud (cpp:521)
+        ok[k] = (uint32_t)(k * 32 + lane) < ccnt && !(z[k] < 0.0f);  // view_culling.cpp:76 (exact: double(z) < 0 <=> z < 0)
+        cur[k] = kZBoundInit;  // FLT_MAX: always an upper bound (cell unknown, or pre-filter off)
+      }
+      if (prefilter_on) {
+        PreA pa[2];
 #pragma unroll
-    for (int k = 0; k < kUnroll; k++) {
-      x[k] = p[k].x; y[k] = p[k].y; z[k] = p[k].z;
-      if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x[k], y[k], z[k]);  // pcl::transformPointCloud (cpp:521)
-    }
-#ifdef PCP_SMZ_PIPE
-    // the registers of p are free again: the next chunk's loads fly during the pre-filter and stage B of this one
-    if (it + 1 < iters) load_chunk(it + 1);
-#endif
+        for (int k = 0; k < 2; k++) pa[k] = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
 #pragma unroll
-    for (int k = 0; k < kUnroll; k++) {
-      const PreA pa = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
-      const unsigned int cur = (pa.flags & 1u) ? zs[pa.cell] : kZBoundInit;
-      const unsigned int f = prefilter_b<kCount>(fp.pre, pa, cur, true);
-      const bool front = valid[k] && !(z[k] < 0.0f);  // view_culling.cpp:76
-      push[k] = front && (f & 1u);
-      if (kCount) ncand += (front && (f & 2u)) ? 1u : 0u;
-    }
+        for (int k = 0; k < 2; k++)
+          if (ok[k] && (pa[k].flags & 1u)) cur[k] = PCP_ZLOAD(zhi + 2 * pa[k].cell);
 #pragma unroll
-    for (int k = 0; k < kUnroll; k++) {
-      const unsigned int m = __ballot_sync(0xffffffffu, push[k]);
-      if (push[k]) cq[cn + __popc(m & lt_mask)] = make_float4(x[k], y[k], z[k], __uint_as_float(idx[k]));
-      cn += __popc(m);
+        for (int k = 0; k < 2; k++) {
+          const unsigned int f = prefilter_b<kCount>(fp.pre, pa[k], cur[k], depth_culling);
+          push[k] = ok[k] && (f & 1u);
+          if (kCount) ncand += (ok[k] && (f & 2u)) ? 1u : 0u;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 2; k++) push[k] = ok[k];
+      }
+#pragma unroll
+      for (int k = 0; k < 2; k++) {
+        const unsigned int m = __ballot_sync(0xffffffffu, push[k]);
+        if (push[k]) q1[n1 + __popc(m & lt_mask)] = make_float4(x[k], y[k], z[k], __uint_as_float(cbase + k * 32 + lane));
+        n1 += __popc(m);
+      }
+      __syncwarp();
+#pragma unroll 1
+      while (n1 >= 32) stage_b(32);
+    };
+#pragma unroll 1
+    while (have[0] || have[1]) {
+      if (have[0]) step(std::integral_constant<int, 0>{});
+      if (have[1]) step(std::integral_constant<int, 1>{});
     }
     __syncwarp();
-#pragma unroll 1
-    while (cn >= 32) stage_b(32);
-    if (((it + 1) & it) == 0 && it + 1 < iters) {  // after iterations 1, 2, 4, 8, ...: pull the other SMs' minima
-      __syncthreads();
-      const unsigned int* zhi = reinterpret_cast<const unsigned int*>(a.zgrid) + 1;
-      for (int i = threadIdx.x; i < cells; i += kSmzThreads) atomicMin(zs + i, __ldcg(zhi + 2 * i));
-      __syncthreads();
+    if (n1 > 0) stage_b(n1);
+    if (rn > 0) {
+      unsigned int rbase = 0;
+      if (lane == 0) rbase = atomicAdd(&a.counters->n_records, (unsigned int)rn);
+      rbase = __shfl_sync(0xffffffffu, rbase, 0);
+      for (int i = lane; i < rn; i += 32) a.records[rbase + i] = rq[i];
     }
-  }
-
-  __syncwarp();
-  if (cn > 0) stage_b(cn);
-  if (rn > 0) {
-    unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(&a.counters->n_records, (unsigned int)rn);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (lane < rn) a.records[base + lane] = rq[lane];
   }
   if (kCount) {
     for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
@@ -790,41 +965,59 @@ __global__ void __launch_bounds__(kSmzThreads, 1) scan_smz_kernel(const ScanArgs
   }
 }
 
-size_t scan_smz_smem_bytes(int cells) { return kSmzQueueBytes + sizeof(unsigned int) * (size_t)(cells > 0 ? cells : 1); }
-
-int launch_scan_smz(const ScanArgs& a, const FrameParams& fp, int sm_count, bool count_candidates, cudaStream_t s) {
-  static bool configured = false;
-  const size_t bytes = scan_smz_smem_bytes(fp.Wc * fp.Hc);
-  if (!configured) {
-    if (cudaFuncSetAttribute(scan_smz_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448) != cudaSuccess) return 1;
-    if (cudaFuncSetAttribute(scan_smz_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448) != cudaSuccess) return 1;
-    configured = true;
-  }
-  if (count_candidates) scan_smz_kernel<true><<<sm_count, kSmzThreads, bytes, s>>>(a, fp);
-  else scan_smz_kernel<false><<<sm_count, kSmzThreads, bytes, s>>>(a, fp);
-  return 0;
+// Launch with the programmatic-stream-serialization attribute: the kernel's CTAs may start while the previous kernel of the
+// stream drains; the kernel itself waits (griddepcontrol.wait) before it touches anything its predecessor wrote.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
-void launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, cudaStream_t s) {
+int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, int device, cudaStream_t s) {
   if (a.aabb) {
-    const int cgrid = (int)((a.n_chunks + 255) / 256);
-    static bool configured = false;
-    if (!configured) {
-      cudaFuncSetAttribute(scan_binned_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem);
-      cudaFuncSetAttribute(scan_binned_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem);
-      configured = true;
+    const int cgrid = a.seed_blocks + (int)((a.n_chunks + 255) / 256);
+    // the opt-in to > 48 KB of dynamic shared memory is a per-device attribute: one flag per device, not per process
+    static bool configured[64] = {};
+    if (device < 0 || device >= 64 || !configured[device]) {
+#ifdef PCP_SCAN_V1
+      if (cudaFuncSetAttribute(scan_binned_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem) != cudaSuccess) return 1;
+      if (cudaFuncSetAttribute(scan_binned_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem) != cudaSuccess) return 1;
+#endif
+      if (cudaFuncSetAttribute(scan_ring_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+      if (cudaFuncSetAttribute(scan_ring_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+      if (device >= 0 && device < 64) configured[device] = true;
     }
-    if (count_candidates) {
-      classify_kernel<true><<<cgrid, 256, 0, s>>>(a, fp);
-      scan_binned_kernel<true><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
-    } else {
-      classify_kernel<false><<<cgrid, 256, 0, s>>>(a, fp);
-      scan_binned_kernel<false><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
-    }
+    cudaError_t e;
+    if (count_candidates) e = launch_pdl(classify_kernel<true>, dim3(cgrid), dim3(256), 0, s, a, fp);
+    else e = launch_pdl(classify_kernel<false>, dim3(cgrid), dim3(256), 0, s, a, fp);
+    if (e != cudaSuccess) return 1;
+#ifdef PCP_SCAN_V1
+    if (count_candidates) scan_binned_kernel<true><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
+    else scan_binned_kernel<false><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
+#else
+#ifdef PCP_NO_PDL_SCAN
+    if (count_candidates) scan_ring_kernel<true><<<grid, kScanThreads, kRingSmem, s>>>(a, fp);
+    else scan_ring_kernel<false><<<grid, kScanThreads, kRingSmem, s>>>(a, fp);
+#else
+    if (count_candidates) e = launch_pdl(scan_ring_kernel<true>, dim3(grid), dim3(kScanThreads), kRingSmem, s, a, fp);
+    else e = launch_pdl(scan_ring_kernel<false>, dim3(grid), dim3(kScanThreads), kRingSmem, s, a, fp);
+    if (e != cudaSuccess) return 1;
+#endif
+#endif
   } else {
     if (count_candidates) scan_kernel<true><<<grid, kScanThreads, 0, s>>>(a, fp);
     else scan_kernel<false><<<grid, kScanThreads, 0, s>>>(a, fp);
   }
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

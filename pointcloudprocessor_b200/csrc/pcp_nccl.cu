@@ -1,6 +1,9 @@
 // pcp_nccl.cu — the one exchange step of the path, after the frames have been sharded across ranks:
 //   SUM accumulators   ncclAllReduce(u32, sum): integer sums are associative, bit-identical for any rank count;
 //   mask accumulators  {hits, max} split into two planes, all-reduced with sum and max;
+//   SUM + finalize     pcp_exchange_finalize*: ncclReduceScatter of the sums (every rank ends up owning the job's sums of 1/G of the
+//                      points), finalize of that slice only, ncclAllGather of the packed colours + counts (8 B per point instead of
+//                      the 16 B of the sums): 21 instead of 28 bytes per point cross NVLink and the finalize arithmetic is done once;
 //   TOP5 slots         ncclAllGather of the ranks' sorted slot lists, block of points by block, and a merge kernel that keeps the
 //                      top_m best of the union under the same total order (score descending, global frame number ascending) the
 //                      insertion uses — so the merged lists equal the single-rank run's when frames carry their global numbers
@@ -21,6 +24,7 @@ typedef int (*fn_get_unique_id)(NcclId*);
 typedef int (*fn_comm_init_rank)(NcclComm*, int, NcclId, int);
 typedef int (*fn_all_reduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t);
 typedef int (*fn_all_gather)(const void*, void*, size_t, int, NcclComm, cudaStream_t);
+typedef int (*fn_reduce_scatter)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t);
 typedef int (*fn_comm_destroy)(NcclComm);
 typedef const char* (*fn_error_string)(int);
 
@@ -30,6 +34,7 @@ struct NcclApi {
   fn_comm_init_rank comm_init_rank = nullptr;
   fn_all_reduce all_reduce = nullptr;
   fn_all_gather all_gather = nullptr;
+  fn_reduce_scatter reduce_scatter = nullptr;
   fn_comm_destroy comm_destroy = nullptr;
   fn_error_string error_string = nullptr;
   bool ok = false;
@@ -48,9 +53,10 @@ NcclApi& api() {
   a.comm_init_rank = (fn_comm_init_rank)dlsym(a.handle, "ncclCommInitRank");
   a.all_reduce = (fn_all_reduce)dlsym(a.handle, "ncclAllReduce");
   a.all_gather = (fn_all_gather)dlsym(a.handle, "ncclAllGather");
+  a.reduce_scatter = (fn_reduce_scatter)dlsym(a.handle, "ncclReduceScatter");
   a.comm_destroy = (fn_comm_destroy)dlsym(a.handle, "ncclCommDestroy");
   a.error_string = (fn_error_string)dlsym(a.handle, "ncclGetErrorString");
-  a.ok = a.get_unique_id && a.comm_init_rank && a.all_reduce && a.all_gather && a.comm_destroy;
+  a.ok = a.get_unique_id && a.comm_init_rank && a.all_reduce && a.all_gather && a.reduce_scatter && a.comm_destroy;
   return a;
 }
 
@@ -80,6 +86,27 @@ __global__ void top_pack_kernel(const float* __restrict__ score, const uint32_t*
     out[((size_t)0 * top_m + k) * cap + j] = __float_as_uint(score[src]);
     out[((size_t)1 * top_m + k) * cap + j] = rgbf[src];
     out[((size_t)2 * top_m + k) * cap + j] = frame[src];
+  }
+}
+
+// ---- SUM: finalize of the rank's slice after the reduce-scatter, and the un-permuting unpack after the all-gather ------------------
+// packed[j] = {r | g << 8 | b << 16, count} of sorted position j (the integer mean of finalize_sum_kernel; `fixed88`: 8.8 sums, rounded)
+__global__ void finalize_slice_kernel(const uint4* __restrict__ acc, uint32_t j0, uint32_t j1, uint2* __restrict__ packed, int fixed88) {
+  for (uint32_t j = j0 + blockIdx.x * blockDim.x + threadIdx.x; j < j1; j += gridDim.x * blockDim.x) {
+    const uint4 s = acc[j];
+    uint32_t r = 0, g = 0, b = 0;
+    if (s.w) { r = s.x / s.w; g = s.y / s.w; b = s.z / s.w; }
+    if (fixed88) { r = min((r + 128u) >> 8, 255u); g = min((g + 128u) >> 8, 255u); b = min((b + 128u) >> 8, 255u); }
+    packed[j] = make_uint2(r | (g << 8) | (b << 16), s.w);
+  }
+}
+// outputs in the caller's point order: walks the output index (coalesced writes) and gathers through inv (null: identity)
+__global__ void unpack_colours_kernel(const uint2* __restrict__ packed, const uint32_t* __restrict__ inv, uint32_t n, uint8_t* __restrict__ rgb,
+                                      uint32_t* __restrict__ count) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint2 v = packed[inv ? __ldg(inv + i) : i];
+    if (rgb) { rgb[3 * (size_t)i] = (uint8_t)(v.x & 255u); rgb[3 * (size_t)i + 1] = (uint8_t)((v.x >> 8) & 255u); rgb[3 * (size_t)i + 2] = (uint8_t)(v.x >> 16); }
+    if (count) count[i] = v.y;
   }
 }
 
@@ -126,6 +153,46 @@ void nccl_teardown(pcp_ctx* ctx) {
   ctx->nccl_comm = nullptr;
 }
 
+// mask accumulators {hits, max}: split into two planes, all-reduced with sum and max, joined (every rank makes the same calls)
+static int exchange_masks(pcp_ctx* ctx) {
+  NcclComm comm = (NcclComm)ctx->nccl_comm;
+  cudaStream_t st = ctx->stream;
+  const uint32_t n = (uint32_t)ctx->n;
+  const int grid = ctx->sm_count * 8;
+  auto nccl_fail = [&](const char* what, int rc) { ctx->fail("%s: %s", what, api().error_string ? api().error_string(rc) : "error"); return PCP_ENCCL; };
+  // mask accumulators exist only on ranks that were handed a mask: agree first (one u32, max), so that every rank makes the same calls
+  uint32_t* d_flag = nullptr;
+  if (cudaMalloc(&d_flag, sizeof(uint32_t)) != cudaSuccess) { ctx->fail("pcp exchange: cudaMalloc failed"); return PCP_ENOMEM; }
+  uint32_t any_mask = ctx->d_mask_acc ? 1u : 0u;
+  cudaMemcpyAsync(d_flag, &any_mask, sizeof(uint32_t), cudaMemcpyHostToDevice, st);
+  {
+    const int rc = api().all_reduce(d_flag, d_flag, 1, kNcclUint32, kNcclMax, comm, st);
+    cudaMemcpyAsync(&any_mask, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    const cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(d_flag);
+    if (rc != 0) return nccl_fail("ncclAllReduce (mask flag)", rc);
+    if (e != cudaSuccess) { ctx->fail("pcp exchange: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+  }
+  if (any_mask && !ctx->d_mask_acc) {
+    if (cudaMalloc(&ctx->d_mask_acc, sizeof(uint2) * (size_t)n) != cudaSuccess) { ctx->fail("pcp exchange: out of device memory for the mask accumulators"); return PCP_ENOMEM; }
+    cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * (size_t)n, st);
+  }
+  if (any_mask) {
+    uint32_t* d_planes = nullptr;
+    if (cudaMalloc(&d_planes, sizeof(uint32_t) * 2 * (size_t)n) != cudaSuccess) { ctx->fail("pcp exchange: out of device memory for the mask exchange"); return PCP_ENOMEM; }
+    mask_split_kernel<<<grid, 256, 0, st>>>(ctx->d_mask_acc, d_planes, d_planes + n, n);
+    int rc = api().all_reduce(d_planes, d_planes, n, kNcclUint32, kNcclSum, comm, st);
+    if (rc == 0) rc = api().all_reduce(d_planes + n, d_planes + n, n, kNcclUint32, kNcclMax, comm, st);
+    if (rc == 0) mask_join_kernel<<<grid, 256, 0, st>>>(ctx->d_mask_acc, d_planes, d_planes + n, n);
+    const cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(d_planes);
+    if (rc != 0) return nccl_fail("ncclAllReduce (mask)", rc);
+    if (e != cudaSuccess) { ctx->fail("pcp exchange: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+    ctx->launches += 4;
+  }
+  return PCP_OK;
+}
+
 extern "C" {
 
 int pcp_nccl_unique_id(uint8_t id128[128]) {
@@ -156,6 +223,10 @@ int pcp_allreduce(pcp_ctx* ctx) {
   if (!ctx) return PCP_EINVAL;
   if (ctx->nccl_nranks <= 1 && !ctx->nccl_comm) return PCP_OK;  // single rank: nothing to exchange
   if (!ctx->nccl_comm) { ctx->fail("pcp_allreduce: call pcp_nccl_init first"); return PCP_ENCCL; }
+  if (ctx->reduced) {  // a second exchange would add the other ranks' sums again (and duplicate TOP5 observations)
+    ctx->fail("pcp_allreduce: the accumulators were already exchanged; call pcp_reset_accumulators before the next pass");
+    return PCP_EINVAL;
+  }
   if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->fail("cudaSetDevice failed"); return PCP_ECUDA; }
   if (ctx->join() != cudaSuccess) { ctx->fail("pcp_allreduce: cudaStreamWaitEvent failed"); return PCP_ECUDA; }
   NcclComm comm = (NcclComm)ctx->nccl_comm;
@@ -197,38 +268,85 @@ int pcp_allreduce(pcp_ctx* ctx) {
     cudaFree(d_recv);
     if (rc != 0) return nccl_fail("ncclAllGather", rc);
     if (e != cudaSuccess) { ctx->fail("pcp_allreduce: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+    // the plain sums / observation counts are kept in TOP5 mode too: exchange them as well, so that pcp_get_accumulators describes the job
+    rc = api().all_reduce(ctx->d_acc, ctx->d_acc, (size_t)n * 4, kNcclUint32, kNcclSum, comm, st);
+    if (rc != 0) return nccl_fail("ncclAllReduce", rc);
+    ctx->launches++;
   }
 
-  // mask accumulators exist only on ranks that were handed a mask: agree first (one u32, max), so that every rank makes the same calls
-  uint32_t* d_flag = nullptr;
-  if (cudaMalloc(&d_flag, sizeof(uint32_t)) != cudaSuccess) { ctx->fail("pcp_allreduce: cudaMalloc failed"); return PCP_ENOMEM; }
-  uint32_t any_mask = ctx->d_mask_acc ? 1u : 0u;
-  cudaMemcpyAsync(d_flag, &any_mask, sizeof(uint32_t), cudaMemcpyHostToDevice, st);
-  {
-    const int rc = api().all_reduce(d_flag, d_flag, 1, kNcclUint32, kNcclMax, comm, st);
-    cudaMemcpyAsync(&any_mask, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
-    const cudaError_t e = cudaStreamSynchronize(st);
-    cudaFree(d_flag);
-    if (rc != 0) return nccl_fail("ncclAllReduce (mask flag)", rc);
-    if (e != cudaSuccess) { ctx->fail("pcp_allreduce: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+  ctx->reduced = true;
+  return exchange_masks(ctx);
+}
+
+/* Reduce-scatter + finalize of the rank's slice + all-gather of colours and counts (SUM accumulators); TOP5: pcp_allreduce + finalize.
+ * Outputs are device pointers (either may be null).  Afterwards only this rank's slice of the sums is the job's: the accumulators
+ * count as consumed until pcp_reset_accumulators / pcp_set_cloud. */
+int pcp_exchange_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out) {
+  if (!ctx) return PCP_EINVAL;
+  if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  if (ctx->nccl_nranks <= 1 && !ctx->nccl_comm) return pcp_finalize_device(ctx, d_rgb_out, d_count_out);
+  if (!ctx->nccl_comm) { ctx->fail("pcp_exchange_finalize: call pcp_nccl_init first"); return PCP_ENCCL; }
+  if (ctx->prm.accum_mode != PCP_ACCUM_SUM) {
+    const int rc = pcp_allreduce(ctx);
+    return rc != PCP_OK ? rc : pcp_finalize_device(ctx, d_rgb_out, d_count_out);
   }
-  if (any_mask && !ctx->d_mask_acc) {
-    if (cudaMalloc(&ctx->d_mask_acc, sizeof(uint2) * (size_t)n) != cudaSuccess) { ctx->fail("pcp_allreduce: out of device memory for the mask accumulators"); return PCP_ENOMEM; }
-    cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * (size_t)n, st);
+  if (ctx->reduced) {
+    ctx->fail("pcp_exchange_finalize: the accumulators were already exchanged; call pcp_reset_accumulators before the next pass");
+    return PCP_EINVAL;
   }
-  if (any_mask) {
-    uint32_t* d_planes = nullptr;
-    if (cudaMalloc(&d_planes, sizeof(uint32_t) * 2 * (size_t)n) != cudaSuccess) { ctx->fail("pcp_allreduce: out of device memory for the mask exchange"); return PCP_ENOMEM; }
-    mask_split_kernel<<<grid, 256, 0, st>>>(ctx->d_mask_acc, d_planes, d_planes + n, n);
-    int rc = api().all_reduce(d_planes, d_planes, n, kNcclUint32, kNcclSum, comm, st);
-    if (rc == 0) rc = api().all_reduce(d_planes + n, d_planes + n, n, kNcclUint32, kNcclMax, comm, st);
-    if (rc == 0) mask_join_kernel<<<grid, 256, 0, st>>>(ctx->d_mask_acc, d_planes, d_planes + n, n);
-    const cudaError_t e = cudaStreamSynchronize(st);
-    cudaFree(d_planes);
-    if (rc != 0) return nccl_fail("ncclAllReduce (mask)", rc);
-    if (e != cudaSuccess) { ctx->fail("pcp_allreduce: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
-    ctx->launches += 4;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->fail("cudaSetDevice failed"); return PCP_ECUDA; }
+  if (ctx->join() != cudaSuccess) { ctx->fail("pcp_exchange_finalize: cudaStreamWaitEvent failed"); return PCP_ECUDA; }
+  const uint32_t n = (uint32_t)ctx->n;
+  if (n == 0) return PCP_OK;
+  NcclComm comm = (NcclComm)ctx->nccl_comm;
+  cudaStream_t st = ctx->stream;
+  const uint32_t G = (uint32_t)ctx->nccl_nranks, r = (uint32_t)ctx->nccl_rank;
+  const uint32_t slice = (n + G - 1) / G;  // points per rank; the accumulator array is padded to G * slice entries (pcp_ctx::kAccPad)
+  if ((size_t)slice * G > ctx->n + pcp_ctx::kAccPad) { ctx->fail("pcp_exchange_finalize: more than %d ranks", (int)pcp_ctx::kAccPad); return PCP_EINVAL; }
+  if (ctx->xchg_points < (size_t)slice * G) {
+    if (ctx->d_xchg) { cudaFree(ctx->d_xchg); ctx->d_xchg = nullptr; }
+    if (cudaMalloc(&ctx->d_xchg, sizeof(uint2) * (size_t)slice * G) != cudaSuccess) { ctx->fail("pcp_exchange_finalize: out of device memory"); return PCP_ENOMEM; }
+    ctx->xchg_points = (size_t)slice * G;
   }
+  auto nccl_fail = [&](const char* what, int rc) { ctx->fail("%s: %s", what, api().error_string ? api().error_string(rc) : "error"); return PCP_ENCCL; };
+  uint32_t* acc_words = reinterpret_cast<uint32_t*>(ctx->d_acc);
+  int rc = api().reduce_scatter(acc_words, acc_words + (size_t)r * slice * 4, (size_t)slice * 4, kNcclUint32, kNcclSum, comm, st);  // in place
+  if (rc != 0) return nccl_fail("ncclReduceScatter", rc);
+  const uint32_t j0 = r * slice, j1 = (r + 1) * slice < n ? (r + 1) * slice : n;
+  if (j1 > j0) finalize_slice_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_acc, j0, j1, ctx->d_xchg, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR);
+  rc = api().all_gather(ctx->d_xchg + (size_t)r * slice, ctx->d_xchg, (size_t)slice * 2, kNcclUint32, comm, st);  // in place
+  if (rc != 0) return nccl_fail("ncclAllGather", rc);
+  if (d_rgb_out || d_count_out) unpack_colours_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_xchg, ctx->d_perm ? ctx->d_inv : nullptr, n, d_rgb_out, d_count_out);
+  ctx->launches += 4;
+  ctx->reduced = true;
+  ctx->acc_scattered = true;  // only this rank's slice of d_acc holds the job's sums now
+  if (cudaGetLastError() != cudaSuccess) { ctx->fail("pcp_exchange_finalize: kernel launch failed"); return PCP_ECUDA; }
+  return exchange_masks(ctx);
+}
+
+/* Same with host outputs (synchronises). */
+int pcp_exchange_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
+  if (!ctx) return PCP_EINVAL;
+  if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  const size_t n = ctx->n;
+  if (n == 0) return PCP_OK;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) { ctx->fail("cudaSetDevice failed"); return PCP_ECUDA; }
+  if (ctx->out_points < n) {
+    if (ctx->d_out_rgb) { cudaFree(ctx->d_out_rgb); ctx->d_out_rgb = nullptr; }
+    if (ctx->d_out_cnt) { cudaFree(ctx->d_out_cnt); ctx->d_out_cnt = nullptr; }
+    if (cudaMalloc(&ctx->d_out_rgb, n * 3) != cudaSuccess || cudaMalloc(&ctx->d_out_cnt, n * sizeof(uint32_t)) != cudaSuccess) {
+      ctx->fail("pcp_exchange_finalize: out of device memory");
+      return PCP_ENOMEM;
+    }
+    ctx->out_points = n;
+  }
+  const int rc = pcp_exchange_finalize_device(ctx, rgb_out ? ctx->d_out_rgb : nullptr, count_out ? ctx->d_out_cnt : nullptr);
+  if (rc != PCP_OK) return rc;
+  cudaError_t e = cudaSuccess;
+  if (rgb_out) e = cudaMemcpyAsync(rgb_out, ctx->d_out_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && count_out) e = cudaMemcpyAsync(count_out, ctx->d_out_cnt, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) { ctx->fail("pcp_exchange_finalize: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
   return PCP_OK;
 }
 

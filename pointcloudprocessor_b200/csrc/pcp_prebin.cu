@@ -87,7 +87,10 @@ __global__ void gather_kernel(const float4* __restrict__ src, const uint32_t* __
 
 // One warp per chunk of kChunk sorted points: {lo.xyz, flag}, {hi.xyz, count}; flag = 1 when the chunk holds a non-finite
 // coordinate (such a chunk is never culled as a whole).
-__global__ void chunk_aabb_kernel(const float4* __restrict__ pts, uint32_t n, uint32_t n_chunks, float4* __restrict__ aabb) {
+// The boxes are stored in VISITING order: chunk w sits at slot (w * mul_inv) % n_chunks, the inverse of the pseudo-random visit
+// sequence slot -> (slot * mul) % n_chunks, so that classify_kernel reads boxes and chunk ids coalesced and without a modulo.
+__global__ void chunk_aabb_kernel(const float4* __restrict__ pts, uint32_t n, uint32_t n_chunks, uint32_t mul_inv, float4* __restrict__ aabb,
+                                  uint32_t* __restrict__ order) {
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (w >= n_chunks) return;
@@ -111,8 +114,10 @@ __global__ void chunk_aabb_kernel(const float4* __restrict__ pts, uint32_t n, ui
     cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
   }
   if (lane == 0) {
-    aabb[2 * w] = make_float4(lo[0], lo[1], lo[2], bad ? 1.0f : 0.0f);
-    aabb[2 * w + 1] = make_float4(hi[0], hi[1], hi[2], (float)cnt);
+    const uint32_t slot = (uint32_t)(((unsigned long long)w * mul_inv) % n_chunks);
+    aabb[2 * slot] = make_float4(lo[0], lo[1], lo[2], bad ? 1.0f : 0.0f);
+    aabb[2 * slot + 1] = make_float4(hi[0], hi[1], hi[2], (float)cnt);
+    order[slot] = w;
   }
 }
 
@@ -122,8 +127,8 @@ __global__ void chunk_aabb_kernel(const float4* __restrict__ pts, uint32_t n, ui
 // d_aabb (2 float4 per chunk).  All buffers are allocated by the caller.
 // `scratch` is a context-owned device buffer that is grown on demand and kept (cudaMalloc/cudaFree per upload cost tens of
 // milliseconds of host time on a busy box); nothing here synchronises the stream.
-cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, void** scratch, size_t* scratch_bytes, int sm_count,
-                         cudaStream_t s) {
+cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, uint32_t* d_order, void** scratch, size_t* scratch_bytes,
+                         int sm_count, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
   cudaError_t e;
   auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
@@ -156,7 +161,17 @@ cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* 
   gather_kernel<<<grid, 256, 0, s>>>(d_cloud, d_perm, n, d_tmp);
   if ((e = cudaMemcpyAsync(d_cloud, d_tmp, sizeof(float4) * n, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) return e;
   const uint32_t n_chunks = (n + kChunk - 1) / kChunk;
-  chunk_aabb_kernel<<<(n_chunks * 32 + 255) / 256, 256, 0, s>>>(d_cloud, n, n_chunks, d_aabb);
+  // visit sequence slot -> (slot * mul) % n_chunks with an odd multiplier coprime with n_chunks (a permutation that spreads the
+  // chunks in flight over the whole map); the kernel needs its inverse
+  auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };
+  uint64_t mul = 1;
+  for (uint32_t cand : {40503u, 7919u, 7907u, 6007u, 5003u, 4001u, 3001u, 2003u, 1009u, 509u, 251u, 127u, 61u, 31u, 13u, 7u, 3u})
+    if (cand < n_chunks && gcd(cand, n_chunks) == 1) { mul = cand; break; }
+  int64_t t0 = 0, t1 = 1, r0 = (int64_t)n_chunks, r1 = (int64_t)(mul % n_chunks);  // extended Euclid: mul * t1 == 1 (mod n_chunks)
+  if (n_chunks == 1) { t1 = 0; r1 = 1; }
+  while (r1 > 1) { const int64_t q = r0 / r1, r2 = r0 - q * r1, t2 = t0 - q * t1; r0 = r1; r1 = r2; t0 = t1; t1 = t2; }
+  const uint32_t mul_inv = (uint32_t)(((t1 % (int64_t)n_chunks) + (int64_t)n_chunks) % (int64_t)n_chunks);
+  chunk_aabb_kernel<<<(n_chunks * 32 + 255) / 256, 256, 0, s>>>(d_cloud, n, n_chunks, mul_inv, d_aabb, d_order);
   return cudaGetLastError();
 }
 

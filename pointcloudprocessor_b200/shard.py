@@ -3,9 +3,11 @@ the u32 accumulators are summed once at the end, so any partition of the frames 
 from __future__ import annotations
 
 
-def frames_of_rank(n_frames: int, rank: int, world: int, mode: str = "interleaved"):
+def frames_of_rank(n_frames: int, rank: int, world: int, mode: str = "interleaved", block: int = 25):
     """Indices of the keyframes rank `rank` processes.  "interleaved": r, r+G, ... (balances the slowly varying
-    visible fraction along a path); "blocks": contiguous stretches (pose locality)."""
+    visible fraction along a path); "blocks": contiguous stretches (pose locality); "dealt": blocks of `block`
+    consecutive keyframes dealt round-robin (both: consecutive frames of a rank stay centimetres apart, which the
+    seed points of pass 1 rely on, and every rank sees every part of the path)."""
     if not (0 <= rank < world):
         raise ValueError("rank out of range")
     if mode == "interleaved":
@@ -14,4 +16,8 @@ def frames_of_rank(n_frames: int, rank: int, world: int, mode: str = "interleave
         lo = n_frames * rank // world
         hi = n_frames * (rank + 1) // world
         return list(range(lo, hi))
+    if mode == "dealt":
+        if block < 1:
+            raise ValueError("block must be >= 1")
+        return [g for b0 in range(0, n_frames, block) if (b0 // block) % world == rank for g in range(b0, min(b0 + block, n_frames))]
     raise ValueError(f"unknown sharding mode {mode}")

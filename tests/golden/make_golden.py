@@ -27,6 +27,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+if HERE not in sys.path:
+    sys.path.insert(0, HERE)
 
 from oracle import pyoracle as O  # noqa: E402
 from pointcloudprocessor_b200 import synth  # noqa: E402
@@ -124,7 +126,15 @@ def nid_case():
 
 
 def distmask_case():
-    """generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265) on the culled cloud of each frame; stored sparse."""
+    """generate_distance_masks (scripts/genNormAndDistanceMask.py:233-265) on the culled cloud of each frame; stored sparse.
+
+    The masks are produced by the REFERENCE'S OWN SOURCE (tests/golden/ref_extract.py cuts the method out of the module with `ast`
+    and runs it): this fixture pins the oracle (and through it the CUDA path) to the reference, not to a restatement.  The winner
+    index per pixel is an extension the reference does not compute; it comes from the oracle and is checked to describe the same
+    filled pixels."""
+    import ref_extract as R
+    if not R.available():
+        raise SystemExit("distmask fixture: /root/reference is not present; this fixture can only be generated next to the reference tree")
     n, f, W, H = 60_000, 3, 640, 480
     intr, dist = synth.make_camera(W, H)
     cloud = synth.make_cloud(n)
@@ -135,13 +145,18 @@ def distmask_case():
         w2c, _ = O.pose_matrices(poses[i])
         pts = O.transform(cloud[:, :3], w2c)
         keep = O.view_culling(cam, W, H, pts)
-        d, xyz, idx = O.distance_masks(cam, W, H, pts[keep])
+        rd, rxyz, lines = R.reference_distance_masks(pts[keep], W, H, intr, dist)   # the reference's statements
+        d, xyz, idx = O.distance_masks(cam, W, H, pts[keep])                          # the restatement
         pix = np.flatnonzero(idx.reshape(-1) >= 0).astype(np.int32)
+        assert np.array_equal(np.flatnonzero(rd.reshape(-1) > 0), pix), "oracle and reference fill different pixels"
+        assert np.array_equal(rd, d) and np.array_equal(rxyz, xyz), "oracle differs from the reference's generate_distance_masks"
         out[f"pix_{i}"] = pix                                            # filled pixels, ascending
-        out[f"index_{i}"] = keep[idx.reshape(-1)[pix]].astype(np.int32)  # winning point, as map index
-        out[f"dist_{i}"] = d.reshape(-1)[pix]
-        out[f"xyz_{i}"] = xyz.reshape(-1, 3)[pix]
-        print("distmask frame", i, "culled", len(keep), "pixels filled", len(pix))
+        out[f"index_{i}"] = keep[idx.reshape(-1)[pix]].astype(np.int32)  # winning point, as map index (extension, from the oracle)
+        out[f"dist_{i}"] = rd.reshape(-1)[pix]                           # from the reference
+        out[f"xyz_{i}"] = rxyz.reshape(-1, 3)[pix]                       # from the reference
+        print("distmask frame", i, "culled", len(keep), "pixels filled", len(pix), "reference lines", lines)
+    out["source"] = np.array(f"dist_*/xyz_* computed by {R.REFERENCE_SCRIPT}:{lines[0]}-{lines[1]} (method cut out with ast and executed); "
+                             "pix_*/index_* from oracle/pcp_oracle.cpp orc_distance_masks, checked to fill the same pixels")
     np.savez_compressed(os.path.join(HERE, "distmask_tiny.npz"), **out)
 
 

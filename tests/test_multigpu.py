@@ -25,8 +25,17 @@ def _run(gc, sc, frames, mask_frames):
         gc.submit_frame(sc["poses"][i], sc["images"][i], mask=sc["masks"][i] if i in mask_frames else None)
 
 
-def _results(gc, mode):
+def _results(gc, mode, exchange="allreduce"):
     from pointcloudprocessor_b200 import api
+    if exchange == "exchange_finalize":  # reduce-scatter + finalize of the slice + all-gather: colours, counts and masks of the job
+        rgb, cnt = gc.exchange_finalize()
+        mh, mm = gc.mask_accumulators()
+        if mode == api.ACCUM_SUM:
+            with pytest.raises(api.PcpError):
+                gc.accumulators()      # the sums were consumed (TOP5 mode falls back to all-reduce + finalize and keeps them)
+        with pytest.raises(api.PcpError):
+            gc.exchange_finalize()     # one exchange per pass
+        return dict(mh=mh, mm=mm, rgb=rgb, cnt=cnt)
     acc, mh, mm = gc.accumulators()
     rgb, cnt = gc.finalize()
     out = dict(mh=mh, mm=mm, rgb=rgb, cnt=cnt)
@@ -35,7 +44,7 @@ def _results(gc, mode):
     return out
 
 
-def _worker(rank, world, port, mode, sharding, out_dir):
+def _worker(rank, world, port, mode, sharding, exchange, out_dir):
     import torch
     import torch.distributed as dist
     from conftest import make_scene
@@ -60,15 +69,19 @@ def _worker(rank, world, port, mode, sharding, out_dir):
         # masks only on frames 0, 2, 4, ... of rank 0's share in the blocks case: rank 1 may then hold no mask accumulator at all
         mask_frames = set(range(0, N_FRAMES, 2)) if sharding == "interleaved" else set(frames_of_rank(N_FRAMES, 0, world, "blocks"))
         _run(gc, sc, mine, mask_frames)
-        gc.allreduce()
-        res = _results(gc, mode)
+        if exchange == "allreduce":
+            gc.allreduce()
+            with pytest.raises(api.PcpError):
+                gc.allreduce()         # a second exchange would double-count
+        res = _results(gc, mode, exchange)
     np.savez(os.path.join(out_dir, f"r{rank}.npz"), **res)
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("exchange", ["allreduce", "exchange_finalize"])
 @pytest.mark.parametrize("sharding", ["interleaved", "blocks"])
 @pytest.mark.parametrize("mode_name", ["sum", "top5"])
-def test_two_gpus_equal_one(tmp_path, built_lib, mode_name, sharding):
+def test_two_gpus_equal_one(tmp_path, built_lib, mode_name, sharding, exchange):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
@@ -77,7 +90,7 @@ def test_two_gpus_equal_one(tmp_path, built_lib, mode_name, sharding):
     from pointcloudprocessor_b200 import api
     from pointcloudprocessor_b200.shard import frames_of_rank
     mode = api.ACCUM_SUM if mode_name == "sum" else api.ACCUM_TOP5
-    mp.spawn(_worker, args=(2, _free_port(), mode, sharding, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), mode, sharding, exchange, str(tmp_path)), nprocs=2, join=True)
     sc = make_scene(N_POINTS, N_FRAMES, W, H, masks=True)
     mask_frames = set(range(0, N_FRAMES, 2)) if sharding == "interleaved" else set(frames_of_rank(N_FRAMES, 0, 2, "blocks"))
     with api.Colorizer(api.create_camera("pinhole", sc["intr"], sc["dist"]), api.default_params(image_size=(W, H), accum_mode=mode)) as gc:
@@ -88,4 +101,6 @@ def test_two_gpus_equal_one(tmp_path, built_lib, mode_name, sharding):
     for r in range(2):
         got = np.load(tmp_path / f"r{r}.npz")
         for k, v in ref.items():
+            if k not in got.files:
+                continue  # exchange_finalize hands back colours / counts / masks, not the sums
             assert np.array_equal(got[k], v), (r, k, int((got[k] != v).sum()))

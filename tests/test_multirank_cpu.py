@@ -55,7 +55,7 @@ def test_two_ranks_equal_one(tmp_path, oracle, mode):
 
 def test_sharding_is_a_partition():
     from pointcloudprocessor_b200.shard import frames_of_rank
-    for mode in ("interleaved", "blocks"):
+    for mode in ("interleaved", "blocks", "dealt"):
         for world in (1, 2, 3, 4, 8):
             for n in (0, 1, 7, 200):
                 got = sorted(sum((frames_of_rank(n, r, world, mode) for r in range(world)), []))

@@ -14,7 +14,7 @@ COLS = [
     ("gpu__time_duration.sum", "time us", 1.0),
     ("dram__bytes_read.sum", "dram rd MB", 1.0),
     ("dram__bytes_write.sum", "dram wr MB", 1.0),
-    ("dram__throughput.avg.pct_of_peak_sustained_elapsed", "dram %", 1.0),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram %", 1.0),
     ("smsp__inst_executed.sum", "warp inst", 1.0),
     ("sm__inst_issued.avg.pct_of_peak_sustained_active", "issue %", 1.0),
     ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps act %", 1.0),
@@ -53,6 +53,23 @@ def main(path, traffic_out=None):
         m = [x / n for x in s]
         print(f"| {k} | {n} | " + " | ".join(f"{x:.2f}" if x < 1e5 else f"{x:.3e}" for x in m) + " |")
         out[k] = {"dram_bytes_per_launch": (m[1] + m[2]) * 1e6, "time_us": m[0]}
+    # stall reasons: warps stalled per issue-active cycle, by reason (smsp__average_warps_issue_stalled_*_per_issue_active.ratio)
+    stall_cols = [h for h in hdr if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio") and "_not_issued" not in h]
+    if stall_cols:
+        sagg = collections.OrderedDict()
+        for d in data:
+            if len(d) != len(hdr):
+                continue
+            k = d[ix["Kernel Name"]].split("(")[0].replace("void ", "").replace("pcp::", "")
+            a = sagg.setdefault(k, [0, [0.0] * len(stall_cols)])
+            a[0] += 1
+            a[1] = [x + float(d[ix[c]].replace(",", "") or 0.0) for x, c in zip(a[1], stall_cols)]
+        print("\nStall reasons (warps stalled per issue-active cycle; the five largest per kernel):\n")
+        print("| kernel | " + " | ".join(f"reason {i + 1}" for i in range(5)) + " |")
+        print("|---|" + "---|" * 5)
+        for k, (n, s) in sagg.items():
+            m = sorted(((x / n, c[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]) for x, c in zip(s, stall_cols)), reverse=True)[:5]
+            print(f"| {k} | " + " | ".join(f"{nm} {v:.2f}" for v, nm in m) + " |")
     if traffic_out:
         scan = next((v for k, v in out.items() if k.startswith("scan")), None)
         doc = {"source": path, "kernels": out}
