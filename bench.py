@@ -300,10 +300,12 @@ def run_native(args):
     ex0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ex1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
 
-    def step_device(frames=mine, timed_step=None):
+    mine_poses = np.ascontiguousarray(poses_all[mine])
+    mine_ptrs = np.array([dimg(g) for g in mine], np.uint64)
+
+    def step_device(timed_step=None):
         gc.reset_accumulators()
-        for g in frames:
-            gc.submit_frame_device(poses_all[g], dimg(g), W * 3)
+        gc.submit_frames_device(mine_poses, mine_ptrs, W * 3)   # the keyframe loop in one call (same work as per-frame calls)
         if world > 1:
             if timed_step is not None:
                 gc.join()                      # the exchange interval starts when the last frame's kernels are done
@@ -446,10 +448,11 @@ def run_native(args):
             g1.set_cloud_device(d_cloud.data_ptr(), n)
             allf = list(range(F))
 
+            all_ptrs = np.array([dimg(g) for g in allf], np.uint64)
+
             def step_single():
                 g1.reset_accumulators()
-                for g in allf:
-                    g1.submit_frame_device(poses_all[g], dimg(g), W * 3)
+                g1.submit_frames_device(poses_all[allf], all_ptrs, W * 3)
                 g1.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
 
             step_single()
@@ -485,8 +488,7 @@ def run_native(args):
 
         def step_serial():
             gc1.reset_accumulators()
-            for g in mine:
-                gc1.submit_frame_device(poses_all[g], dimg(g), W * 3)
+            gc1.submit_frames_device(mine_poses, mine_ptrs, W * 3)
             gc1.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
 
         for _ in range(2 if n <= 20_000_000 else 1):

@@ -121,6 +121,12 @@ int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16,
 /* Same with device-resident image/mask (used to time the kernels with inputs already in HBM). */
 int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
                             const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out);
+/* The same loop body for n_frames device-resident images in one call: frame i takes poses7[7 i ..] and the image d_bgr[i] (a host
+ * array of device pointers; masks likewise when d_mask is not NULL).  Identical to n_frames calls of pcp_submit_frame_device
+ * without per-frame outputs; the per-call host overhead is paid once (tiny frames are bound by it).
+ * Replaces: the keyframe loop header, src/PointCloudProcessor.cpp:488-493. */
+int pcp_submit_frames_device(pcp_ctx* ctx, size_t n_frames, const double* poses7, const double* T_opt16, const uint8_t* const* d_bgr, size_t pitch,
+                             const uint8_t* const* d_mask, size_t mask_pitch);
 
 /* vlcal::ViewCulling::cull(points, T_camera_lidar) (include/vlcal/calib/view_culling.hpp:34, z-buffer variant
  * view_culling.cpp:52-174) on the context's cloud.  w2c16: optional float pre-transform
@@ -184,6 +190,11 @@ int pcp_set_frame_numbering(pcp_ctx* ctx, int next, int stride);
  * weighted mean. */
 int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out);
 
+/* smoothColors + removePointsWithNoColor (hpp:238-252) with the compaction on the device: only the points whose finalized colour is
+ * not (0,0,0), in the caller's point order, as pcl::PointXYZRGB payloads {x, y, z, b | g << 8 | r << 16 | 255 << 24} (16 bytes each).
+ * *n_out = their number; at most `cap` records are written to points_out (NULL: count only).  Synchronises. */
+int pcp_finalize_compact(pcp_ctx* ctx, void* points_out, size_t cap, size_t* n_out);
+
 /* Same as pcp_finalize with device-resident outputs (no host copy; asynchronous on the context's stream). */
 int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out);
 
@@ -232,7 +243,10 @@ typedef struct {
                                           * with enable_nid_optimize it is the initial guess instead of Identity */
   int skip_outputs;                    /* 1: compute everything but write no PCD (benchmarks) */
   int sample_mode;                     /* PCP_SAMPLE_NEAREST (reference) | PCP_SAMPLE_BILINEAR */
-  int reserved[9];
+  int binary_output;                   /* 0 (reference, cpp:920 / :939 / :954): cloudInWorldWithRGB.pcd is written as ASCII; 1: DATA binary (PCL's
+                                        * writeBinary layout of pcl::PointXYZRGB: x y z rgb, 16 bytes per point) — at 1e8 points the text file is
+                                        * the wall time of process() */
+  int reserved[8];
 } pcp_process_args;
 
 typedef struct {
@@ -254,6 +268,9 @@ int pcp_process(const pcp_process_args* args, pcp_process_stats* stats, char* er
  * pcp_image_read: 8-bit image, grayscale != 0 -> 1 channel, else 3 channels B,G,R; JPEG is decoded with nvJPEG (needs a GPU). */
 int pcp_pcd_read_xyzi(const char* path, float** xyzi_out, size_t* n_out);
 int pcp_pcd_write_xyzi(const char* path, const float* xyzi, size_t n);
+/* saveColorizedPointCloud (cpp:912-923) from 16-byte pcl::PointXYZRGB payloads {x, y, z, b | g << 8 | r << 16 | a << 24} as
+ * pcp_finalize_compact delivers them; binary = 0: pcl::io::savePCDFileASCII's layout, 1: pcl::io::savePCDFileBinary's. */
+int pcp_pcd_write_xyzrgb(const char* path, const void* points16, size_t n, int binary);
 int pcp_image_read(const char* path, int grayscale, uint8_t** data_out, int* width, int* height, int* channels);
 void pcp_io_free(void* p);
 

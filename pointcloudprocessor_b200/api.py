@@ -190,6 +190,16 @@ class Colorizer:
             return {"n_candidates": int(out.n_candidates), "n_visible": int(out.n_visible), "n_colored": int(out.n_colored)}
         return None
 
+    def submit_frames_device(self, poses7, d_bgr_ptrs, pitch: int, T_opt=None, d_mask_ptrs=None, mask_pitch: int = 0):
+        """The keyframe loop over device-resident images in one call (frame i: poses7[i], image pointer d_bgr_ptrs[i])."""
+        poses = np.ascontiguousarray(poses7, np.float64).reshape(-1, 7)
+        ptrs = np.ascontiguousarray(d_bgr_ptrs, np.uint64)
+        assert ptrs.shape[0] == poses.shape[0]
+        mptrs = None if d_mask_ptrs is None else np.ascontiguousarray(d_mask_ptrs, np.uint64)
+        T = self._mat16(T_opt)
+        rc = self._L.pcp_submit_frames_device(self._h, poses.shape[0], _ptr(poses), _ptr(T), _ptr(ptrs), pitch, _ptr(mptrs), mask_pitch)
+        self._check(rc, "pcp_submit_frames_device")
+
     def set_cloud_ptr(self, host_ptr: int, n: int, stride: int = 16, intensity_offset: int = 12):
         """set_cloud from a raw (e.g. pinned) host pointer."""
         self._check(self._L.pcp_set_cloud(self._h, C.c_void_p(host_ptr), n, stride, intensity_offset), "pcp_set_cloud")
@@ -261,6 +271,17 @@ class Colorizer:
         cnt = np.empty(self.n, np.uint32) if want_count else None
         self._check(self._L.pcp_finalize(self._h, _ptr(rgb), _ptr(cnt)), "pcp_finalize")
         return (rgb, cnt) if want_count else rgb
+
+    def finalize_compact(self) -> np.ndarray:
+        """smoothColors + removePointsWithNoColor with the compaction on the device: structured array of the coloured points
+        (x, y, z float32, b, g, r, a uint8 = pcl::PointXYZRGB's 16 bytes) in the caller's point order."""
+        dt = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), ("g", "u1"), ("r", "u1"), ("a", "u1")])
+        m = C.c_size_t(0)
+        self._check(self._L.pcp_finalize_compact(self._h, None, 0, C.byref(m)), "pcp_finalize_compact")
+        out = np.empty(m.value, dt)
+        if m.value:
+            self._check(self._L.pcp_finalize_compact(self._h, _ptr(out), m.value, C.byref(m)), "pcp_finalize_compact")
+        return out
 
     def finalize_device(self, d_rgb: int, d_count: int = 0):
         self._check(self._L.pcp_finalize_device(self._h, C.c_void_p(d_rgb or 0), C.c_void_p(d_count or 0)), "pcp_finalize_device")
@@ -349,7 +370,7 @@ class PointCloudProcessor:
 
     def __init__(self, pointCloudPath, odometryPath, imagesFolder, maskImageFolder="", outputPath=".", enableMLS=False, enableNIDOptimize=False,
                  enableInitialGuessManual=False, camera: Camera | None = None, cull_size=None, T_camera_lidar_optimized=None, device=0,
-                 skip_outputs=False, sample_mode=SAMPLE_NEAREST):
+                 skip_outputs=False, sample_mode=SAMPLE_NEAREST, binary_output=False):
         self._keep = [str(pointCloudPath).encode(), str(odometryPath).encode(), str(imagesFolder).encode(), str(maskImageFolder or "").encode(),
                       str(outputPath).encode()]
         a = _capi.ProcessArgs()
@@ -367,6 +388,7 @@ class PointCloudProcessor:
             a.T_camera_lidar_optimized = self._T.ctypes.data_as(C.POINTER(C.c_double))
         a.skip_outputs = int(skip_outputs)
         a.sample_mode = int(sample_mode)
+        a.binary_output = int(binary_output)  # cloudInWorldWithRGB.pcd as DATA binary instead of the reference's ASCII
         self._args = a
         self.stats = None
 

@@ -108,11 +108,13 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   const size_t cells = (size_t)ctx->Wc * ctx->Hc;
   if ((e = cudaMalloc(&ctx->d_zgrid, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zgrid", e);
   if ((e = cudaMalloc(&ctx->d_zprev, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMalloc zprev", e);
-  // index words 0xffffffff: no seed point before a slot's first frame
-  if ((e = cudaMemset(ctx->d_zgrid, 0xff, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMemset zgrid", e);
-  if ((e = cudaMemset(ctx->d_zprev, 0xff, sizeof(unsigned long long) * pcp_ctx::kMaxFlight * (cells ? cells : 1))) != cudaSuccess) return bail("cudaMemset zprev", e);
-  if ((e = cudaMalloc(&ctx->d_counters, pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
-  if ((e = cudaMemset(ctx->d_counters, 0, pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMemset counters", e);
+  if ((e = cudaMalloc(&ctx->d_counters, 2 * pcp_ctx::kMaxFlight * sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+  // every grid empty (FLT_MAX, index 0xffffffff: no seed point before a slot's first frame), every counter block zero
+  for (int i = 0; i < pcp_ctx::kMaxFlight; i++) {
+    launch_zgrid_init(ctx->d_zgrid + (size_t)i * (cells ? cells : 1), (int)cells, ctx->d_counters + 2 * i, ctx->stream);
+    launch_zgrid_init(ctx->d_zprev + (size_t)i * (cells ? cells : 1), (int)cells, ctx->d_counters + 2 * i + 1, ctx->stream);
+  }
+  if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return bail("z-grid set-up", e);
   if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();

@@ -64,15 +64,18 @@ struct pcp_ctx {
   struct FrameSlot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_done = nullptr;
+    int parity = 0;               // which of the slot's two z-grids / counter blocks the next frame uses
   };
   FrameSlot fs[kMaxFlight];
   int flight = 3;                 // frames in flight (pcp_params.frames_in_flight)
   uint64_t frames_run = 0;        // frames submitted since creation (slot = frames_run % flight)
   int last_slot = 0;              // slot of the last submitted frame
+  int last_counters = 0;          // index of its counter block in d_counters
   cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
-  unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys
-  unsigned long long* d_zprev = nullptr;       // kMaxFlight x Wc*Hc: the final z-grid of the slot's previous frame (seed points)
-  pcp::FrameCounters* d_counters = nullptr;    // kMaxFlight entries
+  unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys: grid 0 of every slot
+  unsigned long long* d_zprev = nullptr;       // kMaxFlight x Wc*Hc: grid 1 of every slot (frames of a slot alternate; the other grid
+                                               // holds the previous frame's final state = the seed points)
+  pcp::FrameCounters* d_counters = nullptr;    // 2 x kMaxFlight entries (slot, parity)
   pcp::FrameCounters* h_counters = nullptr;  // pinned
   uint32_t* d_total = nullptr;
 

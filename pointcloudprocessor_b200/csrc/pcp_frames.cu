@@ -107,11 +107,18 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
     ctx->prof_used += 4;
   }
   const int cells = ctx->Wc * ctx->Hc;
-  unsigned long long* zg = ctx->d_zgrid + (size_t)si * (cells ? cells : 1);
-  FrameCounters* ctr = ctx->d_counters + si;
+  // two z-grids and counter blocks per slot: this frame's pair was cleared by the slot's previous frame (or at set-up), the other
+  // pair holds that frame's final grid (the seed points) and is cleared by this frame's classify_kernel for the next one
+  const size_t c1 = cells ? cells : 1;
+  const int par = ctx->fs[si].parity;
+  unsigned long long* zg = (par ? ctx->d_zprev : ctx->d_zgrid) + (size_t)si * c1;
+  unsigned long long* zp = (par ? ctx->d_zgrid : ctx->d_zprev) + (size_t)si * c1;
+  FrameCounters* ctr = ctx->d_counters + 2 * si + par;
+  FrameCounters* ctr_next = ctx->d_counters + 2 * si + (par ^ 1);
   Record* recs = ctx->d_records + (size_t)si * ((ctx->n ? ctx->n : 1) + 64);
-  unsigned long long* zp = (ctx->use_seed && ctx->d_zprev) ? ctx->d_zprev + (size_t)si * (cells ? cells : 1) : nullptr;
-  launch_zgrid_init(zg, zp, cells, ctr, st);  // this slot's z-grid and counters (overlaps the other slots' kernels)
+  const bool binned = ctx->d_perm != nullptr;
+  if (binned) ctx->fs[si].parity ^= 1;
+  else launch_zgrid_init(zg, cells, ctr, st);  // unbinned path: no classify_kernel, the grid is cleared per frame
   if (pe) CU(cudaEventRecord(pe[1], st));
   ScanArgs sa;
   std::memset(&sa, 0, sizeof(sa));
@@ -121,17 +128,20 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.active = ctx->d_active ? ctx->d_active + (size_t)si * ctx->n_chunks : nullptr;
   sa.n_chunks = ctx->n_chunks;
   sa.order = ctx->d_order;
-  sa.seed_blocks = (zp && fp.depth_culling && ctx->d_perm) ? (cells + 255) / 256 : 0;
+  sa.seed_blocks = binned ? ((cells > 16 ? cells : 16) + 255) / 256 : 0;
+  sa.counters_next = ctr_next;
+  sa.seed = (ctx->use_seed && fp.depth_culling) ? 1 : 0;
   sa.zgrid = zg;
   sa.zprev = zp;
   sa.cells = cells;
   sa.records = recs;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
-  if (launch_scan(sa, fp, ctx->scan_grid, count_candidates, ctx->device, st) != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
+  if (launch_scan(sa, fp, ctx->scan_grid, ctx->sm_count, count_candidates, ctx->device, st) != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
   if (pe) CU(cudaEventRecord(pe[2], st));
-  // the resolve kernels update the accumulators without atomics: they run in frame order
-  if (ctx->last_done && ctx->flight > 1) CU(cudaStreamWaitEvent(st, ctx->last_done, 0));
+  // TOP5 slot lists are read-modify-write: those resolve kernels run in frame order.  SUM accumulators are updated with
+  // atomics (integer sums commute): frames on different slots are fully independent.
+  if (ctx->last_done && ctx->flight > 1 && ctx->prm.accum_mode != PCP_ACCUM_SUM) CU(cudaStreamWaitEvent(st, ctx->last_done, 0));
   if (img_ready) CU(cudaStreamWaitEvent(st, img_ready, 0));
 
   ResolveArgs ra;
@@ -161,15 +171,16 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   if (img_free) CU(cudaEventRecord(img_free, st));
   ctx->last_done = slot.ev_done;
   ctx->last_slot = si;
+  ctx->last_counters = 2 * si + par;
   ctx->frames_run++;
-  ctx->launches += ctx->d_perm ? 4 : 3;
+  ctx->launches += 3;  // classify + scan + resolve, or clear + scan + resolve (unbinned)
   CU(cudaGetLastError());
   return PCP_OK;
 }
 
 int fetch_outputs(pcp_ctx* ctx, pcp_frame_out* out) {
   CU(ctx->join());
-  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters + ctx->last_slot, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(ctx->h_counters, ctx->d_counters + ctx->last_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->visible_bits) CU(cudaMemcpyAsync(out->visible_bits, ctx->d_vis_bits, sizeof(uint32_t) * ((ctx->n + 31) / 32), cudaMemcpyDeviceToHost, ctx->stream));
   if (out->pixel_index) CU(cudaMemcpyAsync(out->pixel_index, ctx->d_pix, sizeof(int32_t) * ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
@@ -218,6 +229,20 @@ extern "C" {
 int pcp_submit_frame_device(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* d_bgr, size_t pitch,
                             const uint8_t* d_mask, size_t mask_pitch, pcp_frame_out* out) {
   return submit_device(ctx, pose7, T_opt16, d_bgr, pitch, d_mask, mask_pitch, out, nullptr, nullptr);
+}
+
+/* The keyframe loop (cpp:488-595) over device-resident images in one call: frame i uses poses7[7 i .. 7 i + 6] and the image
+ * d_bgr[i] (mask d_mask[i] when d_mask is not null).  Same work and results as n_frames calls of pcp_submit_frame_device without
+ * per-frame outputs; only the per-call host overhead is paid once. */
+int pcp_submit_frames_device(pcp_ctx* ctx, size_t n_frames, const double* poses7, const double* T_opt16, const uint8_t* const* d_bgr, size_t pitch,
+                             const uint8_t* const* d_mask, size_t mask_pitch) {
+  if (!ctx) return PCP_EINVAL;
+  if (n_frames && (!poses7 || !d_bgr)) { ctx->fail("pcp_submit_frames_device: null argument"); return PCP_EINVAL; }
+  for (size_t i = 0; i < n_frames; i++) {
+    const int rc = submit_device(ctx, poses7 + 7 * i, T_opt16, d_bgr[i], pitch, d_mask ? d_mask[i] : nullptr, mask_pitch, nullptr, nullptr, nullptr);
+    if (rc != PCP_OK) return rc;
+  }
+  return PCP_OK;
 }
 
 int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* bgr, size_t pitch,
@@ -382,7 +407,7 @@ int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]) {
   if (!ctx || !out16) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   CU(ctx->drain());
-  CU(cudaMemcpy(out16, ctx->d_counters + ctx->last_slot, 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  CU(cudaMemcpy(out16, ctx->d_counters + ctx->last_counters, 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
   return PCP_OK;
 }
 
@@ -422,6 +447,53 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
   else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
   ctx->launches++;
   CU(cudaGetLastError());
+  return PCP_OK;
+}
+
+/* smoothColors + removePointsWithNoColor (cpp:604-631, hpp:238-252) with the compaction on the device: the coloured points only, as
+ * pcl::PointXYZRGB payloads {x, y, z, b | g << 8 | r << 16 | 255 << 24} (16 bytes), in the caller's point order.
+ * `*n_out` receives their number; at most `cap` records are written (call with points_out = NULL to learn the number first). */
+int pcp_finalize_compact(pcp_ctx* ctx, void* points_out, size_t cap, size_t* n_out) {
+  if (!ctx || !n_out) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->d_acc) { ctx->fail("no cloud"); return PCP_EINVAL; }
+  if (ctx->acc_scattered) { ctx->fail("pcp_finalize_compact: the accumulators were consumed by pcp_exchange_finalize"); return PCP_EINVAL; }
+  const size_t n = ctx->n;
+  *n_out = 0;
+  if (n == 0) return PCP_OK;
+  if (ctx->out_points < n) {
+    if (ctx->d_out_rgb) { cudaFree(ctx->d_out_rgb); ctx->d_out_rgb = nullptr; }
+    if (ctx->d_out_cnt) { cudaFree(ctx->d_out_cnt); ctx->d_out_cnt = nullptr; }
+    CU(cudaMalloc(&ctx->d_out_rgb, n * 3));
+    CU(cudaMalloc(&ctx->d_out_cnt, n * sizeof(uint32_t)));
+    ctx->out_points = n;
+  }
+  int rc = pcp_finalize_device(ctx, ctx->d_out_rgb, nullptr);
+  if (rc != PCP_OK) return rc;
+  if (!ctx->d_vis_bits) CU(cudaMalloc(&ctx->d_vis_bits, sizeof(uint32_t) * ((n + 31) / 32)));
+  if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n));
+  if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)n)));
+  launch_coloured_bits(ctx->d_out_rgb, (uint32_t)n, ctx->d_vis_bits, ctx->stream);
+  launch_compact_bits(ctx->d_vis_bits, (uint32_t)n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
+  uint32_t total = 0;
+  CU(cudaMemcpyAsync(&total, ctx->d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->launches += 4;
+  *n_out = total;
+  if (!points_out || total == 0) return PCP_OK;
+  const uint32_t m = (uint32_t)(total < cap ? total : cap);
+  if (m == 0) return PCP_OK;
+  // the 16-byte records are staged in the (idle) count buffer when they fit, else in a temporary
+  uint4* d_pts = nullptr;
+  bool own = false;
+  if ((size_t)m * sizeof(uint4) <= n * sizeof(uint32_t)) d_pts = reinterpret_cast<uint4*>(ctx->d_out_cnt);
+  else { CU(cudaMalloc(&d_pts, (size_t)m * sizeof(uint4))); own = true; }
+  launch_gather_coloured(ctx->d_idx, m, ctx->d_cloud, ctx->d_perm ? ctx->d_inv : nullptr, ctx->d_out_rgb, d_pts, ctx->stream);
+  ctx->launches++;
+  cudaError_t e = cudaMemcpyAsync(points_out, d_pts, (size_t)m * sizeof(uint4), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (own) cudaFree(d_pts);
+  if (e != cudaSuccess) { ctx->fail("pcp_finalize_compact: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
   return PCP_OK;
 }
 

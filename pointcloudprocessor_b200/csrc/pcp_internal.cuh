@@ -78,7 +78,10 @@ struct ScanArgs {
   uint4* active;                      // pre-binned: {chunk id, ChunkInfo rect, org, d2lo bits} of the chunks worth processing this frame
   uint32_t n_chunks;                  // ceil(n / kChunk)
   unsigned long long* zgrid;          // Wc*Hc packed keys
-  const unsigned long long* zprev;    // the slot's previous final z-grid (its index words name the seed points), or null
+  unsigned long long* zprev;          // pre-binned: the slot's other z-grid = the previous frame's final grid (its index words name the
+                                      // seed points); classify_kernel clears it for the slot's next frame
+  FrameCounters* counters_next;       // pre-binned: the counter block of the slot's next frame (cleared by classify_kernel)
+  int seed;                           // 1: the previous frame's winners go through the exact path first
   int cells;                          // Wc*Hc
   Record* records;
   FrameCounters* counters;
@@ -105,8 +108,8 @@ struct ResolveArgs {
   int sample_mode;
 };
 
-void launch_zgrid_init(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters, cudaStream_t s);
-int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, int device, cudaStream_t s);
+void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s);
+int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, int sm_count, bool count_candidates, int device, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
 void launch_finalize_sum(const uint4* acc, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
@@ -124,6 +127,9 @@ void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,
                          uint32_t* d_total, cudaStream_t s);
 size_t compact_scratch_words(uint32_t n);
+// removePointsWithNoColor on the device: coloured-point bitmask, then the gather of {x, y, z, packed bgra} records (pcp_kernels.cu)
+void launch_coloured_bits(const uint8_t* rgb, uint32_t n, uint32_t* bits, cudaStream_t s);
+void launch_gather_coloured(const int32_t* idx, uint32_t m, const float4* cloud, const uint32_t* inv, const uint8_t* rgb, uint4* out, cudaStream_t s);
 // distance / 3-D point masks of a frame from the resolve kernel's pixel indices (pcp_splat.cu); `winner` = imgW*imgH zeroed u64 words
 void launch_splat(const int32_t* pix, const uint32_t* perm, uint32_t n, const float4* cloud, const FrameParams& fp, unsigned long long* winner,
                   float* dist, float* xyz, int32_t* index, unsigned int* n_filled, int sm_count, cudaStream_t s);

@@ -194,6 +194,7 @@ inline bool write_pcd_xyzi(const std::string& path, const XYZI* pts, size_t n) {
 inline bool write_pcd_xyzrgb(const std::string& path, const XYZRGB* pts, size_t n) {
   FILE* f = std::fopen(path.c_str(), "wb");
   if (!f) return false;
+  std::setvbuf(f, nullptr, _IOFBF, 1 << 22);
   pcd_header(f, "x y z rgb", "4 4 4 4", "F F F U", "1 1 1 1", n);
   char line[160];
   for (size_t i = 0; i < n; i++) {
@@ -204,6 +205,17 @@ inline bool write_pcd_xyzrgb(const std::string& path, const XYZRGB* pts, size_t 
     std::fwrite(line, 1, (size_t)o, f);
   }
   return std::fclose(f) == 0;
+}
+// pcl::PCDWriter::writeBinary<pcl::PointXYZRGB> (opt-in, pcp_process_args.binary_output): the header generateHeader emits for the
+// point type (rgb stays the float field it is registered as) and the fields of every point packed without padding.
+inline bool write_pcd_xyzrgb_binary(const std::string& path, const XYZRGB* pts, size_t n) {
+  static_assert(sizeof(XYZRGB) == 16, "pcl::PointXYZRGB payload");
+  FILE* f = std::fopen(path.c_str(), "wb");
+  if (!f) return false;
+  std::fprintf(f, "# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z rgb\nSIZE 4 4 4 4\nTYPE F F F F\nCOUNT 1 1 1 1\nWIDTH %zu\nHEIGHT 1\n"
+                  "VIEWPOINT 0 0 0 1 0 0 0\nPOINTS %zu\nDATA binary\n", n, n);
+  const bool ok = n == 0 || std::fwrite(pts, sizeof(XYZRGB), n, f) == n;
+  return (std::fclose(f) == 0) && ok;
 }
 inline bool write_pcd_xyzrgbmask(const std::string& path, const XYZRGBMask* pts, size_t n) {
   FILE* f = std::fopen(path.c_str(), "wb");

@@ -59,21 +59,19 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-// Also hands the grid the slot's previous frame ended with to `zprev`: its index words name that frame's nearest point of
-// every cell, which classify_kernel sends through the exact path before anything else (seed points).
-__global__ void zgrid_init_kernel(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters) {
+// Clears a z-grid and a counter block.  Frames of a pre-binned cloud do not need it per frame: every frame slot owns TWO grids and
+// counter blocks, and classify_kernel of frame k clears the pair frame k + 1 of the slot will use while it reads the seed points out
+// of it (see classify_kernel).  Used at set-up, and per frame by the unbinned path.
+__global__ void zgrid_init_kernel(unsigned long long* zgrid, int cells, FrameCounters* counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   pdl_launch_dependents();
-  if (i < cells) {
-    if (zprev) zprev[i] = zgrid[i];
-    zgrid[i] = kZInit;
-  }
+  if (i < cells) zgrid[i] = kZInit;
   if (i < (int)(sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(counters)[i] = 0u;
 }
 
-void launch_zgrid_init(unsigned long long* zgrid, unsigned long long* zprev, int cells, FrameCounters* counters, cudaStream_t s) {
+void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s) {
   const int n = cells > 32 ? cells : 32;
-  zgrid_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(zgrid, zprev, cells, counters);
+  zgrid_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(zgrid, cells, counters);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -237,20 +235,24 @@ __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const _
   const int lane = threadIdx.x & 31;
   unsigned int ncand = 0;
   pdl_launch_dependents();  // the scan kernel's CTAs may take their places (they wait for this grid before reading its list)
-  pdl_wait();               // zgrid_init_kernel's grid, counters and seed copy
-  // Seed points.  The point that was nearest in a cell of this slot's previous frame is very likely near the front of the
-  // new view too (consecutive keyframes are centimetres apart).  Sending those <= Wc*Hc points through the exact path FIRST
+  pdl_wait();               // the previous kernel of the stream (the slot's previous frame, or the set-up)
+  // The first seed_blocks CTAs own one cell each of the slot's OTHER z-grid: the grid the slot's previous frame ended with, and
+  // the one its next frame will start from.  Each thread reads its cell's winner, puts the cell back to "empty", and — seed
+  // points — sends that winner through the exact path of THIS frame first.  The point that was nearest in a cell of the previous
+  // frame is very likely near the front of the new view too (consecutive keyframes are centimetres apart), and processing it first
   // is nothing but a different processing order (the final grid is min over all in-grid candidates whatever the order,
   // SURVEY.md 3.4), but the scan kernel then starts against minima that are already close to final: more chunks fail the
-  // distance test without being loaded and fewer points reach the FP64 stage or leave a record.  Seeds emit no record and
-  // are not counted; the scan kernel meets the same points again in their chunks.  A stale or foreign index (first frame
-  // of a slot, new cloud) names some other point of the cloud, which is just as valid.  The seeds have their own CTAs (the
-  // first seed_blocks of the grid), so that their chain of dependent accesses runs beside the chunk classification.
+  // distance test without being loaded and fewer points reach the FP64 stage or leave a record.  Seeds emit no record and are not
+  // counted; the scan kernel meets the same points again in their chunks.  A stale or foreign index (first frame of a slot, new
+  // cloud) names some other point of the cloud, which is just as valid.  The same CTAs clear the next frame's counter block, so a
+  // frame is three launches (classify, scan, resolve) with no separate clearing kernel.
   if ((int)blockIdx.x < a.seed_blocks) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < (int)(sizeof(FrameCounters) / sizeof(unsigned int))) reinterpret_cast<unsigned int*>(a.counters_next)[c] = 0u;
     if (c < a.cells) {
-      const uint32_t pos = (uint32_t)__ldcg(a.zprev + c);  // index word = position in the (sorted) cloud (written by zgrid_init_kernel while this CTA may already have been resident: L2 load)
-      if (pos < a.n) {
+      const uint32_t pos = (uint32_t)__ldcg(a.zprev + c);  // index word = position in the (sorted) cloud
+      a.zprev[c] = kZInit;
+      if (a.seed && pos < a.n) {
         const float4 p = __ldg(a.cloud + pos);
         float x = p.x, y = p.y, z = p.z;
         if (fp.use_w2c) transform_point(fp.w2c, p.x, p.y, p.z, x, y, z);
@@ -274,14 +276,21 @@ __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const _
       if (kCount && cls == kChunkAllCandidates) ncand += (unsigned int)a1.w;
     }
   }
+  // one global atomic per CTA (same-address atomics serialise in L2: one per warp was 4.9 k of them at C2)
+  __shared__ unsigned int s_cnt[8], s_base;
   const unsigned int m = __ballot_sync(0xffffffffu, cls == kChunkProcess);
-  if (m) {
-    unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(&a.counters->n_active_blocks, (unsigned int)__popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (cls == kChunkProcess)
-      a.active[base + __popc(m & ((1u << lane) - 1u))] = make_uint4(chunk, info.rect, info.org, __float_as_uint(info.d2lo));
+  const int warp = threadIdx.x >> 5;
+  if (lane == 0) s_cnt[warp] = (unsigned int)__popc(m);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) { const unsigned int c = s_cnt[w]; s_cnt[w] = tot; tot += c; }
+    s_base = tot ? atomicAdd(&a.counters->n_active_blocks, tot) : 0u;
   }
+  __syncthreads();
+  if (cls == kChunkProcess)
+    a.active[s_base + s_cnt[warp] + __popc(m & ((1u << lane) - 1u))] = make_uint4(chunk, info.rect, info.org, __float_as_uint(info.d2lo));
   if (kCount) {
     for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
     if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
@@ -704,7 +713,10 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
 // one global atomic each, which evens out the end of the launch (chunk costs differ by orders of magnitude).
 // ---------------------------------------------------------------------------------------------------------------------
 #ifndef PCP_AHEAD
-#define PCP_AHEAD 24
+#define PCP_AHEAD 16
+#endif
+#ifndef PCP_POLL_NS
+#define PCP_POLL_NS 100
 #endif
 #ifndef PCP_POOL_PCT
 #define PCP_POOL_PCT 30
@@ -712,7 +724,14 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
 #ifndef PCP_POOL_BATCH
 #define PCP_POOL_BATCH 16
 #endif
-static constexpr int kWorkers = kWarpsPerCta - 1;       // warps 0 .. kWorkers-1 work, warp kWorkers scouts
+#ifndef PCP_RING_THREADS
+#define PCP_RING_THREADS 256
+#endif
+#ifndef PCP_RING_CTAS
+#define PCP_RING_CTAS 4
+#endif
+static constexpr int kRingThreads = PCP_RING_THREADS;
+static constexpr int kWorkers = kRingThreads / 32 - 1;  // warps 0 .. kWorkers-1 work, warp kWorkers scouts
 static constexpr int kWorkCap = 128;                    // work-ring entries (power of two, >= kAhead + 32 + kWorkers)
 static constexpr int kAhead = PCP_AHEAD;                // the scout tests at most this many chunks ahead of the tickets taken
 static constexpr int kPoolPct = PCP_POOL_PCT;           // share of the active list handed out dynamically
@@ -734,7 +753,7 @@ __device__ __forceinline__ void sts_volatile_v2(uint2* p, uint2 v) {
 }
 
 template <bool kCount>
-__global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_ring_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+__global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
   extern __shared__ __align__(128) unsigned char ring_smem[];
   __shared__ __align__(8) uint64_t s_bar[kWorkers][2];  // completion of the bulk copy into buffer b of worker w
   __shared__ __align__(8) uint2 s_work[kWorkCap];       // {chunk id, ticket number} or {_, kWorkFree}
@@ -775,15 +794,28 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_ring_kernel(
       // stay close to the workers: a test against minima that are kAhead chunks old skips less
       while ((int)(count - *(volatile unsigned int*)&s_ticket) > kAhead) __nanosleep(64);
       bool skip = false;
-      if (valid && ent.y != 0u) {
-        const int w = (int)(ent.y & 63u), h = (int)((ent.y >> 6) & 63u);
-        const unsigned int* row = zhi + 2 * ((int)(ent.z >> 16) * fp.Wc + (int)(ent.z & 0xffffu));
+      // The rectangles hold <= 32 cells.  Every lane walks ITS entry's cells eight at a time with independent loads (one L2 round
+      // trip per eight cells for the whole batch of 32 entries): this loop is what bounds how fast a scout can feed seven workers.
+      const int w = (int)(ent.y & 63u), wh = valid ? w * (int)((ent.y >> 6) & 63u) : 0;
+      const int wh_max = __reduce_max_sync(0xffffffffu, wh);
+      if (wh > 0) {
+        const unsigned int* org = zhi + 2 * ((int)(ent.z >> 16) * fp.Wc + (int)(ent.z & 0xffffu));
+        // c / w == (c * inv_w) >> 16 for c < 32, w <= 32 with inv_w = ceil(65536 / w) (+1 at most from the approximate division:
+        // the quotient c / w lies >= 1/32 below the next integer, the error of the product is < 2 * 32 / 65536)
+        const unsigned int inv_w = (unsigned int)__float2int_ru(__fdividef(65536.0f, (float)w));
         unsigned int m = 0u;  // max over the rectangle of (minimum + tol)^2 rounded up, as bits (non-negative floats order like their bits)
-        for (int cy = 0; cy < h; cy++, row += 2 * fp.Wc) {
-#pragma unroll 4
-          for (int cx = 0; cx < w; cx++) {
-            const float lim = __fadd_ru(__uint_as_float(PCP_ZLOAD0(row + 2 * cx)), fp.pre.tol_up);
-            m = max(m, __float_as_uint(__fmul_ru(lim, lim)));
+        for (int c0 = 0; c0 < wh_max; c0 += 8) {
+          unsigned int zb[8];
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const int c = c0 + k;
+            const int cy = (int)(((unsigned int)c * inv_w) >> 16), cx = c - cy * w;
+            zb[k] = c < wh ? PCP_ZLOAD0(org + 2 * (cy * fp.Wc + cx)) : 0u;
+          }
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const float lim = __fadd_ru(__uint_as_float(zb[k]), fp.pre.tol_up);
+            if (c0 + k < wh) m = max(m, __float_as_uint(__fmul_ru(lim, lim)));
           }
         }
         skip = __uint_as_float(ent.w) > __uint_as_float(m);  // the whole chunk is farther than every cell it can fall into
@@ -876,7 +908,7 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_ring_kernel(
           const uint2 v = lds_volatile_v2(e);
           if (v.y == t) { chunk = v.x; sts_volatile_v2(e, make_uint2(0u, kWorkFree)); break; }
           if (t >= s_total) break;  // the scout is done and never issued this ticket
-          __nanosleep(32);
+          __nanosleep(PCP_POLL_NS);
         }
         if (chunk != kWorkFree) {
           const uint32_t b0 = chunk * kChunk;
@@ -982,8 +1014,10 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
-int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_candidates, int device, cudaStream_t s) {
+int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, int sm_count, bool count_candidates, int device, cudaStream_t s) {
   if (a.aabb) {
+    const int rgrid = sm_count * PCP_RING_CTAS;  // one persistent CTA per resident slot
+    (void)rgrid;
     const int cgrid = a.seed_blocks + (int)((a.n_chunks + 255) / 256);
     // the opt-in to > 48 KB of dynamic shared memory is a per-device attribute: one flag per device, not per process
     static bool configured[64] = {};
@@ -1005,11 +1039,11 @@ int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, bool count_c
     else scan_binned_kernel<false><<<grid, kScanThreads, kBinnedSmem, s>>>(a, fp);
 #else
 #ifdef PCP_NO_PDL_SCAN
-    if (count_candidates) scan_ring_kernel<true><<<grid, kScanThreads, kRingSmem, s>>>(a, fp);
-    else scan_ring_kernel<false><<<grid, kScanThreads, kRingSmem, s>>>(a, fp);
+    if (count_candidates) scan_ring_kernel<true><<<rgrid, kRingThreads, kRingSmem, s>>>(a, fp);
+    else scan_ring_kernel<false><<<rgrid, kRingThreads, kRingSmem, s>>>(a, fp);
 #else
-    if (count_candidates) e = launch_pdl(scan_ring_kernel<true>, dim3(grid), dim3(kScanThreads), kRingSmem, s, a, fp);
-    else e = launch_pdl(scan_ring_kernel<false>, dim3(grid), dim3(kScanThreads), kRingSmem, s, a, fp);
+    if (count_candidates) e = launch_pdl(scan_ring_kernel<true>, dim3(rgrid), dim3(kRingThreads), kRingSmem, s, a, fp);
+    else e = launch_pdl(scan_ring_kernel<false>, dim3(rgrid), dim3(kRingThreads), kRingSmem, s, a, fp);
     if (e != cudaSuccess) return 1;
 #endif
 #endif
@@ -1112,6 +1146,10 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
     uint32_t rgb[kRes], mv[kRes];
     uint4 s[kRes];
     const bool gather = a.bgr != nullptr;
+    // SUM accumulators are updated with no-return atomics (RED.ADD.U32): integer sums commute, so frames in flight on different
+    // slots need no ordering between their resolve kernels and the accumulator is never read here.  TOP5 inserts are
+    // read-modify-write on sorted lists: those frames stay ordered (the caller chains their resolve kernels) and keep plain stores.
+    const bool ordered = a.accum_mode != 0;
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       hi[k] = 0u; rgb[k] = 0u; mv[k] = 0u; s[k] = make_uint4(0u, 0u, 0u, 0u);
@@ -1122,7 +1160,7 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
         const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
         rgb[k] = (uint32_t)__ldg(px + 2) | ((uint32_t)__ldg(px + 1) << 8) | ((uint32_t)__ldg(px) << 16);  // r | g<<8 | b<<16 (cpp:760-762)
         if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);  // cpp:804
-        s[k] = a.acc[idx[k]];
+        if (ordered) s[k] = a.acc[idx[k]];
       }
     }
     if (fp.depth_culling) {
@@ -1147,7 +1185,7 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
           const uint8_t* px = a.bgr + (size_t)pv * a.pitch + (size_t)pu * 3;
           rgb[k] = (uint32_t)__ldg(px + 2) | ((uint32_t)__ldg(px + 1) << 8) | ((uint32_t)__ldg(px) << 16);
           if (a.mask) mv[k] = __ldg(a.mask + (size_t)pv * a.mask_pitch + pu);
-          s[k] = a.acc[idx[k]];
+          if (ordered) s[k] = a.acc[idx[k]];
         }
       }
       live[k] = pix[k] >= 0;
@@ -1156,19 +1194,23 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
       if (a.pix_out) a.pix_out[orig] = pix[k];
     }
     if (!gather) continue;
-    // a point appears at most once per frame, so the accumulator update needs no atomics
 #pragma unroll
     for (int k = 0; k < kRes; k++) {
       if (!live[k]) continue;
+      uint32_t ar, ag, ab;
       if (a.sample_mode == 0) {
-        s[k].x += rgb[k] & 255u; s[k].y += (rgb[k] >> 8) & 255u; s[k].z += rgb[k] >> 16; s[k].w += 1u;
+        ar = rgb[k] & 255u; ag = (rgb[k] >> 8) & 255u; ab = rgb[k] >> 16;
       } else {
-        uint32_t qr, qg, qb;
-        bilinear_sample(a.bgr, a.pitch, fp, a.records + (base + k * blockDim.x + threadIdx.x), pix[k], qr, qg, qb);
-        s[k].x += qr; s[k].y += qg; s[k].z += qb; s[k].w += 1u;
-        rgb[k] = min((qr + 128u) >> 8, 255u) | (min((qg + 128u) >> 8, 255u) << 8) | (min((qb + 128u) >> 8, 255u) << 16);  // TOP5 lists
+        bilinear_sample(a.bgr, a.pitch, fp, a.records + (base + k * blockDim.x + threadIdx.x), pix[k], ar, ag, ab);
+        rgb[k] = min((ar + 128u) >> 8, 255u) | (min((ag + 128u) >> 8, 255u) << 8) | (min((ab + 128u) >> 8, 255u) << 16);  // TOP5 lists
       }
-      a.acc[idx[k]] = s[k];
+      if (ordered) {  // a point appears at most once per frame and TOP5 frames are ordered: plain read-modify-write
+        s[k].x += ar; s[k].y += ag; s[k].z += ab; s[k].w += 1u;
+        a.acc[idx[k]] = s[k];
+      } else {
+        unsigned int* w = reinterpret_cast<unsigned int*>(a.acc + idx[k]);
+        atomicAdd(w, ar); atomicAdd(w + 1, ag); atomicAdd(w + 2, ab); atomicAdd(w + 3, 1u);
+      }
       if (a.accum_mode != 0) {
         const Record* rp = a.records + (base + k * blockDim.x + threadIdx.x);
         const float rx = rp->x, ry = rp->y, rz = rp->z;
@@ -1177,10 +1219,16 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
         top_insert(a, idx[k], final_score(o, d), rgb[k], (uint32_t)fp.frame_index);
       }
       if (a.mask) {
-        uint2 m = a.mask_acc[idx[k]];
-        m.x += (mv[k] == 255u) ? 1u : 0u;                                    // cpp:806
-        m.y = mv[k] > m.y ? mv[k] : m.y;
-        a.mask_acc[idx[k]] = m;
+        unsigned int* mw = reinterpret_cast<unsigned int*>(a.mask_acc + idx[k]);
+        if (ordered) {
+          uint2 m = a.mask_acc[idx[k]];
+          m.x += (mv[k] == 255u) ? 1u : 0u;                                  // cpp:806
+          m.y = mv[k] > m.y ? mv[k] : m.y;
+          a.mask_acc[idx[k]] = m;
+        } else {
+          if (mv[k] == 255u) atomicAdd(mw, 1u);                              // cpp:806
+          if (mv[k]) atomicMax(mw + 1, mv[k]);
+        }
       }
     }
   }
@@ -1395,6 +1443,43 @@ void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offset
   compact_tile_sums<<<tiles, 256, 0, s>>>(bits, words, tile_sums);
   compact_scan_tiles<<<1, 1024, 0, s>>>(tile_sums, tiles, d_total);
   compact_scatter<<<tiles, kTileWords, 0, s>>>(bits, words, n, tile_sums, idx_out);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// removePointsWithNoColor (include/PointCloudProcessor.hpp:238-252) on the device: bit i = the finalized colour of point i is not
+// (0,0,0); the ascending index list comes from launch_compact_bits; the survivors are gathered as pcl::PointXYZRGB payloads
+// {x, y, z, b | g << 8 | r << 16 | 255 << 24}, 16 bytes each, in the caller's point order.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void coloured_bits_kernel(const uint8_t* __restrict__ rgb, uint32_t n, uint32_t* __restrict__ bits) {
+  const uint32_t words = (n + 31) / 32;
+  for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < words; w += gridDim.x * blockDim.x) {
+    uint32_t m = 0;
+    for (uint32_t b = 0; b < 32; b++) {
+      const uint32_t i = w * 32 + b;
+      if (i < n && (rgb[3 * (size_t)i] | rgb[3 * (size_t)i + 1] | rgb[3 * (size_t)i + 2])) m |= 1u << b;
+    }
+    bits[w] = m;
+  }
+}
+__global__ void gather_coloured_kernel(const int32_t* __restrict__ idx, uint32_t m, const float4* __restrict__ cloud, const uint32_t* __restrict__ inv,
+                                       const uint8_t* __restrict__ rgb, uint4* __restrict__ out) {
+  for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < m; k += gridDim.x * blockDim.x) {
+    const uint32_t i = (uint32_t)idx[k];
+    const float4 p = cloud[inv ? inv[i] : i];  // the device copy of the cloud is in sorted order
+    const uint32_t r = rgb[3 * (size_t)i], g = rgb[3 * (size_t)i + 1], b = rgb[3 * (size_t)i + 2];
+    out[k] = make_uint4(__float_as_uint(p.x), __float_as_uint(p.y), __float_as_uint(p.z), b | (g << 8) | (r << 16) | (255u << 24));
+  }
+}
+void launch_coloured_bits(const uint8_t* rgb, uint32_t n, uint32_t* bits, cudaStream_t s) {
+  if (n == 0) return;
+  const uint32_t words = (n + 31) / 32;
+  const int grid = (words + 255) / 256 < 148 * 16 ? (words + 255) / 256 : 148 * 16;
+  coloured_bits_kernel<<<grid, 256, 0, s>>>(rgb, n, bits);
+}
+void launch_gather_coloured(const int32_t* idx, uint32_t m, const float4* cloud, const uint32_t* inv, const uint8_t* rgb, uint4* out, cudaStream_t s) {
+  if (m == 0) return;
+  const int grid = (m + 255) / 256 < 148 * 16 ? (m + 255) / 256 : 148 * 16;
+  gather_coloured_kernel<<<grid, 256, 0, s>>>(idx, m, cloud, inv, rgb, out);
 }
 
 }  // namespace pcp

@@ -60,7 +60,7 @@ bool load_image(const std::string& path, bool grey, HostImage& im, std::string& 
   } else if (file[0] == 'P') {
     ok = io::decode_pnm(file, im);
   } else {
-    ok = io::decode_png(file, im);
+    ok = io::decode_png(file, im, grey);
   }
   if (!ok) { if (why.empty()) why = "unsupported or corrupt image"; return false; }
   if (grey) io::to_grey(im); else io::to_bgr(im);
@@ -300,11 +300,19 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
       check(ctx, pcp_hsv_roundtrip(ctx, h_img[sb], (size_t)W * 3, h_img[sb], (size_t)W * 3, W, H, prm.saturation_scale, prm.brightness_scale),
             "pcp_hsv_roundtrip");
       HostImage m;
-      if (load_image(kf->mask_path, true, m, why) && m.width == W && m.height == H) {
+      why.clear();
+      if (load_image(kf->mask_path, true, m, why)) {
+        if (m.width != W || m.height != H)
+          throw ProcError(PCP_EIO, "mask image " + kf->mask_path + " is " + std::to_string(m.width) + "x" + std::to_string(m.height) + ", the camera image " +
+                                       std::to_string(W) + "x" + std::to_string(H));
         std::memcpy(h_msk[sb], m.data.data(), (size_t)W * H);
         have_mask = true;
+      } else if (why == "cannot open") {
+        std::fprintf(stdout, "Failed to read image from: %s\n", kf->mask_path.c_str());  // cpp:776-781: the file is missing: log and carry on without the mask
       } else {
-        std::fprintf(stdout, "Failed to read image from: %s\n", kf->mask_path.c_str());  // cpp:776-781: log and carry on without the mask
+        // the file is there but this build cannot decode it: cv::imread would have read it, so going on without the mask would silently
+        // drop <ts>_rgb-mask.pcd and the mask cloud.  Fail with the path instead.
+        throw ProcError(PCP_EIO, "Failed to decode mask image: " + kf->mask_path + " (" + why + ")");
       }
     }
     pcp_frame_out fo;
@@ -346,12 +354,14 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
     write_s += now_s() - tw;
   }
   // smoothColors + removePointsWithNoColor (cpp:604-631, hpp:238-252)
-  std::vector<uint8_t> rgb(N * 3);
-  check(ctx, pcp_finalize(ctx, rgb.data(), nullptr), "pcp_finalize");
+  // the compaction runs on the device (pcp_finalize_compact): only the coloured points cross the host link, already in
+  // pcl::PointXYZRGB's 16-byte layout and in the map's point order
   std::vector<io::XYZRGB> colored;
-  for (size_t i = 0; i < N; i++) {
-    const uint8_t r = rgb[3 * i], g = rgb[3 * i + 1], b = rgb[3 * i + 2];
-    if (r != 0 || g != 0 || b != 0) colored.push_back(io::XYZRGB{cloud[i].x, cloud[i].y, cloud[i].z, b, g, r, 255});
+  {
+    size_t m = 0;
+    check(ctx, pcp_finalize_compact(ctx, nullptr, 0, &m), "pcp_finalize_compact");
+    colored.resize(m);
+    if (m) check(ctx, pcp_finalize_compact(ctx, colored.data(), m, &m), "pcp_finalize_compact");
   }
   S.n_colored_points = (int64_t)colored.size();
   S.seconds_color_pass = now_s() - t_col - write_s;
@@ -362,7 +372,8 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
     if (masks_on && !world_mask_cloud.empty() &&
         !io::write_pcd_xyzrgbmask(out_path + "cloudInWorldWithRGBandMask.pcd", world_mask_cloud.data(), world_mask_cloud.size()))
       throw ProcError(PCP_EIO, "Couldn't save colorized and segment colored point cloud.");  // cpp:941
-    if (!colored.empty() && !io::write_pcd_xyzrgb(out_path + "cloudInWorldWithRGB.pcd", colored.data(), colored.size()))
+    if (!colored.empty() && !(A.binary_output ? io::write_pcd_xyzrgb_binary(out_path + "cloudInWorldWithRGB.pcd", colored.data(), colored.size())
+                                              : io::write_pcd_xyzrgb(out_path + "cloudInWorldWithRGB.pcd", colored.data(), colored.size())))
       throw ProcError(PCP_EIO, "Couldn't save colorized point cloud.");  // cpp:922, :956
   }
   S.seconds_write = write_s + (now_s() - tw);
@@ -424,6 +435,12 @@ extern "C" int pcp_image_read(const char* path, int grayscale, uint8_t** data_ou
   *data_out = out;
   *width = im.width; *height = im.height; *channels = im.channels;
   return PCP_OK;
+}
+
+extern "C" int pcp_pcd_write_xyzrgb(const char* path, const void* points16, size_t n, int binary) {
+  if (!path || (!points16 && n)) return PCP_EINVAL;
+  const pcp::io::XYZRGB* p = static_cast<const pcp::io::XYZRGB*>(points16);
+  return (binary ? pcp::io::write_pcd_xyzrgb_binary(path, p, n) : pcp::io::write_pcd_xyzrgb(path, p, n)) ? PCP_OK : PCP_EIO;
 }
 
 extern "C" void pcp_io_free(void* p) { std::free(p); }

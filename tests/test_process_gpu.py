@@ -203,3 +203,41 @@ def test_cli_matches_library(built_lib, tmp_path):
     assert len(names) > 8
     for nme in names:
         assert (out_dir / nme).read_bytes() == (out2 / nme).read_bytes(), nme
+
+
+def test_binary_output_and_device_compaction(built_lib, tmp_path):
+    """cloudInWorldWithRGB.pcd as DATA binary (pcl::PCDWriter::writeBinary's layout of pcl::PointXYZRGB, opt-in) holds the points the
+    ASCII file holds (positions to the 8 digits the text keeps, colours exactly), and pcp_finalize_compact == finalize + the host-side
+    removePointsWithNoColor (hpp:238-252)."""
+    from pointcloudprocessor_b200 import api
+    W, H = 330, 240
+    sc, frames, img_dir, mask_dir, out_dir = _dataset(tmp_path, W=W, H=H, masks=False)
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    args = (tmp_path / "scans.pcd", tmp_path / "odom.txt", str(img_dir) + "/", "")
+    api.PointCloudProcessor(*args, str(out_dir) + "/", camera=cam, cull_size=(W, H)).process()
+    out2 = tmp_path / "out_bin"
+    out2.mkdir()
+    st = api.PointCloudProcessor(*args, str(out2) + "/", camera=cam, cull_size=(W, H), binary_output=True).process()
+    raw = (out2 / "cloudInWorldWithRGB.pcd").read_bytes()
+    k = raw.index(b"DATA binary\n") + len(b"DATA binary\n")
+    hdr = raw[:k].decode()
+    assert "FIELDS x y z rgb\nSIZE 4 4 4 4\nTYPE F F F F\nCOUNT 1 1 1 1\n" in hdr and f"POINTS {st['n_colored_points']}\n" in hdr
+    rec = np.frombuffer(raw[k:], np.dtype([("xyz", "<f4", 3), ("bgra", "u1", 4)]))
+    assert len(rec) == st["n_colored_points"] > 100
+    fields, rows = _read_ascii_pcd(out_dir / "cloudInWorldWithRGB.pcd")
+    arr = np.array(rows)
+    assert len(rows) == len(rec)
+    assert np.array_equal(arr[:, :3].astype(np.float32), _f8(rec["xyz"]))
+    u = arr[:, 3].astype(np.uint64)
+    assert np.array_equal(np.stack([u & 255, (u >> 8) & 255, (u >> 16) & 255, u >> 24], axis=1).astype(np.uint8), rec["bgra"])
+    # the compaction itself, against finalize + a host filter
+    with api.Colorizer(cam, api.default_params(image_size=(W, H))) as gc:
+        gc.set_cloud(sc["cloud"])
+        for i, pose in enumerate(sc["poses"]):
+            gc.submit_frame(pose, sc["images"][i])
+        rgb, _ = gc.finalize()
+        pts = gc.finalize_compact()
+    keep = np.nonzero(rgb.any(axis=1))[0]
+    assert len(pts) == len(keep) > 100
+    assert np.array_equal(np.stack([pts["x"], pts["y"], pts["z"]], axis=1), sc["cloud"][keep, :3])
+    assert np.array_equal(np.stack([pts["r"], pts["g"], pts["b"]], axis=1), rgb[keep]) and np.all(pts["a"] == 255)

@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--sample", default="nearest", choices=["nearest", "bilinear"])
     ap.add_argument("--tag", default="")
+    ap.add_argument("--per-frame-calls", action="store_true", help="one pcp_submit_frame_device call per frame instead of the loop call")
     a = ap.parse_args()
     n, f, W, H = synth.CONFIGS[a.workload]
     n = a.points or n
@@ -51,10 +52,15 @@ def main():
         gc.set_stream(stream.cuda_stream)
         gc.set_cloud_device(cloud.data_ptr(), n)
 
+        ptrs = np.array([d_imgs.data_ptr() + i * ib for i in range(f)], np.uint64)
+
         def step():
             gc.reset_accumulators()
-            for i in range(f):
-                gc.submit_frame_device(poses[i], d_imgs.data_ptr() + i * ib, W * 3)
+            if a.per_frame_calls:
+                for i in range(f):
+                    gc.submit_frame_device(poses[i], d_imgs.data_ptr() + i * ib, W * 3)
+            else:
+                gc.submit_frames_device(poses[:f], ptrs, W * 3)
 
         for _ in range(2):
             step()
