@@ -516,7 +516,7 @@ def run_native(args):
         pipe_gbs = pipe_bytes / (frame_ms * 1e-3) / 1e9 if frame_ms > 0 else 0.0
         ms_step_rank = ms / args.steps
         roofline = {
-            "bound": "hbm", "kernel": "classify_kernel + scan_binned_kernel (pass 1)" if dominant == "scan" else dominant, "achieved": scan_gbs, "peak": peak,
+            "bound": "hbm", "kernel": "classify_kernel + scan_ring_kernel (pass 1)" if dominant == "scan" else dominant, "achieved": scan_gbs, "peak": peak,
             "unit": "GB/s", "frac": scan_gbs / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": scan_bytes,
             "kernel_ms_per_frame": kern_ms, "kernel_share_of_frame": {k: v / frame_ms for k, v in kern_ms.items()} if frame_ms > 0 else None,
             "pipeline": {"algorithmic_bytes_per_frame": pipe_bytes, "f_vis": f_vis, "achieved": pipe_gbs, "frac": pipe_gbs / peak},

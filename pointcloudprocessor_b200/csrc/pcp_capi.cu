@@ -193,9 +193,16 @@ int pcp_pose_matrices(const double pose7[7], const double* T_opt16, float w2c16[
 // ---------------------------------------------------------------------------------------------------------------------
 // cloud
 // ---------------------------------------------------------------------------------------------------------------------
+// ctx->stream waits for the frames of EVERY slot: SUM frames on different slots are independent of each other (their resolve
+// kernels are not chained), so the last submitted frame's event says nothing about the other slots.
 cudaError_t pcp_ctx::join() {
   if (!last_done) return cudaSuccess;
-  return cudaStreamWaitEvent(stream, last_done, 0);
+  for (int i = 0; i < kMaxFlight; i++) {
+    if (!fs[i].used) continue;
+    const cudaError_t e = cudaStreamWaitEvent(stream, fs[i].ev_done, 0);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t pcp_ctx::drain() {

@@ -65,6 +65,7 @@ struct pcp_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_done = nullptr;
     int parity = 0;               // which of the slot's two z-grids / counter blocks the next frame uses
+    bool used = false;            // ev_done has been recorded at least once
   };
   FrameSlot fs[kMaxFlight];
   int flight = 3;                 // frames in flight (pcp_params.frames_in_flight)

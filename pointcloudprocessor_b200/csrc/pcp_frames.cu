@@ -168,6 +168,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   launch_resolve(ra, fp, ctx->resolve_grid, st);
   if (pe) CU(cudaEventRecord(pe[3], st));
   CU(cudaEventRecord(slot.ev_done, st));
+  slot.used = true;
   if (img_free) CU(cudaEventRecord(img_free, st));
   ctx->last_done = slot.ev_done;
   ctx->last_slot = si;

@@ -98,6 +98,29 @@ def test_async_pipeline_matches_oracle(oracle, built_lib):
         assert np.array_equal(acc_g, acc_o) and np.array_equal(mh_g, mh_o) and np.array_equal(mm_g, mm_o)
 
 
+def test_frames_in_flight_are_all_joined(built_lib):
+    """A small cloud with several frames in flight and no per-frame outputs: SUM frames on different slots are independent, so
+    reading the accumulators must wait for every slot, not only for the last submitted frame (bench C1 caught that race)."""
+    from pointcloudprocessor_b200 import api
+    W, H = 1280, 720
+    sc = make_scene(1_000_000, 12, W, H)
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    accs = {}
+    for flight in (1, 3):
+        with api.Colorizer(cam, api.default_params(image_size=(W, H), frames_in_flight=flight)) as gc:
+            gc.set_cloud(sc["cloud"])
+            for rep in range(4):
+                gc.reset_accumulators()
+                for i, pose in enumerate(sc["poses"]):
+                    gc.submit_frame(pose, sc["images"][i])
+                acc, _, _ = gc.accumulators()
+                rgb, cnt = gc.finalize()
+                if flight == 1 and rep == 0:
+                    accs["acc"], accs["rgb"], accs["cnt"] = acc, rgb, cnt
+                assert np.array_equal(acc, accs["acc"]) and np.array_equal(rgb, accs["rgb"]) and np.array_equal(cnt, accs["cnt"]), (flight, rep)
+    assert accs["cnt"].sum() > 10_000
+
+
 def test_tiny_masks(oracle, built_lib):
     _run_pair(oracle, make_scene(20_000, 3, 320, 240, masks=True), masks=True)
 

@@ -71,10 +71,11 @@ def main(path, traffic_out=None):
             m = sorted(((x / n, c[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]) for x, c in zip(s, stall_cols)), reverse=True)[:5]
             print(f"| {k} | " + " | ".join(f"{nm} {v:.2f}" for v, nm in m) + " |")
     if traffic_out:
-        scan = next((v for k, v in out.items() if k.startswith("scan")), None)
+        pass1 = [v for k, v in out.items() if k.startswith("scan") or k.startswith("classify")]  # pass 1 = classify + scan
         doc = {"source": path, "kernels": out}
-        if scan:
-            doc["scan_kernel_dram_bytes_per_launch"] = scan["dram_bytes_per_launch"]
+        if pass1:
+            doc["scan_kernel_dram_bytes_per_launch"] = sum(v["dram_bytes_per_launch"] for v in pass1)
+            doc["source_note"] = "profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum per frame of classify_kernel + scan kernel, from " + path
         json.dump(doc, open(traffic_out, "w"), indent=1)
 
 
