@@ -195,6 +195,21 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out);
  * *n_out = their number; at most `cap` records are written to points_out (NULL: count only).  Synchronises. */
 int pcp_finalize_compact(pcp_ctx* ctx, void* points_out, size_t cap, size_t* n_out);
 
+/* pcp_compact_bits_noalloc — NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Bitmask -> ascending index list (the order of ViewCulling::sample's output), i.e. the compaction inside pcp_cull, with its
+ * scratch in a file-scope static __device__ array instead of a context-owned buffer: the call allocates NOTHING (no cudaMalloc,
+ * cudaFree or allocating library routine).  All pointers are DEVICE pointers owned by the caller:
+ *   d_bits       ceil(n_bits / 32) words, bit i of word i / 32 set = element i is kept (the layout of pcp_frame_out.visible_bits)
+ *   d_idx_out    room for as many int32 as bits are set (n_bits is always enough): the set positions, ascending
+ *   d_count_out  one u32: the number of set bits (always written)
+ * Asynchronous on the context's stream.  Limit: n_bits <= PCP_NOALLOC_MAX_BITS, larger sizes return PCP_EINVAL with a message
+ * (the static scratch is 16.6 KB per GPU, held until the process exits).  Every call on a device shares that scratch: calls
+ * that overlap on the GPU (other streams or contexts of the same device) race — serialise them.  The first call on a device
+ * resolves the scratch's device address (cudaGetSymbolAddress); make it once outside a graph capture. */
+#define PCP_NOALLOC_MAX_BITS (1ull << 27)
+int pcp_compact_bits_noalloc(pcp_ctx* ctx, const uint32_t* d_bits, size_t n_bits, int32_t* d_idx_out, uint32_t* d_count_out);
+
 /* Same as pcp_finalize with device-resident outputs (no host copy; asynchronous on the context's stream). */
 int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out);
 

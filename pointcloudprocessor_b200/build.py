@@ -12,7 +12,7 @@ import sys
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libpcp_b200.so")
-SOURCES = ["pcp_kernels.cu", "pcp_capi.cu", "pcp_frames.cu", "pcp_nid.cu", "pcp_nccl.cu", "pcp_prebin.cu", "pcp_image.cu", "pcp_jpeg.cu", "pcp_process.cu", "pcp_calib.cu", "pcp_splat.cu"]
+SOURCES = ["pcp_kernels.cu", "pcp_capi.cu", "pcp_frames.cu", "pcp_nid.cu", "pcp_nccl.cu", "pcp_prebin.cu", "pcp_image.cu", "pcp_jpeg.cu", "pcp_process.cu", "pcp_calib.cu", "pcp_splat.cu", "pcp_noalloc.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
