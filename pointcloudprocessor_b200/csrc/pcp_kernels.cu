@@ -1208,8 +1208,11 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
         s[k].x += ar; s[k].y += ag; s[k].z += ab; s[k].w += 1u;
         a.acc[idx[k]] = s[k];
       } else {
-        unsigned int* w = reinterpret_cast<unsigned int*>(a.acc + idx[k]);
-        atomicAdd(w, ar); atomicAdd(w + 1, ag); atomicAdd(w + 2, ab); atomicAdd(w + 3, 1u);
+        // {sum_r, sum_g} and {sum_b, count} as two 64-bit words: one no-return RED.ADD.64 each adds both halves at once (a half
+        // cannot carry into its neighbour before the 32-bit sum itself would have wrapped)
+        unsigned long long* w = reinterpret_cast<unsigned long long*>(a.acc + idx[k]);
+        atomicAdd(w, (unsigned long long)ar | ((unsigned long long)ag << 32));
+        atomicAdd(w + 1, (unsigned long long)ab | (1ull << 32));
       }
       if (a.accum_mode != 0) {
         const Record* rp = a.records + (base + k * blockDim.x + threadIdx.x);
