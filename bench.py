@@ -363,11 +363,23 @@ def run_native(args):
     prof = gc.profile_read()
     gc.profile_enable(False)
     clocks = sampler.stop() if sampler else None
+    ms_rank = ms
     ms = max_over_ranks(ms)
     value = n * F * args.steps / (ms * 1e-3)
-    exchange_ms = None
+    exchange_ms = exchange_min = exchange_mean = None
     if world > 1:
-        exchange_ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in zip(ex0, ex1)) / args.steps)
+        mine_ex = sum(a.elapsed_time(b) for a, b in zip(ex0, ex1)) / args.steps
+        exchange_ms = max_over_ranks(mine_ex)
+        # the rank that arrives LAST waits for nobody: the minimum over ranks is the cost of the exchange itself, the rest of the
+        # maximum is time spent waiting for slower ranks (frame-cost imbalance between the shards)
+        t = torch.tensor([mine_ex, -mine_ex, mine_ex], device="cuda", dtype=torch.float64)
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        exchange_min, exchange_mean = -float(tmax[1].item()), float(tsum[2].item()) / world
+        frames_mine = ms_rank / args.steps - mine_ex      # this rank's frames alone (its step minus its exchange interval)
+        t2 = torch.tensor([frames_mine, -frames_mine], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        frames_max, frames_min = float(t2[0].item()), -float(t2[1].item())
 
     # ---- e2e: host buffers through the C ABI --------------------------------------------------------------------------
     e2e_steps = max(1, min(args.steps, 10 if n <= 20_000_000 else 3))
@@ -546,7 +558,7 @@ def run_native(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if strong and world > 1 else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": cfg,
             "host": {"affinity": (f"rank bound to the {numa} CPUs NVML lists for its GPU" if numa else "unbound"), "threads": threads},
-            "frames_in_flight": int(prm.frames_in_flight), "frames_per_rank": f,
+            "frames_in_flight": (int(prm.frames_in_flight) or "auto (6 for clouds <= 4e6 points, else 3)"), "frames_per_rank": f,
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "colours_equal_device_path": e2e_matches_device},
@@ -554,7 +566,10 @@ def run_native(args):
         }
         if exchange_ms is not None:
             line["exchange"] = {"ms_per_step": exchange_ms, "what": "reduce-scatter of the u32 sums (16 B/point), finalize of the rank's slice, all-gather of colours + counts (8 B/point); "
-                                "CUDA events around it on the launching stream, max over ranks", "share_of_step": exchange_ms / (ms / args.steps)}
+                                "CUDA events around it on the launching stream, max over ranks", "share_of_step": exchange_ms / (ms / args.steps),
+                                "ms_min_over_ranks": exchange_min, "ms_mean_over_ranks": exchange_mean,
+                                "frames_ms_per_step_min_max_over_ranks": [frames_min, frames_max],
+                                "note": "min over ranks = the exchange itself (the last rank to arrive waits for nobody); max - min = waiting for slower ranks"}
         if single is not None:
             line["single_gpu_same_workload"] = single
         if cpu is not None:

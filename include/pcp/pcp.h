@@ -51,7 +51,7 @@ typedef struct {
   int prebin;                      /* 1 (default): Morton-sort the device copy of the cloud into 64-point chunks with bounding
                                     * boxes at set_cloud; chunks certainly behind the camera / outside the z-grid are skipped per
                                     * frame.  Every output stays in the caller's point order.  0: keep the caller's order. */
-  int frames_in_flight;            /* 1..3 (0 = default 3): frames run on that many internal streams, each with its own z-grid / record
+  int frames_in_flight;            /* 1..6; 0 (default) = chosen per cloud: 6 for clouds of <= 4e6 points, else 3.  Frames run on that many internal streams, each with its own z-grid / record
                                     * scratch, so that the scan of frame f+1 overlaps the tail of frame f and its resolve pass.
                                     * Accumulator updates stay in frame order; results do not depend on this value. */
   int hsv_adjust;                  /* 1: pcp_submit_frame applies generateColorMap's 8-bit BGR->HSV->BGR round trip (cpp:722-741) to the
@@ -224,6 +224,14 @@ int pcp_profile_read(pcp_ctx* ctx, double ms3[3], uint64_t* frames);
  * visual_camera_calibration.cpp:173), row-major. */
 int pcp_nid_create(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const double* image,
                    int width, int height, int bins, pcp_nid** out);
+/* The same cost from the 8-bit image itself (visual_camera_calibration.cpp:171-173: imread, then convertTo(CV_64FC1, 1.0 / 255.0)):
+ * `image` is a host plane of `height` rows of `width` bytes, `pitch` bytes apart.  The conversion to [0,1] doubles and the binning
+ * happen on the device (the cost uses a pixel only through its bin, a function of the byte: results equal pcp_nid_create on
+ * double(byte) * (1.0 / 255.0) bit for bit) and 8x fewer bytes cross the host link.  Grey plane: pitch = width.  The reference's
+ * actual read (a 3-channel CV_64FC3 image indexed with at<double>(y, x), x < cols: the first `cols` interleaved B,G,R values of every
+ * row, nid_cost.hpp:61, :88) is image = the BGR image, pitch = 3 * width. */
+int pcp_nid_create_u8(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const uint8_t* image,
+                      size_t pitch, int width, int height, int bins, pcp_nid** out);
 void pcp_nid_destroy(pcp_nid* nid);
 /* NIDCost::operator()<double> for B candidate poses at once.  se3: B x 7 doubles in Sophus order
  * {qx,qy,qz,qw,tx,ty,tz}; nid_out: B doubles; ok_out: B bytes, 0 where the reference returns false
@@ -258,10 +266,12 @@ typedef struct {
                                           * with enable_nid_optimize it is the initial guess instead of Identity */
   int skip_outputs;                    /* 1: compute everything but write no PCD (benchmarks) */
   int sample_mode;                     /* PCP_SAMPLE_NEAREST (reference) | PCP_SAMPLE_BILINEAR */
+  int nid_grey_plane;                  /* 0 (reference): the NID cost reads the image as NIDCost does, the first `cols` interleaved B,G,R values of
+                                        * every row (nid_cost.hpp:61, :88); 1: the grey image a single-channel read would have seen */
   int binary_output;                   /* 0 (reference, cpp:920 / :939 / :954): cloudInWorldWithRGB.pcd is written as ASCII; 1: DATA binary (PCL's
                                         * writeBinary layout of pcl::PointXYZRGB: x y z rgb, 16 bytes per point) — at 1e8 points the text file is
                                         * the wall time of process() */
-  int reserved[8];
+  int reserved[7];
 } pcp_process_args;
 
 typedef struct {

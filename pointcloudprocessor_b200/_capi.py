@@ -44,7 +44,7 @@ class ProcessArgs(C.Structure):
         ("point_cloud_path", C.c_char_p), ("odometry_path", C.c_char_p), ("images_folder", C.c_char_p), ("mask_image_folder", C.c_char_p),
         ("output_path", C.c_char_p), ("enable_mls", C.c_int), ("enable_nid_optimize", C.c_int), ("enable_initial_guess_manual", C.c_int),
         ("device", C.c_int), ("camera", C.POINTER(Camera)), ("cull_width", C.c_int), ("cull_height", C.c_int),
-        ("T_camera_lidar_optimized", C.POINTER(C.c_double)), ("skip_outputs", C.c_int), ("sample_mode", C.c_int), ("binary_output", C.c_int), ("reserved", C.c_int * 8),
+        ("T_camera_lidar_optimized", C.POINTER(C.c_double)), ("skip_outputs", C.c_int), ("sample_mode", C.c_int), ("nid_grey_plane", C.c_int), ("binary_output", C.c_int), ("reserved", C.c_int * 7),
     ]
 
 
@@ -65,7 +65,7 @@ SYMBOLS = [
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
     "pcp_bfgs_default_options", "pcp_se3_bfgs", "pcp_calib_default_params", "pcp_calibrate", "pcp_set_frame_numbering", "pcp_splat_masks_pose",
-    "pcp_join", "pcp_exchange_finalize", "pcp_exchange_finalize_device", "pcp_finalize_compact", "pcp_pcd_write_xyzrgb", "pcp_submit_frames_device", "pcp_compact_bits_noalloc",
+    "pcp_join", "pcp_exchange_finalize", "pcp_exchange_finalize_device", "pcp_finalize_compact", "pcp_pcd_write_xyzrgb", "pcp_submit_frames_device", "pcp_compact_bits_noalloc", "pcp_nid_create_u8",
 ]
 class BfgsOptions(C.Structure):
     _fields_ = [
@@ -150,6 +150,7 @@ def load():
     L.pcp_profile_enable.argtypes = [vp, i32]
     L.pcp_profile_read.argtypes = [vp, vp, vp]
     L.pcp_nid_create.argtypes = [vp, vp, sz, sz, sz, vp, i32, i32, i32, C.POINTER(vp)]
+    L.pcp_nid_create_u8.argtypes = [vp, vp, sz, sz, sz, vp, sz, i32, i32, i32, C.POINTER(vp)]
     L.pcp_nid_destroy.argtypes = [vp]
     L.pcp_nid_destroy.restype = None
     L.pcp_nid_eval.argtypes = [vp, vp, i32, vp, vp]

@@ -370,7 +370,7 @@ class PointCloudProcessor:
 
     def __init__(self, pointCloudPath, odometryPath, imagesFolder, maskImageFolder="", outputPath=".", enableMLS=False, enableNIDOptimize=False,
                  enableInitialGuessManual=False, camera: Camera | None = None, cull_size=None, T_camera_lidar_optimized=None, device=0,
-                 skip_outputs=False, sample_mode=SAMPLE_NEAREST, binary_output=False):
+                 skip_outputs=False, sample_mode=SAMPLE_NEAREST, binary_output=False, nid_grey_plane=False):
         self._keep = [str(pointCloudPath).encode(), str(odometryPath).encode(), str(imagesFolder).encode(), str(maskImageFolder or "").encode(),
                       str(outputPath).encode()]
         a = _capi.ProcessArgs()
@@ -388,6 +388,7 @@ class PointCloudProcessor:
             a.T_camera_lidar_optimized = self._T.ctypes.data_as(C.POINTER(C.c_double))
         a.skip_outputs = int(skip_outputs)
         a.sample_mode = int(sample_mode)
+        a.nid_grey_plane = int(nid_grey_plane)
         a.binary_output = int(binary_output)  # cloudInWorldWithRGB.pcd as DATA binary instead of the reference's ASCII
         self._args = a
         self.stats = None
@@ -438,12 +439,22 @@ class NIDCost:
     def __init__(self, ctx: Colorizer, normalized_image: np.ndarray, points: np.ndarray, bins: int = 16):
         self._ctx = ctx
         self._L = ctx._L
-        img = np.ascontiguousarray(normalized_image, np.float64)
-        if img.ndim != 2:
-            raise PcpError("NIDCost: normalized_image must be a single-channel HxW float64 plane")
         pts = np.ascontiguousarray(points, np.float32)
         ioff = 12 if pts.shape[1] == 4 else 16
         self._h = C.c_void_p()
+        if normalized_image.dtype == np.uint8:
+            # the 8-bit image itself (pcp_nid_create_u8): HxW grey plane, or HxWx3 B,G,R read the way NIDCost reads it (the first W
+            # interleaved values of every row, nid_cost.hpp:61, :88); converted to [0,1] and binned on the device
+            img = np.ascontiguousarray(normalized_image)
+            if img.ndim not in (2, 3):
+                raise PcpError("NIDCost: uint8 image must be HxW or HxWx3")
+            rc = self._L.pcp_nid_create_u8(ctx.handle, _ptr(pts), pts.shape[0], pts.shape[1] * 4, ioff, _ptr(img), img.strides[0], img.shape[1],
+                                           img.shape[0], int(bins), C.byref(self._h))
+            ctx._check(rc, "pcp_nid_create_u8")
+            return
+        img = np.ascontiguousarray(normalized_image, np.float64)
+        if img.ndim != 2:
+            raise PcpError("NIDCost: normalized_image must be a single-channel HxW float64 plane")
         rc = self._L.pcp_nid_create(ctx.handle, _ptr(pts), pts.shape[0], pts.shape[1] * 4, ioff, _ptr(img), img.shape[1], img.shape[0],
                                     int(bins), C.byref(self._h))
         ctx._check(rc, "pcp_nid_create")

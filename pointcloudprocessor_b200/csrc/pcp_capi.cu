@@ -47,7 +47,7 @@ void pcp_default_params(pcp_params* p) {
   p->accum_mode = PCP_ACCUM_SUM;
   p->sample_mode = PCP_SAMPLE_NEAREST;
   p->top_m = 5;
-  p->frames_in_flight = 3;
+  p->frames_in_flight = 0;  // auto
   p->hsv_adjust = 0;
   p->saturation_scale = 1.0f;  // cpp:726-727
   p->brightness_scale = 1.0f;
@@ -99,6 +99,7 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
     if ((e = cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaEventCreateWithFlags(&ctx->ev_free[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
   }
+  ctx->flight_auto = params->frames_in_flight <= 0;  // decided per cloud in alloc_cloud_state
   ctx->flight = params->frames_in_flight > 0 ? params->frames_in_flight : 3;
   for (int i = 0; i < pcp_ctx::kMaxFlight; i++) {
     if ((e = cudaStreamCreateWithFlags(&ctx->fs[i].stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
@@ -251,6 +252,9 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
 
 static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
   const size_t n1 = n ? n : 1;
+  // frames in flight, when left to the library: small clouds are latency-bound (three dependent kernels per frame of a few us
+  // each), six slots keep the GPU busy (C1: 17.7 -> 12.2 us per frame); large clouds fill the GPU with three
+  if (ctx->flight_auto) ctx->flight = n <= 4000000 ? pcp_ctx::kMaxFlight : 3;
   CU(cudaMalloc(&ctx->d_acc, sizeof(uint4) * (n1 + pcp_ctx::kAccPad)));
   CU(cudaMalloc(&ctx->d_records, sizeof(Record) * (n1 + 64) * ctx->flight));
   if (ctx->prm.accum_mode == PCP_ACCUM_TOP5) {

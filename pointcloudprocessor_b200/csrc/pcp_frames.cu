@@ -165,7 +165,10 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ra.top_m = ctx->prm.top_m;
   ra.accum_mode = ctx->prm.accum_mode;
   ra.sample_mode = ctx->prm.sample_mode;
-  launch_resolve(ra, fp, ctx->resolve_grid, st);
+  int rgrid = ctx->resolve_grid;  // small clouds: fewer CTAs (the records are a fraction of the points), SMs stay free for the other slots
+  const int by_work = (int)(ctx->n / 4096);
+  if (by_work < rgrid) rgrid = by_work > ctx->sm_count / 2 ? by_work : ctx->sm_count / 2;
+  launch_resolve(ra, fp, rgrid, st);
   if (pe) CU(cudaEventRecord(pe[3], st));
   CU(cudaEventRecord(slot.ev_done, st));
   slot.used = true;

@@ -724,6 +724,9 @@ __global__ void __launch_bounds__(kScanThreads, PCP_SCAN_CTAS) scan_binned_kerne
 #ifndef PCP_POOL_BATCH
 #define PCP_POOL_BATCH 16
 #endif
+#ifndef PCP_CHUNKS_PER_CTA
+#define PCP_CHUNKS_PER_CTA 128
+#endif
 #ifndef PCP_RING_THREADS
 #define PCP_RING_THREADS 256
 #endif
@@ -738,8 +741,9 @@ static constexpr int kPoolPct = PCP_POOL_PCT;           // share of the active l
 static constexpr int kPoolBatch = PCP_POOL_BATCH;       // pool entries per global atomic (<= 32)
 static constexpr uint32_t kWorkFree = 0xffffffffu;
 static constexpr size_t kBufBytes = (size_t)kWorkers * 2 * kChunk * sizeof(float4);  // two chunk buffers per worker warp
-static constexpr size_t kRingSmem = kBufBytes + (size_t)kWorkers * (kQ1Cap * sizeof(float4) + kRqCap * sizeof(Record));
-static_assert(kChunk == 64, "scan_ring_kernel: two points per worker lane");
+static constexpr int kRingQ1Cap = 32 * (kGroups + 1);  // < 32 left over + one chunk
+static constexpr size_t kRingSmem = kBufBytes + (size_t)kWorkers * (kRingQ1Cap * sizeof(float4) + kRqCap * sizeof(Record));
+static_assert(kGroups >= 1 && kGroups <= 4, "scan_ring_kernel: kGroups points per worker lane");
 static_assert(kPoolBatch >= 1 && kPoolBatch <= 32, "pool batch: one lane per entry");
 static_assert((kWorkCap & (kWorkCap - 1)) == 0 && kWorkCap >= kAhead + 32 + kWorkers, "work ring too small");
 
@@ -862,8 +866,8 @@ __global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_kernel(
   } else {
     // ------------------------------------------------------------ workers -------------------------------------------------
     float4* buf = reinterpret_cast<float4*>(ring_smem) + (size_t)warp * 2 * kChunk;
-    float4* q1 = reinterpret_cast<float4*>(ring_smem + kBufBytes) + (size_t)warp * kQ1Cap;
-    Record* rq = reinterpret_cast<Record*>(ring_smem + kBufBytes + (size_t)kWorkers * kQ1Cap * sizeof(float4)) + (size_t)warp * kRqCap;
+    float4* q1 = reinterpret_cast<float4*>(ring_smem + kBufBytes) + (size_t)warp * kRingQ1Cap;
+    Record* rq = reinterpret_cast<Record*>(ring_smem + kBufBytes + (size_t)kWorkers * kRingQ1Cap * sizeof(float4)) + (size_t)warp * kRqCap;
     int n1 = 0, rn = 0;
 
     auto stage_b = [&](int cnt) {
@@ -934,41 +938,41 @@ __global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_kernel(
       constexpr int b = decltype(B)::value;
       mbar_wait(&s_bar[warp][b], phase[b]);
       phase[b] ^= 1u;
-      float4 p[2];
-      p[0] = buf[(size_t)b * kChunk + lane];
-      p[1] = buf[(size_t)b * kChunk + 32 + lane];
+      float4 p[kGroups];
+#pragma unroll
+      for (int k = 0; k < kGroups; k++) p[k] = buf[(size_t)b * kChunk + k * 32 + lane];
       const uint32_t cbase = base[b], ccnt = cnt[b];
       __syncwarp();  // every lane has its points: the buffer can take the warp's next chunk while this one is processed
       have[b] = fetch(b, base[b], cnt[b]);
-      float x[2], y[2], z[2];
-      bool ok[2], push[2];
-      unsigned int cur[2];
+      float x[kGroups], y[kGroups], z[kGroups];
+      bool ok[kGroups], push[kGroups];
+      unsigned int cur[kGroups];
 #pragma unroll
-      for (int k = 0; k < 2; k++) {
+      for (int k = 0; k < kGroups; k++) {
         x[k] = p[k].x; y[k] = p[k].y; z[k] = p[k].z;
         if (fp.use_w2c) transform_point(fp.w2c, p[k].x, p[k].y, p[k].z, x[k], y[k], z[k]);  // pcl::transformPointCloud (cpp:521)
         ok[k] = (uint32_t)(k * 32 + lane) < ccnt && !(z[k] < 0.0f);  // view_culling.cpp:76 (exact: double(z) < 0 <=> z < 0)
         cur[k] = kZBoundInit;  // FLT_MAX: always an upper bound (cell unknown, or pre-filter off)
       }
       if (prefilter_on) {
-        PreA pa[2];
+        PreA pa[kGroups];
 #pragma unroll
-        for (int k = 0; k < 2; k++) pa[k] = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
+        for (int k = 0; k < kGroups; k++) pa[k] = prefilter_a<kCount>(fp.pre, x[k], y[k], z[k]);
 #pragma unroll
-        for (int k = 0; k < 2; k++)
+        for (int k = 0; k < kGroups; k++)
           if (ok[k] && (pa[k].flags & 1u)) cur[k] = PCP_ZLOAD(zhi + 2 * pa[k].cell);
 #pragma unroll
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < kGroups; k++) {
           const unsigned int f = prefilter_b<kCount>(fp.pre, pa[k], cur[k], depth_culling);
           push[k] = ok[k] && (f & 1u);
           if (kCount) ncand += (ok[k] && (f & 2u)) ? 1u : 0u;
         }
       } else {
 #pragma unroll
-        for (int k = 0; k < 2; k++) push[k] = ok[k];
+        for (int k = 0; k < kGroups; k++) push[k] = ok[k];
       }
 #pragma unroll
-      for (int k = 0; k < 2; k++) {
+      for (int k = 0; k < kGroups; k++) {
         const unsigned int m = __ballot_sync(0xffffffffu, push[k]);
         if (push[k]) q1[n1 + __popc(m & lt_mask)] = make_float4(x[k], y[k], z[k], __uint_as_float(cbase + k * 32 + lane));
         n1 += __popc(m);
@@ -1016,7 +1020,11 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 
 int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, int sm_count, bool count_candidates, int device, cudaStream_t s) {
   if (a.aabb) {
-    const int rgrid = sm_count * PCP_RING_CTAS;  // one persistent CTA per resident slot
+    // one persistent CTA per resident slot for a large cloud; a small cloud takes fewer CTAs (>= PCP_CHUNKS_PER_CTA chunks each), so
+    // that the kernels of the frames in flight on the other slots find free SMs instead of queueing behind a grid that fills the GPU
+    int rgrid = sm_count * PCP_RING_CTAS;
+    const int by_work = (int)(a.n_chunks / (unsigned)PCP_CHUNKS_PER_CTA);  // measured at C1 (15.6 k chunks): 64 / 128 per CTA, see DESIGN 4.5
+    if (by_work < rgrid) rgrid = by_work > sm_count / 2 ? by_work : sm_count / 2;
     (void)rgrid;
     const int cgrid = a.seed_blocks + (int)((a.n_chunks + 255) / 256);
     // the opt-in to > 48 KB of dynamic shared memory is a per-device attribute: one flag per device, not per process

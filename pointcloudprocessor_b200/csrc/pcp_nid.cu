@@ -24,6 +24,16 @@ struct pcp_nid {
   double* d_hist_g = nullptr;   // gradient path: B x (8 * bins*bins + bins)
   double* d_out_g = nullptr;    // B x 9: NID, ok flag, 7 partials
   int cap_Bg = 0;
+  // batched MultiNIDCost evaluation (pcp_nid_eval_multi_grad), owned by the FIRST cost of the batch: one descriptor per cost, one
+  // contiguous histogram / output buffer for all costs x poses, so that an evaluation is two launches and one read-back
+  void* d_multi_args = nullptr;  // K x NidArgs
+  double* d_multi_hist = nullptr;
+  double* d_multi_out = nullptr;
+  double* d_multi_se3 = nullptr;
+  size_t multi_cap_costs = 0, multi_cap_rows = 0;
+  int multi_cap_B = 0;
+  std::vector<const void*> multi_key;  // the costs the descriptors were built for
+  int multi_key_B = 0;
 };
 
 namespace {
@@ -38,6 +48,20 @@ __global__ void nid_bin_image_kernel(const double* __restrict__ img, size_t npix
     if (!(pb == pb)) b = 0;
     b = b < bins - 1 ? b : bins - 1;
     out[i] = (uint8_t)(b < 0 ? 0 : b);
+  }
+}
+
+// The same bins from the 8-bit image itself: the cost uses a pixel only through min(int(pix * bins), bins - 1) with pix = the CV_64F
+// value convertTo(CV_64FC1, 1.0 / 255.0) makes of the byte (visual_camera_calibration.cpp:173), a function of the byte alone: `lut`.
+__global__ void nid_bin_image_u8_kernel(const uint8_t* __restrict__ img, size_t pitch, int W, int H, const uint8_t* __restrict__ lut,
+                                        uint8_t* __restrict__ out) {
+  __shared__ uint8_t s_lut[256];
+  s_lut[threadIdx.x & 255] = lut[threadIdx.x & 255];
+  __syncthreads();
+  const size_t npix = (size_t)W * H;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t y = i / (size_t)W, x = i - y * (size_t)W;
+    out[i] = s_lut[img[y * pitch + x]];
   }
 }
 
@@ -221,7 +245,7 @@ __device__ __forceinline__ void bspline_d(double s, double b[4], double d[4]) {
   d[3] = (3.0 * k) * s2;
 }
 
-__global__ void __launch_bounds__(kNidThreads) nid_hist_grad_kernel(const NidArgs a) {
+__device__ __forceinline__ void nid_hist_grad_body(const NidArgs& a) {
   extern __shared__ double shg[];  // 8 planes x bins x bins
   __shared__ unsigned int sh_pts[8 * 32];
   const int bins = a.bins, nb2 = bins * bins;
@@ -334,6 +358,16 @@ __global__ void __launch_bounds__(kNidThreads) nid_hist_grad_kernel(const NidArg
   }
 }
 
+__global__ void __launch_bounds__(kNidThreads) nid_hist_grad_kernel(const NidArgs a) { nid_hist_grad_body(a); }
+
+// All the keyframes of a MultiNIDCost evaluation in one launch: blockIdx.z = cost (keyframe), blockIdx.y = pose, blockIdx.x = point
+// tile; the grid's x extent is sized for the largest cloud, tiles beyond a cost's own cloud leave at once.
+__global__ void __launch_bounds__(kNidThreads) nid_hist_grad_multi_kernel(const NidArgs* __restrict__ items) {
+  const NidArgs a = items[blockIdx.z];
+  if (blockIdx.x * blockDim.x >= a.m) return;
+  nid_hist_grad_body(a);
+}
+
 // Entropies, NID and d NID / d theta; one warp per pose.  out: {NID, ok, g0..g6} per pose.
 //   H = -sum p log(p + eps), dH = -sum dp (log(p + eps) + p / (p + eps));  NID = (2 Hj - Hi - Hp) / Hj
 __global__ void nid_entropy_grad_kernel(const double* __restrict__ hist, int bins, int B, double* __restrict__ out) {
@@ -417,11 +451,11 @@ int ensure_batch(pcp_nid* nid, int B) {
 
 extern "C" {
 
-int pcp_nid_create(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const double* image,
-                   int width, int height, int bins, pcp_nid** out) {
+static int nid_create_impl(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const double* image,
+                           const uint8_t* image_u8, size_t pitch_u8, int width, int height, int bins, pcp_nid** out) {
   if (!ctx || !out) return PCP_EINVAL;
   *out = nullptr;
-  if ((!points && m) || !image || width <= 0 || height <= 0 || bins < 2 || bins > 32 || stride_bytes < 12 || (stride_bytes & 3) ||
+  if ((!points && m) || (!image && !image_u8) || (image_u8 && pitch_u8 < (size_t)(width > 0 ? width : 0)) || width <= 0 || height <= 0 || bins < 2 || bins > 32 || stride_bytes < 12 || (stride_bytes & 3) ||
       (intensity_offset & 3) || intensity_offset + 4 > stride_bytes || m >= 0xfffffff0ull) {
     ctx->fail("pcp_nid_create: invalid argument");
     return PCP_EINVAL;
@@ -433,13 +467,29 @@ int pcp_nid_create(pcp_ctx* ctx, const void* points, size_t m, size_t stride_byt
   const size_t npix = (size_t)width * height;
   double* d_img = nullptr;
   uint8_t* d_aos = nullptr;
-  auto cleanup = [&]() { if (d_img) cudaFree(d_img); if (d_aos) cudaFree(d_aos); };
+  uint8_t* d_u8 = nullptr;  // the 8-bit plane (W x H, packed) followed by the 256-entry bin table
+  auto cleanup = [&]() { if (d_img) cudaFree(d_img); if (d_aos) cudaFree(d_aos); if (d_u8) cudaFree(d_u8); };
+  uint8_t lut[256];
   cudaError_t e;
   if ((e = cudaMalloc(&nid->d_pts, sizeof(float4) * (m ? m : 1))) != cudaSuccess) goto fail;
   if ((e = cudaMalloc(&nid->d_binimg, npix)) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&d_img, npix * sizeof(double))) != cudaSuccess) goto fail;
-  if ((e = cudaMemcpyAsync(d_img, image, npix * sizeof(double), cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
-  nid_bin_image_kernel<<<ctx->sm_count * 8, 256, 0, s>>>(d_img, npix, bins, nid->d_binimg);
+  if (image_u8) {
+    // byte -> bin, evaluated on the host in the operations of the double path: (double)v * (1.0 / 255.0), then * bins, truncation, clamp
+    for (int v = 0; v < 256; v++) {
+      const double pix = (double)v * (1.0 / 255.0);
+      int b = (int)(pix * (double)bins);
+      b = b < bins - 1 ? b : bins - 1;
+      lut[v] = (uint8_t)(b < 0 ? 0 : b);
+    }
+    if ((e = cudaMalloc(&d_u8, npix + 256)) != cudaSuccess) goto fail;
+    if ((e = cudaMemcpy2DAsync(d_u8, (size_t)width, image_u8, pitch_u8, (size_t)width, (size_t)height, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
+    if ((e = cudaMemcpyAsync(d_u8 + npix, lut, 256, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
+    nid_bin_image_u8_kernel<<<ctx->sm_count * 8, 256, 0, s>>>(d_u8, (size_t)width, width, height, d_u8 + npix, nid->d_binimg);
+  } else {
+    if ((e = cudaMalloc(&d_img, npix * sizeof(double))) != cudaSuccess) goto fail;
+    if ((e = cudaMemcpyAsync(d_img, image, npix * sizeof(double), cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
+    nid_bin_image_kernel<<<ctx->sm_count * 8, 256, 0, s>>>(d_img, npix, bins, nid->d_binimg);
+  }
   ctx->launches++;
   if (m) {
     if (stride_bytes == 16 && intensity_offset == 12) {
@@ -462,6 +512,18 @@ fail:
   return PCP_ECUDA;
 }
 
+int pcp_nid_create(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const double* image,
+                   int width, int height, int bins, pcp_nid** out) {
+  if (ctx && !image) { ctx->fail("pcp_nid_create: invalid argument"); return PCP_EINVAL; }
+  return nid_create_impl(ctx, points, m, stride_bytes, intensity_offset, image, nullptr, 0, width, height, bins, out);
+}
+
+int pcp_nid_create_u8(pcp_ctx* ctx, const void* points, size_t m, size_t stride_bytes, size_t intensity_offset, const uint8_t* image,
+                      size_t pitch, int width, int height, int bins, pcp_nid** out) {
+  if (ctx && !image) { ctx->fail("pcp_nid_create_u8: invalid argument"); return PCP_EINVAL; }
+  return nid_create_impl(ctx, points, m, stride_bytes, intensity_offset, nullptr, image, pitch, width, height, bins, out);
+}
+
 void pcp_nid_destroy(pcp_nid* nid) {
   if (!nid) return;
   if (nid->ctx) cudaSetDevice(nid->ctx->device);
@@ -472,6 +534,10 @@ void pcp_nid_destroy(pcp_nid* nid) {
   if (nid->d_out) cudaFree(nid->d_out);
   if (nid->d_hist_g) cudaFree(nid->d_hist_g);
   if (nid->d_out_g) cudaFree(nid->d_out_g);
+  if (nid->d_multi_args) cudaFree(nid->d_multi_args);
+  if (nid->d_multi_hist) cudaFree(nid->d_multi_hist);
+  if (nid->d_multi_out) cudaFree(nid->d_multi_out);
+  if (nid->d_multi_se3) cudaFree(nid->d_multi_se3);
   delete nid;
 }
 
@@ -627,29 +693,100 @@ int pcp_nid_eval_multi(pcp_nid* const* costs, int n_costs, const double init_se3
 int pcp_nid_eval_multi_grad(pcp_nid* const* costs, int n_costs, const double init_se3[7], const double* se3, int B, double* sum_out,
                             double* grad_sum_out, uint8_t* ok_out) {
   if (!costs || n_costs <= 0 || !init_se3 || !se3 || B <= 0 || !sum_out || !grad_sum_out || !ok_out) return PCP_EINVAL;
-  std::vector<double> vals(B), grads(7 * (size_t)B);
-  std::vector<uint8_t> oks(B);
   for (int b = 0; b < B; b++) {
     ok_out[b] = nid_pose_gate(init_se3, se3 + 7 * (size_t)b) ? 1 : 0;
     sum_out[b] = 0.0;
     for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] = 0.0;
   }
-  // every cost's kernels are enqueued before the first read-back: one host synchronisation per evaluation instead of one per keyframe
-  // (the costs own their pose / histogram / output buffers); the sums below keep the reference's order of the keyframes
-  for (int c = 0; c < n_costs; c++) {
+  for (int c = 0; c < n_costs; c++)
     if (!costs[c]) return PCP_EINVAL;
-    const int rc = nid_grad_enqueue(costs[c], se3, B);
-    if (rc != PCP_OK) return rc;
-  }
-  for (int c = 0; c < n_costs; c++) {
-    const int rc = nid_grad_collect(costs[c], B, vals.data(), grads.data(), oks.data());
-    if (rc != PCP_OK) return rc;
-    for (int b = 0; b < B; b++) {
-      sum_out[b] += vals[b];  // residuals[0] += residuals[i] on Jets: values and dual parts add (visual_camera_calibration.cpp:116-119)
-      for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] += grads[7 * (size_t)b + k];
-      if (!oks[b]) ok_out[b] = 0;
+  pcp_nid* head = costs[0];
+  pcp_nid* nid = head;  // CUN reports through nid->ctx
+  pcp_ctx* ctx = head->ctx;
+  bool same = n_costs <= 65535 && B <= 65535;
+  for (int c = 1; c < n_costs; c++) same = same && costs[c]->ctx == ctx && costs[c]->bins == head->bins;
+  if (!same) {
+    // costs of different contexts / bin counts: one cost at a time (every cost's kernels are enqueued before the first read-back)
+    std::vector<double> vals(B), grads(7 * (size_t)B);
+    std::vector<uint8_t> oks(B);
+    for (int c = 0; c < n_costs; c++) {
+      const int rc = nid_grad_enqueue(costs[c], se3, B);
+      if (rc != PCP_OK) return rc;
     }
+    for (int c = 0; c < n_costs; c++) {
+      const int rc = nid_grad_collect(costs[c], B, vals.data(), grads.data(), oks.data());
+      if (rc != PCP_OK) return rc;
+      for (int b = 0; b < B; b++) {
+        sum_out[b] += vals[b];
+        for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] += grads[7 * (size_t)b + k];
+        if (!oks[b]) ok_out[b] = 0;
+      }
+    }
+    return PCP_OK;
   }
+  // ---- batched: every keyframe in ONE histogram launch and ONE entropy launch, one pose upload, one read-back ----------------
+  CUN(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  const int bins = head->bins, nb2 = bins * bins, nb = 8 * nb2 + bins;
+  const size_t rows = (size_t)n_costs * B;
+  if (head->multi_cap_costs < (size_t)n_costs || head->multi_cap_rows < rows || head->multi_cap_B < B) {
+    if (head->d_multi_args) cudaFree(head->d_multi_args);
+    if (head->d_multi_hist) cudaFree(head->d_multi_hist);
+    if (head->d_multi_out) cudaFree(head->d_multi_out);
+    if (head->d_multi_se3) cudaFree(head->d_multi_se3);
+    head->d_multi_args = nullptr; head->d_multi_hist = head->d_multi_out = head->d_multi_se3 = nullptr;
+    head->multi_cap_costs = head->multi_cap_rows = 0; head->multi_cap_B = 0; head->multi_key.clear();
+    CUN(cudaMalloc(&head->d_multi_args, sizeof(NidArgs) * n_costs));
+    CUN(cudaMalloc(&head->d_multi_hist, sizeof(double) * nb * rows));
+    CUN(cudaMalloc(&head->d_multi_out, sizeof(double) * 9 * rows));
+    CUN(cudaMalloc(&head->d_multi_se3, sizeof(double) * 7 * B));
+    head->multi_cap_costs = n_costs; head->multi_cap_rows = rows; head->multi_cap_B = B;
+  }
+  uint32_t m_max = 0;
+  for (int c = 0; c < n_costs; c++) m_max = costs[c]->m > m_max ? (uint32_t)costs[c]->m : m_max;
+  bool fresh = head->multi_key.size() != (size_t)n_costs || head->multi_key_B != B;
+  for (int c = 0; c < n_costs && !fresh; c++) fresh = head->multi_key[c] != (const void*)costs[c];
+  if (fresh) {  // the descriptors change only when the set of costs (or B) does: a BFGS solve uploads them once
+    std::vector<NidArgs> items(n_costs);
+    const pcp_camera& cm = ctx->cam;
+    for (int c = 0; c < n_costs; c++) {
+      NidArgs& a = items[c];
+      a.pts = costs[c]->d_pts; a.binimg = costs[c]->d_binimg; a.se3 = head->d_multi_se3;
+      a.hist = head->d_multi_hist + (size_t)c * B * nb;
+      a.m = (uint32_t)costs[c]->m; a.W = costs[c]->W; a.H = costs[c]->H; a.bins = bins; a.copies = 1;
+      a.cam = CamD{cm.fx, cm.fy, cm.cx, cm.cy, cm.dist[0], cm.dist[1], cm.dist[2], cm.dist[3], cm.dist[4]};
+    }
+    CUN(cudaMemcpyAsync(head->d_multi_args, items.data(), sizeof(NidArgs) * n_costs, cudaMemcpyHostToDevice, s));
+    CUN(cudaStreamSynchronize(s));  // `items` is pageable stack data
+    head->multi_key.assign(n_costs, nullptr);
+    for (int c = 0; c < n_costs; c++) head->multi_key[c] = costs[c];
+    head->multi_key_B = B;
+  }
+  CUN(cudaMemcpyAsync(head->d_multi_se3, se3, sizeof(double) * 7 * B, cudaMemcpyHostToDevice, s));
+  CUN(cudaMemsetAsync(head->d_multi_hist, 0, sizeof(double) * nb * rows, s));
+  const size_t smem = sizeof(double) * 8 * nb2;
+  CUN(cudaFuncSetAttribute(nid_hist_grad_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_pose = (int)((m_max + kNidThreads - 1) / kNidThreads);
+  const int want = (int)((ctx->sm_count * 4 + rows - 1) / rows);
+  if (per_pose > want) per_pose = want;
+  if (per_pose < 1) per_pose = 1;
+  if (m_max) {
+    nid_hist_grad_multi_kernel<<<dim3(per_pose, B, n_costs), kNidThreads, smem, s>>>(static_cast<const NidArgs*>(head->d_multi_args));
+    ctx->launches++;
+  }
+  nid_entropy_grad_kernel<<<(unsigned)rows, 32, 0, s>>>(head->d_multi_hist, bins, (int)rows, head->d_multi_out);
+  ctx->launches++;
+  CUN(cudaGetLastError());
+  std::vector<double> h(9 * rows);
+  CUN(cudaMemcpyAsync(h.data(), head->d_multi_out, sizeof(double) * 9 * rows, cudaMemcpyDeviceToHost, s));
+  CUN(cudaStreamSynchronize(s));
+  for (int c = 0; c < n_costs; c++)  // the sums keep the reference's order of the keyframes (visual_camera_calibration.cpp:116-119)
+    for (int b = 0; b < B; b++) {
+      const double* r = &h[9 * ((size_t)c * B + b)];
+      sum_out[b] += r[0];  // residuals[0] += residuals[i] on Jets: values and dual parts add
+      for (int k = 0; k < 7; k++) grad_sum_out[7 * (size_t)b + k] += r[2 + k];
+      if (r[1] == 0.0) ok_out[b] = 0;
+    }
   return PCP_OK;
 }
 

@@ -229,26 +229,22 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
   if (A.enable_nid_optimize) {
     const double t_nid = now_s();
     struct NidGuard { std::vector<pcp_nid*> v; ~NidGuard() { for (pcp_nid* n : v) pcp_nid_destroy(n); } } nids;
-    std::vector<double> plane;
     for (size_t k = 0; k < keyframes.size(); k++) {
       HostImage img;
       if (k == 0) img = first;
       else if (!load_image(keyframes[k]->image_path, false, img, why)) throw ProcError(PCP_EIO, "Failed to read image from: " + keyframes[k]->image_path);
       // cv::imread gives a 3-channel image and convertTo(CV_64FC1, 1/255) keeps the channels (only the depth changes), yet NIDCost reads
       // it with at<double>(y, x) and cols x rows bounds (nid_cost.hpp:61, :88): element x of row y of the INTERLEAVED doubles, i.e. the
-      // first cols values B0 G0 R0 B1 ... of each row.  Restated literally (PCP_NID_GREY_PLANE=1 in the environment takes the grey image
-      // a single-channel reading would have seen instead).
+      // first cols values B0 G0 R0 B1 ... of each row.  Restated literally: the 8-bit BGR image goes to the device as it is, with the
+      // row pitch of the interleaved image and `cols` bytes per row (nid_grey_plane = 1 takes the grey image a single-channel read
+      // would have seen instead).  The conversion to doubles / bins happens on the device (pcp_nid_create_u8).
       const int w = img.width, h = img.height;
-      static const bool grey = std::getenv("PCP_NID_GREY_PLANE") != nullptr;
-      if (grey) io::to_grey(img);
-      plane.resize((size_t)w * h);
-      const size_t row = (size_t)w * (size_t)img.channels;
-      for (int y = 0; y < h; y++)
-        for (int x = 0; x < w; x++) plane[(size_t)y * w + x] = (double)img.data[(size_t)y * row + x] * (1.0 / 255.0);
+      if (A.nid_grey_plane) io::to_grey(img);
       pcp_nid* nid = nullptr;
       const std::vector<io::XYZI>& pts = culled_for_nid[k];
       if (pts.empty()) continue;  // a frame that sees nothing adds no cost
-      check(ctx, pcp_nid_create(ctx, pts.data(), pts.size(), sizeof(io::XYZI), 12, plane.data(), w, h, 16, &nid), "pcp_nid_create");  // nid_bins = 16, calibrate.cpp:52
+      check(ctx, pcp_nid_create_u8(ctx, pts.data(), pts.size(), sizeof(io::XYZI), 12, img.data.data(), (size_t)w * (size_t)img.channels, w, h, 16, &nid),
+            "pcp_nid_create_u8");  // nid_bins = 16, calibrate.cpp:52
       nids.v.push_back(nid);
     }
     if (nids.v.empty()) throw ProcError(PCP_EINVAL, "pcp_process: NID optimisation has no visible points in any keyframe");

@@ -306,6 +306,22 @@ def test_nid(oracle, built_lib):
             ref, rok = oracle.nid(cam_o, grey, culled, cands[b])
             assert ok[b] == rok
             assert abs(got[b] - ref) <= 1e-5 * abs(ref), (b, got[b], ref)
+        # the 8-bit image itself (pcp_nid_create_u8: conversion to [0,1] and binning on the device): the same doubles, bit for bit
+        grey_u8 = np.rint(grey * 255.0).astype(np.uint8)
+        assert np.array_equal(grey_u8.astype(np.float64) * (1.0 / 255.0), grey)
+        cost_u8 = api.NIDCost(gc, grey_u8, culled, 16)
+        got_u8, ok_u8 = cost_u8(cands)
+        assert np.array_equal(got_u8, got) and np.array_equal(ok_u8, ok)
+        cost_u8.close()
+        # ... and the reference's actual read of a 3-channel image: the first W interleaved B,G,R values of every row (nid_cost.hpp:61, :88)
+        bgr = sc["images"][0]
+        cost_q = api.NIDCost(gc, bgr, culled, 16)
+        plane_q = np.ascontiguousarray(bgr.reshape(H, W * 3)[:, :W]).astype(np.float64) * (1.0 / 255.0)
+        got_q, ok_q = cost_q(cands[:4])
+        for b in range(4):
+            ref, rok = oracle.nid(cam_o, plane_q, culled, cands[b])
+            assert ok_q[b] == rok and abs(got_q[b] - ref) <= 1e-5 * abs(ref)
+        cost_q.close()
         # MultiNIDCost: gate + sum
         far = cands[1].copy()
         far[4] += 0.5

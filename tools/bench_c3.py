@@ -30,6 +30,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--frames", type=int, default=0)
+    ap.add_argument("--double-planes", action="store_true", help="hand the NID image planes over as float64 (pcp_nid_create) instead of uint8 (pcp_nid_create_u8)")
     args = ap.parse_args()
     import torch
     from oracle import pyoracle as O
@@ -43,7 +44,9 @@ def main():
     poses, _ = synth.make_poses(f)
     images = [synth.make_image(i, W, H) for i in range(f)]
     masks = [synth.make_mask(i, W, H) for i in range(f)]
-    greys = [synth.grey_plane(im) for im in images]
+    greys = [synth.grey_plane(im) for im in images]                      # v * (1 / 255) as doubles: what the oracle reads
+    greys_u8 = [np.rint(g * 255.0).astype(np.uint8) for g in greys]      # the same planes as bytes: what pcp_nid_create_u8 takes
+    assert all(np.array_equal(u.astype(np.float64) * (1.0 / 255.0), g) for u, g in zip(greys_u8, greys))
     cam_o = O.camera(intr, dist)
     sync = torch.cuda.synchronize
     t = {k: [] for k in ("cull", "nid_build", "refine", "colorize")}
@@ -59,7 +62,7 @@ def main():
                 w2cs = [O.pose_matrices(poses[i])[0] for i in range(f)]
                 pts = [np.ascontiguousarray(np.concatenate([O.transform(cloud[idx[i]], w2cs[i]), cloud[idx[i], 3:]], 1)) for i in range(f)]
             sync(); t1b = time.perf_counter()
-            costs = [api.NIDCost(gc, greys[i], pts[i], 16) for i in range(f)]
+            costs = [api.NIDCost(gc, greys[i] if args.double_planes else greys_u8[i], pts[i], 16) for i in range(f)]
             sync(); t2 = time.perf_counter()
             T, s = api.calibrate(costs)
             sync(); t3 = time.perf_counter()
