@@ -119,7 +119,10 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
   if ((e = cudaMallocHost(&ctx->h_counters, sizeof(FrameCounters))) != cudaSuccess) return bail("cudaMallocHost", e);
   if ((e = cudaMalloc(&ctx->d_total, sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
   ctx->scan_grid = ctx->sm_count * scan_ctas_per_sm();
-  ctx->resolve_grid = ctx->sm_count * 6;
+#ifndef PCP_RES_GRID_MULT
+#define PCP_RES_GRID_MULT 4  // = the resident CTAs per SM of resolve_kernel: one persistent wave
+#endif
+  ctx->resolve_grid = ctx->sm_count * PCP_RES_GRID_MULT;
   ctx->prefilter = !(params->debug_flags & PCP_DEBUG_NO_PREFILTER);
   ctx->use_seed = !(params->debug_flags & PCP_DEBUG_NO_SEED);
   *out = ctx;

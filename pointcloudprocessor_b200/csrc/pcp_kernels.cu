@@ -1117,11 +1117,13 @@ __device__ __noinline__ void bilinear_sample(const uint8_t* __restrict__ bgr, si
 // z-grid cell -> pixel -> accumulator) are in flight together: the kernel is latency-bound, not bandwidth-bound.  Only the
 // fields every record needs (index, dist, cell, pixel) stay in registers; x,y,z are re-read for the rare paths that use
 // them (TOP5 scores, re-projection after a double T), which keeps the kernel at 3 CTAs per SM.
+// measured at C2 (serialized resolve / frame with three in flight): 4 records x 3 CTAs per SM x 6 CTAs per SM launched 20.9 / 38.0 us;
+// 2 x 4 x 4 (one resident wave, 64 registers) 17.2 / 35.6 us; 1 x 4 x 12 24.1 / 41.4; 8 x 3 x 3 22.9 / 39.9
 #ifndef PCP_RES
-#define PCP_RES 4
+#define PCP_RES 2
 #endif
 #ifndef PCP_RES_CTAS
-#define PCP_RES_CTAS 3
+#define PCP_RES_CTAS 4
 #endif
 static constexpr int kRes = PCP_RES;
 
