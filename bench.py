@@ -76,7 +76,7 @@ def _plan(args, world):
         total = f
         period = args.image_period or (40 if f > 400 else f)
         period = min(period, f)
-    return dict(name=name, n=n, frames_total=total, frames_per_rank_weak=f, W=w, H=h, scaling=scaling, period=period)
+    return dict(name=name, n=n, frames_total=total, frames_per_rank_weak=f, W=w, H=h, scaling=scaling, period=period, block=args.frame_block or FRAME_BLOCK)
 
 
 def _frames_of_rank(plan, rank, world):
@@ -86,13 +86,13 @@ def _frames_of_rank(plan, rank, world):
         f = plan["frames_per_rank_weak"]
         return list(range(rank * f, (rank + 1) * f))
     from pointcloudprocessor_b200.shard import frames_of_rank
-    return frames_of_rank(F, rank, world, "dealt", FRAME_BLOCK)
+    return frames_of_rank(F, rank, world, "dealt", plan.get("block", FRAME_BLOCK))
 
 
 def _config(plan, world, sample):
     """The `config` object: identical in the native and the reference arm of the same launch."""
     n, F, W, H = plan["n"], plan["frames_total"], plan["W"], plan["H"]
-    mode = {"single": "one GPU", "strong": f"frames sharded over {world} GPUs in blocks of {FRAME_BLOCK} (fixed total work)",
+    mode = {"single": "one GPU", "strong": f"frames sharded over {world} GPUs in blocks of {plan.get('block', FRAME_BLOCK)} (fixed total work)",
             "weak": f"{plan['frames_per_rank_weak']} frames per GPU x {world} GPUs (work grows with N)"}[plan["scaling"]]
     return {
         "workload": f"{plan['name']}: {n} points x {F} frames @ {W}x{H}, colorize + z-buffer culling, SUM accumulators, {sample} sampling",
@@ -264,7 +264,7 @@ def run_native(args):
     cloud_np = synth.make_cloud(n)
 
     # images: frame g reads image g mod P.  Rank 0 of a strong run also times the whole frame set alone, so it holds all P.
-    need = sorted({g % P for g in (range(F) if (strong and rank == 0) else mine)})
+    need = sorted({g % P for g in (range(F) if strong else mine)})   # strong mode: the shares are re-dealt after the warm-up, keep every image
     slot_of = {im: k for k, im in enumerate(need)}
     img_bytes = H * W * 3
     h_cloud = torch.empty((n, 4), dtype=torch.float32).pin_memory()
@@ -345,6 +345,73 @@ def run_native(args):
     gc.synchronize()
     torch.cuda.synchronize()
     barrier()
+
+    # ---- strong scaling: cost-aware dealing of the frame blocks (untimed) -----------------------------------------------
+    # The blocks of a path do not cost the same (what the camera sees changes along it) and eight GPUs under load do not run
+    # at the same speed: with equal block counts the ranks' frame times differ by > 10 % and the fast ranks wait in the
+    # exchange.  So, after the warm-up: (1) every rank times each of ITS blocks once (events around the block, untimed step);
+    # (2) the ranks all-gather the per-block costs and deal the blocks longest-first to the rank that would finish earliest
+    # (shard.deal_by_cost); (3) one more untimed step measures each rank's time on its new share, which gives the ranks' relative
+    # speeds, and the deal is repeated with them.  The partition is a deterministic function of the gathered numbers, identical
+    # on every rank; any partition gives bit-identical sums (integer accumulators), which the parity check below verifies.
+    rebalance = None
+    if strong and world > 1 and not args.no_rebalance:
+        from pointcloudprocessor_b200.shard import deal_by_cost
+        B_ = plan["block"]
+        n_blocks = (F + B_ - 1) // B_
+        frames_of_block = lambda bb: list(range(bb * B_, min((bb + 1) * B_, F)))
+        my_blocks = sorted({g // B_ for g in mine})
+        evs = []
+        gc.reset_accumulators()
+        for bb in my_blocks:
+            fr = frames_of_block(bb)
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            gc.join()
+            ea.record(stream)
+            gc.submit_frames_device(poses_all[fr], np.array([dimg(g) for g in fr], np.uint64), W * 3)
+            gc.join()
+            eb.record(stream)
+            evs.append((bb, ea, eb))
+        gc.exchange_finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+        gc.synchronize()
+        torch.cuda.synchronize()
+        t = torch.zeros(n_blocks, device="cuda", dtype=torch.float64)
+        for bb, ea, eb in evs:
+            t[bb] = ea.elapsed_time(eb)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        costs = [float(x) for x in t.cpu()]
+        speed = [1.0] * world
+        hist = []
+        for it in range(2):
+            owner = deal_by_cost(costs, world, speed)
+            mine = [g for bb in range(n_blocks) if owner[bb] == rank for g in frames_of_block(bb)]
+            f = len(mine)
+            mine_poses = np.ascontiguousarray(poses_all[mine])
+            mine_ptrs = np.array([dimg(g) for g in mine], np.uint64)
+            predicted = [sum(c for bb, c in enumerate(costs) if owner[bb] == r) for r in range(world)]
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            gc.reset_accumulators()
+            ea.record(stream)
+            gc.submit_frames_device(mine_poses, mine_ptrs, W * 3)
+            gc.join()
+            eb.record(stream)
+            gc.exchange_finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
+            gc.synchronize()
+            torch.cuda.synchronize()
+            m = torch.zeros(world, device="cuda", dtype=torch.float64)
+            m[rank] = ea.elapsed_time(eb)
+            dist.all_reduce(m, op=dist.ReduceOp.SUM)
+            measured = [float(x) for x in m.cpu()]
+            hist.append({"blocks_by_rank": [owner.count(r) for r in range(world)], "frames_ms_by_rank": [round(x, 3) for x in measured],
+                         "speed_used": [round(x, 4) for x in speed]})
+            rel = [predicted[r] / max(measured[r], 1e-9) for r in range(world)]   # work per millisecond, relative
+            mean_rel = sum(rel) / world
+            speed = [speed[r] * 0 + rel[r] / mean_rel for r in range(world)]
+        barrier()
+        rebalance = {"block_cost_ms_min_mean_max": [round(min(costs), 3), round(sum(costs) / n_blocks, 3), round(max(costs), 3)], "iterations": hist,
+                     "what": "blocks of %d keyframes timed once each, dealt longest-first to the earliest-finishing rank (shard.deal_by_cost), repeated once "
+                             "with the ranks' measured relative speeds; untimed steps after the warm-up; results do not depend on the partition" % B_}
+
     sampler = ClockSampler(local) if rank == 0 else None
     gc.profile_enable(True)
     l0 = gc.launch_count()
@@ -361,6 +428,7 @@ def run_native(args):
     ms = ev0.elapsed_time(ev1)
     launches = gc.launch_count() - l0
     prof = gc.profile_read()
+    xphases = gc.exchange_times() if world > 1 else None   # phases of this rank's last exchange of the timed region
     gc.profile_enable(False)
     clocks = sampler.stop() if sampler else None
     ms_rank = ms
@@ -434,9 +502,11 @@ def run_native(args):
                 gc.submit_frame_device(poses_all[g], dimg(g), W * 3)
             gc.allreduce()
             gc.synchronize()
+            parts = [None] * world
+            dist.all_gather_object(parts, [int(g) for g in mine[:kp]])   # the frames every rank actually put through
             if rank == 0:
                 acc_g, _, _ = gc.accumulators()
-                frames_chk = sorted(g for r in range(world) for g in _frames_of_rank(plan, r, world)[:kp])
+                frames_chk = sorted(g for part in parts for g in part)
                 imgs_chk = {}
 
                 def img_of(g):
@@ -569,9 +639,12 @@ def run_native(args):
                                 "CUDA events around it on the launching stream, max over ranks", "share_of_step": exchange_ms / (ms / args.steps),
                                 "ms_min_over_ranks": exchange_min, "ms_mean_over_ranks": exchange_mean,
                                 "frames_ms_per_step_min_max_over_ranks": [frames_min, frames_max],
+                                "phases_ms_rank0_last_step": xphases,
                                 "note": "min over ranks = the exchange itself (the last rank to arrive waits for nobody); max - min = waiting for slower ranks"}
         if single is not None:
             line["single_gpu_same_workload"] = single
+        if rebalance is not None:
+            line["rebalance"] = rebalance
         if cpu is not None:
             line["cpu_baseline"] = cpu
         if parity is not None:
@@ -611,6 +684,8 @@ def main():
     ap.add_argument("--points", type=int, default=0)
     ap.add_argument("--frames", type=int, default=0)
     ap.add_argument("--image-period", type=int, default=0)
+    ap.add_argument("--no-rebalance", action="store_true", help="strong scaling: keep the equal-count dealing of the frame blocks")
+    ap.add_argument("--frame-block", type=int, default=0, help="strong scaling: consecutive keyframes per dealt block (default 25)")
     ap.add_argument("--sample", default="nearest", choices=["nearest", "bilinear"])
     ap.add_argument("--parity-frames", type=int, default=2, help="N>1: frames per rank of the oracle check of the exchanged accumulators")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")

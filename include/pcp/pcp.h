@@ -218,6 +218,9 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
  * {zgrid init, scan, resolve} and the number of frames, then resets the accumulation. */
 int pcp_profile_enable(pcp_ctx* ctx, int on);
 int pcp_profile_read(pcp_ctx* ctx, double ms3[3], uint64_t* frames);
+/* Debug: milliseconds of the phases of the last pcp_exchange_finalize[_device] made while profiling was enabled:
+ * {reduce-scatter, finalize of the rank's slice, all-gather, unpack into the caller's order}.  Synchronises. */
+int pcp_debug_exchange_times(pcp_ctx* ctx, double ms4[4]);
 
 /* vlcal::NIDCost (include/vlcal/costs/nid_cost.hpp:24-126).  points: m x {x,y,z,intensity} floats with
  * `stride_bytes` per record; image: W x H doubles in [0,1] (the CV_64F plane of

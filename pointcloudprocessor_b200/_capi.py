@@ -65,7 +65,7 @@ SYMBOLS = [
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
     "pcp_bfgs_default_options", "pcp_se3_bfgs", "pcp_calib_default_params", "pcp_calibrate", "pcp_set_frame_numbering", "pcp_splat_masks_pose",
-    "pcp_join", "pcp_exchange_finalize", "pcp_exchange_finalize_device", "pcp_finalize_compact", "pcp_pcd_write_xyzrgb", "pcp_submit_frames_device", "pcp_compact_bits_noalloc", "pcp_nid_create_u8",
+    "pcp_join", "pcp_exchange_finalize", "pcp_exchange_finalize_device", "pcp_finalize_compact", "pcp_pcd_write_xyzrgb", "pcp_submit_frames_device", "pcp_compact_bits_noalloc", "pcp_nid_create_u8", "pcp_debug_exchange_times",
 ]
 class BfgsOptions(C.Structure):
     _fields_ = [

@@ -322,6 +322,12 @@ class Colorizer:
     def exchange_finalize_device(self, d_rgb: int, d_count: int = 0):
         self._check(self._L.pcp_exchange_finalize_device(self._h, C.c_void_p(d_rgb or 0), C.c_void_p(d_count or 0)), "pcp_exchange_finalize_device")
 
+    def exchange_times(self):
+        """ms of {reduce-scatter, slice finalize, all-gather, unpack} of the last exchange_finalize made with profiling enabled."""
+        ms = (C.c_double * 4)()
+        self._check(self._L.pcp_debug_exchange_times(self._h, ms), "pcp_debug_exchange_times")
+        return {"reduce_scatter_ms": ms[0], "finalize_slice_ms": ms[1], "all_gather_ms": ms[2], "unpack_ms": ms[3]}
+
     def join(self):
         """The context's stream waits (on the device) for every frame submitted so far."""
         self._check(self._L.pcp_join(self._h), "pcp_join")

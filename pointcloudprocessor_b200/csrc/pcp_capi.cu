@@ -134,6 +134,7 @@ void pcp_destroy(pcp_ctx* ctx) {
   cudaSetDevice(ctx->device);
   ctx->drain();
   nccl_teardown(ctx);
+  for (cudaEvent_t& e : ctx->xchg_ev) if (e) { cudaEventDestroy(e); e = nullptr; }
   for (int i = 0; i < pcp_ctx::kMaxFlight; i++) {
     if (ctx->fs[i].stream) cudaStreamDestroy(ctx->fs[i].stream);
     if (ctx->fs[i].ev_fork) cudaEventDestroy(ctx->fs[i].ev_fork);

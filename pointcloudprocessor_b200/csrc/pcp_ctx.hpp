@@ -45,6 +45,8 @@ struct pcp_ctx {
   uint4* d_acc = nullptr;         // N x 16 B  {sum_r,sum_g,sum_b,count}
   uint2* d_xchg = nullptr;        // pcp_exchange_finalize: packed {rgb, count} of every point in sorted order (all-gather buffer)
   size_t xchg_points = 0;
+  cudaEvent_t xchg_ev[5] = {};    // phase timing of pcp_exchange_finalize while profiling is enabled
+  bool xchg_timed = false;
   bool reduced = false;           // the accumulators were exchanged since the last reset (a second exchange would double-count)
   bool acc_scattered = false;     // ... by pcp_exchange_finalize: only this rank's slice of d_acc is meaningful until the next reset
   uint2* d_mask_acc = nullptr;    // N x 8 B   {hits, max}; allocated at the first frame that carries a mask

@@ -310,18 +310,44 @@ int pcp_exchange_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_c
   }
   auto nccl_fail = [&](const char* what, int rc) { ctx->fail("%s: %s", what, api().error_string ? api().error_string(rc) : "error"); return PCP_ENCCL; };
   uint32_t* acc_words = reinterpret_cast<uint32_t*>(ctx->d_acc);
+  // optional phase timing (pcp_profile_enable): events after every phase, read with pcp_debug_exchange_times
+  cudaEvent_t* xe = nullptr;
+  if (ctx->profiling) {
+    for (int i = 0; i < 5; i++)
+      if (!ctx->xchg_ev[i] && cudaEventCreate(&ctx->xchg_ev[i]) != cudaSuccess) { ctx->fail("pcp_exchange_finalize: cudaEventCreate failed"); return PCP_ECUDA; }
+    xe = ctx->xchg_ev;
+    cudaEventRecord(xe[0], st);
+  }
   int rc = api().reduce_scatter(acc_words, acc_words + (size_t)r * slice * 4, (size_t)slice * 4, kNcclUint32, kNcclSum, comm, st);  // in place
+  if (xe) cudaEventRecord(xe[1], st);
   if (rc != 0) return nccl_fail("ncclReduceScatter", rc);
   const uint32_t j0 = r * slice, j1 = (r + 1) * slice < n ? (r + 1) * slice : n;
   if (j1 > j0) finalize_slice_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_acc, j0, j1, ctx->d_xchg, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR);
+  if (xe) cudaEventRecord(xe[2], st);
   rc = api().all_gather(ctx->d_xchg + (size_t)r * slice, ctx->d_xchg, (size_t)slice * 2, kNcclUint32, comm, st);  // in place
+  if (xe) cudaEventRecord(xe[3], st);
   if (rc != 0) return nccl_fail("ncclAllGather", rc);
   if (d_rgb_out || d_count_out) unpack_colours_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_xchg, ctx->d_perm ? ctx->d_inv : nullptr, n, d_rgb_out, d_count_out);
+  if (xe) { cudaEventRecord(xe[4], st); ctx->xchg_timed = true; }
   ctx->launches += 4;
   ctx->reduced = true;
   ctx->acc_scattered = true;  // only this rank's slice of d_acc holds the job's sums now
   if (cudaGetLastError() != cudaSuccess) { ctx->fail("pcp_exchange_finalize: kernel launch failed"); return PCP_ECUDA; }
   return exchange_masks(ctx);
+}
+
+/* Debug: milliseconds of the last pcp_exchange_finalize[_device] call made while profiling was enabled (pcp_profile_enable):
+ * {reduce-scatter, finalize of the slice, all-gather, unpack}.  Synchronises the context's stream. */
+int pcp_debug_exchange_times(pcp_ctx* ctx, double ms4[4]) {
+  if (!ctx || !ms4) return PCP_EINVAL;
+  if (!ctx->xchg_timed) { ctx->fail("pcp_debug_exchange_times: no exchange was timed"); return PCP_EINVAL; }
+  if (cudaSetDevice(ctx->device) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess) { ctx->fail("pcp_debug_exchange_times: synchronisation failed"); return PCP_ECUDA; }
+  for (int i = 0; i < 4; i++) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->xchg_ev[i], ctx->xchg_ev[i + 1]) != cudaSuccess) { ctx->fail("pcp_debug_exchange_times: cudaEventElapsedTime failed"); return PCP_ECUDA; }
+    ms4[i] = ms;
+  }
+  return PCP_OK;
 }
 
 /* Same with host outputs (synchronises). */

@@ -62,3 +62,21 @@ def test_sharding_is_a_partition():
                 assert got == list(range(n))
     with pytest.raises(ValueError):
         frames_of_rank(4, 2, 2)
+
+
+def test_deal_by_cost_balances_and_is_a_partition():
+    from pointcloudprocessor_b200.shard import deal_by_cost
+    rng = np.random.default_rng(3)
+    costs = rng.uniform(3.0, 8.0, 80)
+    for world in (1, 2, 4, 8):
+        owner = deal_by_cost(costs, world)
+        assert len(owner) == 80 and set(owner) == set(range(world))
+        loads = [costs[[b for b in range(80) if owner[b] == r]].sum() for r in range(world)]
+        assert max(loads) - min(loads) <= costs.min() + 1e-9          # LPT: the spread is below one (small) unit
+        assert owner == deal_by_cost(list(costs), world)               # deterministic
+    # a rank that is 20 % slower gets ~20 % less work
+    owner = deal_by_cost(costs, 4, speed=[1.0, 1.0, 1.0, 0.8])
+    loads = [costs[[b for b in range(80) if owner[b] == r]].sum() for r in range(4)]
+    assert abs(loads[3] / np.mean(loads[:3]) - 0.8) < 0.05
+    with pytest.raises(ValueError):
+        deal_by_cost(costs, 2, speed=[1.0])
