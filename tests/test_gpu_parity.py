@@ -121,6 +121,42 @@ def test_frames_in_flight_are_all_joined(built_lib):
     assert accs["cnt"].sum() > 10_000
 
 
+def _big_shape_parity(oracle, n, f, W, H, n_images, flight):
+    """Accumulators of f frames over an n-point cloud against the oracle (all host threads), frames submitted without per-frame
+    outputs so that `flight` of them are in flight; images are cycled (the kernels see the same work)."""
+    import os
+    from pointcloudprocessor_b200 import api, synth
+    intr, dist = synth.make_camera(W, H)
+    cloud = synth.make_cloud(n)
+    poses, _ = synth.make_poses(f)
+    images = [synth.make_image(i, W, H) for i in range(n_images)]
+    threads = max(1, len(os.sched_getaffinity(0)))
+    oc = oracle.Colorizer(oracle.camera(intr, dist), W, H, cloud)
+    with api.Colorizer(api.create_camera("pinhole", intr, dist), api.default_params(image_size=(W, H), frames_in_flight=flight)) as gc:
+        gc.set_cloud(cloud)
+        for i in range(f):
+            gc.submit_frame(poses[i], images[i % n_images])
+        for i in range(f):
+            oc.frame(poses[i], images[i % n_images], threads=threads)
+        acc_g, _, _ = gc.accumulators()
+        rgb_g, cnt_g = gc.finalize()
+    acc_o = oc.accumulators()[0]
+    assert np.array_equal(acc_g, acc_o), int((acc_g != acc_o).any(axis=1).sum())
+    assert np.array_equal(rgb_g, oc.finalize_sum()) and int(cnt_g.astype(bool).sum()) > n // 50
+    oc.close()
+
+
+def test_c5_shape_200_small_frames(oracle, built_lib):
+    """BASELINE config 5's regime (tiny frames over a large cloud, launch / occlusion dominated): 5e6 points x 200 frames @ 640x480,
+    three frames in flight, bit-exact accumulators."""
+    _big_shape_parity(oracle, 5_000_000, 200, 640, 480, n_images=8, flight=3)
+
+
+def test_c4_shape_large_cloud(oracle, built_lib):
+    """BASELINE config 4's regime (a 1e8-class map): 2e7 points x 6 frames @ 1920x1080, bit-exact accumulators."""
+    _big_shape_parity(oracle, 20_000_000, 6, 1920, 1080, n_images=3, flight=3)
+
+
 def test_tiny_masks(oracle, built_lib):
     _run_pair(oracle, make_scene(20_000, 3, 320, 240, masks=True), masks=True)
 
