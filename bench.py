@@ -269,6 +269,14 @@ def run_native(args):
     img_bytes = H * W * 3
     h_cloud = torch.empty((n, 4), dtype=torch.float32).pin_memory()
     h_cloud.numpy()[...] = cloud_np
+    # the e2e leg hands the map over the way the reference holds it: pcl::PointXYZI records of 32 bytes {x, y, z, 1, intensity, pad x 3}
+    pcl_layout = args.cloud_layout == "pcl"
+    if pcl_layout:
+        h_cloud32 = torch.zeros((n, 8), dtype=torch.float32).pin_memory()
+        h32 = h_cloud32.numpy()
+        h32[:, :3] = cloud_np[:, :3]
+        h32[:, 3] = 1.0
+        h32[:, 4] = cloud_np[:, 3]
     h_imgs = torch.empty((len(need), H, W, 3), dtype=torch.uint8).pin_memory()
     for k, im in enumerate(need):
         synth.make_image(im, W, H, out=h_imgs.numpy()[k])
@@ -317,7 +325,10 @@ def run_native(args):
             gc.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
 
     def step_e2e():
-        gc.set_cloud_ptr(h_cloud.data_ptr(), n)          # H2D cloud (resets the accumulators)
+        if pcl_layout:
+            gc.set_cloud_ptr(h_cloud32.data_ptr(), n, stride=32, intensity_offset=16)   # H2D cloud as pcl::PointXYZI (resets the accumulators)
+        else:
+            gc.set_cloud_ptr(h_cloud.data_ptr(), n)      # H2D cloud as float4
         for g in mine:
             gc.submit_frame_ptr(poses_all[g], himg(g), W * 3)  # H2D image per frame, overlapped on the copy stream
         if world > 1:
@@ -334,9 +345,13 @@ def run_native(args):
     gc.reset_accumulators()
     nvis = 0
     stat_frames = mine[:16]
+    stat_sum = {"chunks_fetched": 0, "active_chunks": 0, "records": 0}
     for g in stat_frames:
         r = gc.submit_frame_device(poses_all[g], dimg(g), W * 3, want_counts=True)
         nvis += r["n_visible"]
+        c = gc.debug_counters()          # the device counters of that frame (untimed pass)
+        for k in stat_sum:
+            stat_sum[k] += c[k]
     f_vis = nvis / (max(len(stat_frames), 1) * n)
 
     # ---- value: HBM-resident ------------------------------------------------------------------------------------------
@@ -462,7 +477,7 @@ def run_native(args):
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
     e2e_value = n * F * e2e_steps / e2e_s
-    h2d = world * n * 16 + F * img_bytes       # every rank uploads the cloud; every frame's image goes up once
+    h2d = world * n * (32 if pcl_layout else 16) + F * img_bytes   # every rank uploads the cloud; every frame's image goes up once
     d2h = n * 3 + n * 4                        # colours + counts, read back once (rank 0 when N > 1)
     e2e_matches_device = None
     if rank == 0:
@@ -609,6 +624,16 @@ def run_native(args):
             "pipeline_in_timed_region": {"achieved": pipe_bytes * f / (ms_step_rank * 1e-3) / 1e9, "frac": pipe_bytes * f / (ms_step_rank * 1e-3) / 1e9 / peak,
                                          "note": "algorithmic bytes of this rank's frames / ms_per_step of the headline (overlapped) run"},
         }
+        # DRAM bytes of pass 1 from THIS run's device counters: every fetched chunk is one 1 KB bulk copy; classify_kernel reads the chunk
+        # boxes and ids (36 B per chunk) and writes the 16-byte list entries the scouts read back; records are written once (32 B)
+        ns = max(len(stat_frames), 1)
+        n_chunks_total = (n + 63) // 64
+        counted = {k: v / ns for k, v in stat_sum.items()}
+        in_run = counted["chunks_fetched"] * 1024.0 + n_chunks_total * 36.0 + counted["active_chunks"] * 32.0 + counted["records"] * 32.0
+        roofline["traffic_in_run"] = {"bytes_per_launch": in_run, "frac_of_peak": in_run / (kern_ms["scan"] * 1e-3) / 1e9 / peak if kern_ms["scan"] > 0 else None,
+                                      "per_frame_counters": counted,
+                                      "how": "chunks fetched x 1 KB + chunks x 36 B (boxes, ids) + active entries x 32 B (written, read) + records x 32 B, "
+                                             "from the frame counters of this run's statistics pass"}
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             try:
@@ -631,7 +656,8 @@ def run_native(args):
             "frames_in_flight": (int(prm.frames_in_flight) or "auto (6 for clouds <= 4e6 points, else 3)"), "frames_per_rank": f,
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                    "colours_equal_device_path": e2e_matches_device},
+                    "colours_equal_device_path": e2e_matches_device,
+                    "cloud_layout": "pcl::PointXYZI, 32-byte records (the reference's)" if pcl_layout else "float4 {x,y,z,intensity}"},
             "roofline": roofline,
         }
         if exchange_ms is not None:
@@ -687,6 +713,7 @@ def main():
     ap.add_argument("--no-rebalance", action="store_true", help="strong scaling: keep the equal-count dealing of the frame blocks")
     ap.add_argument("--frame-block", type=int, default=0, help="strong scaling: consecutive keyframes per dealt block (default 25)")
     ap.add_argument("--sample", default="nearest", choices=["nearest", "bilinear"])
+    ap.add_argument("--cloud-layout", default="pcl", choices=["pcl", "float4"], help="record layout of the cloud handed over in the e2e leg")
     ap.add_argument("--parity-frames", type=int, default=2, help="N>1: frames per rank of the oracle check of the exchanged accumulators")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")

@@ -114,7 +114,7 @@ class Colorizer:
         """Device counters of the last submitted frame (see pcp_debug_counters)."""
         out = np.zeros(16, np.uint32)
         self._check(self._L.pcp_debug_counters(self._h, _ptr(out)), "pcp_debug_counters")
-        keys = ("records", "candidates", "visible", "colored", "active_chunks", "chunks_skipped", "kept_a0", "kept_a1")
+        keys = ("records", "candidates", "visible", "colored", "active_chunks", "chunks_skipped", "chunks_fetched", "kept_a1")
         return {k: int(out[i]) for i, k in enumerate(keys)}
 
     # -- cloud -----------------------------------------------------------------------------------------

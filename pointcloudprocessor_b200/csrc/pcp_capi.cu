@@ -221,7 +221,8 @@ cudaError_t pcp_ctx::drain() {
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
   F(d_cloud); F(d_perm); F(d_inv); F(d_aabb); F(d_order); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
-  F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt); F(d_xchg);
+  F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt); F(d_xchg); F(d_aos);
+  aos_bytes = 0;
   xchg_points = 0;
   if (d_prebin_scratch) { cudaFree(d_prebin_scratch); d_prebin_scratch = nullptr; prebin_scratch_bytes = 0; }
   out_points = 0;
@@ -318,16 +319,17 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
     if (stride_bytes == 16 && intensity_offset == 12) {
       CU(cudaMemcpyAsync(ctx->d_cloud, points, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
     } else {
-      uint8_t* d_aos = nullptr;
-      CU(cudaMalloc(&d_aos, n * stride_bytes));
-      cudaError_t e = cudaMemcpyAsync(d_aos, points, n * stride_bytes, cudaMemcpyHostToDevice, ctx->stream);
-      if (e == cudaSuccess) {
-        launch_aos_to_soa(d_aos, n, stride_bytes, intensity_offset, ctx->d_cloud, ctx->stream);
-        ctx->launches++;
-        e = cudaStreamSynchronize(ctx->stream);
+      // record layouts other than float4 (pcl::PointXYZI: 32 bytes, intensity at 16) are staged on the device and converted there; the
+      // staging buffer is kept across uploads and nothing synchronises (the copy, the conversion and the pre-binning are stream-ordered)
+      const size_t need = n * stride_bytes;
+      if (ctx->aos_bytes < need) {
+        if (ctx->d_aos) { CU(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_aos); ctx->d_aos = nullptr; ctx->aos_bytes = 0; }
+        CU(cudaMalloc(&ctx->d_aos, need));
+        ctx->aos_bytes = need;
       }
-      cudaFree(d_aos);
-      if (e != cudaSuccess) { ctx->fail("pcp_set_cloud: upload failed: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+      CU(cudaMemcpyAsync(ctx->d_aos, points, need, cudaMemcpyHostToDevice, ctx->stream));
+      launch_aos_to_soa(ctx->d_aos, n, stride_bytes, intensity_offset, ctx->d_cloud, ctx->stream);
+      ctx->launches++;
     }
   }
   {

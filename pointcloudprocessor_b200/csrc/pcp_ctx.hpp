@@ -30,6 +30,8 @@ struct pcp_ctx {
   // cloud + per-point state (HBM layout: see DESIGN.md)
   size_t n = 0;
   float4* d_cloud = nullptr;      // N x 16 B  {x,y,z,intensity}
+  uint8_t* d_aos = nullptr;       // staging of clouds handed over in a record layout other than float4 (kept across uploads)
+  size_t aos_bytes = 0;
   uint32_t* d_perm = nullptr;     // N x 4 B   sorted position -> original index (pre-binned mode; null otherwise)
   uint32_t* d_inv = nullptr;      // N x 4 B   original index -> sorted position (pre-binned mode): finalize gathers through it
   float4* d_aabb = nullptr;       // 2 float4 per chunk of 64 sorted points, stored in visiting order (pre-binned mode)
