@@ -64,8 +64,10 @@ typedef struct {
   int reserved;
 } pcp_params;
 /* PCP_DEBUG_NO_PREFILTER: every point takes the exact FP64 path of pass 1 (no FP32 pre-filter, no chunk skipping by distance).
- * PCP_DEBUG_NO_SEED: the previous frame's nearest points are not sent through pass 1 first. */
-enum { PCP_DEBUG_NO_PREFILTER = 1, PCP_DEBUG_NO_SEED = 2 };
+ * PCP_DEBUG_NO_SEED: the previous frame's nearest points are not sent through pass 1 first.
+ * PCP_DEBUG_FINALIZE_ONEPASS / _TWOPASS: pcp_finalize always gathers the 16-byte sums in one kernel / always packs them to 8 bytes
+ * first (by default the cloud size decides). */
+enum { PCP_DEBUG_NO_PREFILTER = 1, PCP_DEBUG_NO_SEED = 2, PCP_DEBUG_FINALIZE_ONEPASS = 4, PCP_DEBUG_FINALIZE_TWOPASS = 8 };
 
 /* Optional per-frame outputs (host buffers, caller-owned; any pointer may be NULL). */
 typedef struct {
@@ -304,7 +306,9 @@ void pcp_io_free(void* p);
 
 /* Debug/bench: the 16 u32 device counters of the last submitted frame: {records emitted by the scan, candidates, visible,
  * coloured, active chunks, then (library built with -DPCP_STATS only) chunks skipped whole, points kept by the chunk-level
- * depth test, points kept by the FP32 projection pre-filter}.  No reference counterpart. */
+ * depth test, points kept by the FP32 projection pre-filter}.  Words 14 and 15 (pre-binned cloud): of [15] sampled neighbours in the
+ * caller's point order, [14] are also neighbours in the library's sorted order (pcp_finalize picks its gather by that ratio).
+ * No reference counterpart. */
 int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]);
 
 /* NIDCost::operator()<ceres::Jet<double, 7>> — the instantiation ceres::AutoDiffFirstOrderFunction<MultiNIDCost, 7> evaluates

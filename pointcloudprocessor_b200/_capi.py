@@ -35,7 +35,7 @@ class FrameOut(C.Structure):
 
 
 OUT_SKIP_CANDIDATES = 1
-DEBUG_NO_PREFILTER, DEBUG_NO_SEED = 1, 2
+DEBUG_NO_PREFILTER, DEBUG_NO_SEED, DEBUG_FINALIZE_ONEPASS, DEBUG_FINALIZE_TWOPASS = 1, 2, 4, 8
 
 
 # every symbol include/pcp/pcp.h declares

@@ -115,7 +115,9 @@ class Colorizer:
         out = np.zeros(16, np.uint32)
         self._check(self._L.pcp_debug_counters(self._h, _ptr(out)), "pcp_debug_counters")
         keys = ("records", "candidates", "visible", "colored", "active_chunks", "chunks_skipped", "chunks_fetched", "kept_a1")
-        return {k: int(out[i]) for i, k in enumerate(keys)}
+        d = {k: int(out[i]) for i, k in enumerate(keys)}
+        d["order_locality"] = float(out[14]) / float(out[15]) if out[15] else None
+        return d
 
     # -- cloud -----------------------------------------------------------------------------------------
     def set_cloud(self, points: np.ndarray, intensity_offset: int | None = None):

@@ -210,6 +210,14 @@ cudaError_t pcp_ctx::join() {
   return cudaSuccess;
 }
 
+void pcp_ctx::end_batch() {
+  for (int i = 0; i < kMaxFlight; i++)
+    if ((batch_pending >> i) & 1u) cudaEventRecord(fs[i].ev_done, fs[i].stream);
+  batch_pending = 0;
+  batch_forked = 0;
+  in_batch = false;
+}
+
 cudaError_t pcp_ctx::drain() {
   cudaError_t e = cudaSuccess;
   for (int i = 0; i < kMaxFlight; i++)
@@ -220,10 +228,11 @@ cudaError_t pcp_ctx::drain() {
 
 void pcp_ctx::free_cloud() {
   auto F = [](auto*& p) { if (p) { cudaFree(p); p = nullptr; } };
-  F(d_cloud); F(d_perm); F(d_inv); F(d_aabb); F(d_order); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
+  F(d_cloud); F(d_perm); F(d_inv); F(d_inv_local); F(d_aabb); F(d_order); F(d_active); F(d_acc); F(d_mask_acc); F(d_top_score); F(d_top_rgbf); F(d_top_frame); F(d_records); F(d_vis_bits);
   F(d_pix); F(d_idx); F(d_scratch); F(d_out_rgb); F(d_out_cnt); F(d_xchg); F(d_aos);
   aos_bytes = 0;
   xchg_points = 0;
+  inv_local = -1.0f;
   if (d_prebin_scratch) { cudaFree(d_prebin_scratch); d_prebin_scratch = nullptr; prebin_scratch_bytes = 0; }
   out_points = 0;
   n = 0;
@@ -235,6 +244,7 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   if (!on) {
     if (ctx->d_perm) { cudaFree(ctx->d_perm); ctx->d_perm = nullptr; }
     if (ctx->d_inv) { cudaFree(ctx->d_inv); ctx->d_inv = nullptr; }
+    if (ctx->d_inv_local) { cudaFree(ctx->d_inv_local); ctx->d_inv_local = nullptr; }
     if (ctx->d_aabb) { cudaFree(ctx->d_aabb); ctx->d_aabb = nullptr; }
     if (ctx->d_order) { cudaFree(ctx->d_order); ctx->d_order = nullptr; }
     if (ctx->d_active) { cudaFree(ctx->d_active); ctx->d_active = nullptr; }
@@ -250,8 +260,11 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->d_order, &ctx->d_prebin_scratch, &ctx->prebin_scratch_bytes, ctx->sm_count,
                   ctx->stream));
   launch_invert_perm(ctx->d_perm, (uint32_t)n, ctx->d_inv, ctx->stream);
+  if (!ctx->d_inv_local) CU(cudaMalloc(&ctx->d_inv_local, 2 * sizeof(uint32_t)));
+  launch_inv_locality(ctx->d_inv, (uint32_t)n, ctx->d_inv_local, ctx->stream);
+  ctx->inv_local = -1.0f;
   ctx->n_chunks = n_chunks;
-  ctx->launches += 6;
+  ctx->launches += 7;
   return PCP_OK;
 }
 

@@ -35,6 +35,8 @@ struct pcp_ctx {
   uint32_t* d_perm = nullptr;     // N x 4 B   sorted position -> original index (pre-binned mode; null otherwise)
   uint32_t* d_inv = nullptr;      // N x 4 B   original index -> sorted position (pre-binned mode): finalize gathers through it
   float4* d_aabb = nullptr;       // 2 float4 per chunk of 64 sorted points, stored in visiting order (pre-binned mode)
+  uint32_t* d_inv_local = nullptr; // {close pairs, pairs looked at} of inv_locality_kernel (pre-binned mode)
+  float inv_local = -1.0f;        // their ratio once read back (pcp_finalize), -1 = not read yet
   uint32_t* d_order = nullptr;    // visit slot -> chunk id (pre-binned mode)
   uint4* d_active = nullptr;      // per-frame list of chunks to scan + their cell rectangle / distance bound (pre-binned mode)
   uint32_t n_chunks = 0;
@@ -77,6 +79,12 @@ struct pcp_ctx {
   uint64_t frames_run = 0;        // frames submitted since creation (slot = frames_run % flight)
   int last_slot = 0;              // slot of the last submitted frame
   int last_counters = 0;          // index of its counter block in d_counters
+  // pcp_submit_frames_device (many frames, no per-frame outputs): a slot's stream forks from ctx->stream once per call, not once per
+  // frame, and (SUM) its done-event is recorded once at the end of the call: 6 -> 3-4 driver calls per frame (C1 is bound by them)
+  bool in_batch = false;
+  uint32_t batch_forked = 0;    // slots whose stream already waited for ctx->stream in this call
+  uint32_t batch_pending = 0;   // slots whose ev_done is still to be recorded
+  void end_batch();
   cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
   unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys: grid 0 of every slot
   unsigned long long* d_zprev = nullptr;       // kMaxFlight x Wc*Hc: grid 1 of every slot (frames of a slot alternate; the other grid

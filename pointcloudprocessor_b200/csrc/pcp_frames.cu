@@ -6,6 +6,15 @@
 #include "../../include/pcp/pcp.h"
 #include "pcp_ctx.hpp"
 
+#ifdef PCP_HOST_TIMING  // tools/ variant only: where the submitting thread's time goes (printed at the end of every loop call)
+#include <chrono>
+#include <cstdio>
+namespace { double g_ht[8]; uint64_t g_ht_frames; inline double ht_now() { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); } }
+#define HT(k, stmt) do { const double t0_ = ht_now(); stmt; g_ht[k] += ht_now() - t0_; } while (0)
+#else
+#define HT(k, stmt) stmt
+#endif
+
 using namespace pcp;
 
 #define CU(call)                                                                             \
@@ -85,6 +94,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   if (d_mask && !ctx->d_mask_acc) {
     CU(cudaMalloc(&ctx->d_mask_acc, sizeof(uint2) * (ctx->n ? ctx->n : 1)));
     CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * (ctx->n ? ctx->n : 1), ctx->stream));
+    ctx->batch_forked = 0;  // every slot has to see this memset
   }
   if (want_vis || want_pix) CU(ctx->join());  // the previous frame's resolve kernel may still write these shared buffers
   if (want_vis) CU(cudaMemsetAsync(ctx->d_vis_bits, 0, sizeof(uint32_t) * ((ctx->n + 31) / 32), ctx->stream));
@@ -93,8 +103,11 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   const int si = (int)(ctx->frames_run % (uint64_t)ctx->flight);
   pcp_ctx::FrameSlot& slot = ctx->fs[si];
   cudaStream_t st = slot.stream;
-  CU(cudaEventRecord(slot.ev_fork, ctx->stream));
-  CU(cudaStreamWaitEvent(st, slot.ev_fork, 0));
+  const bool batch = ctx->in_batch && !want_vis && !want_pix && !ctx->profiling && !img_ready && !img_free;
+  if (!batch || !((ctx->batch_forked >> si) & 1u)) {
+    HT(0, CU(cudaEventRecord(slot.ev_fork, ctx->stream)); CU(cudaStreamWaitEvent(st, slot.ev_fork, 0)));
+    if (batch) ctx->batch_forked |= 1u << si;
+  }
 
   cudaEvent_t* pe = nullptr;
   if (ctx->profiling) {
@@ -137,7 +150,9 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   sa.records = recs;
   sa.counters = ctr;
   sa.n = (uint32_t)ctx->n;
-  if (launch_scan(sa, fp, ctx->scan_grid, ctx->sm_count, count_candidates, ctx->device, st) != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
+  int scan_rc = 0;
+  HT(1, scan_rc = launch_scan(sa, fp, ctx->scan_grid, ctx->sm_count, count_candidates, ctx->device, st));
+  if (scan_rc != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
   if (pe) CU(cudaEventRecord(pe[2], st));
   // TOP5 slot lists are read-modify-write: those resolve kernels run in frame order.  SUM accumulators are updated with
   // atomics (integer sums commute): frames on different slots are fully independent.
@@ -168,9 +183,10 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   int rgrid = ctx->resolve_grid;  // small clouds: fewer CTAs (the records are a fraction of the points), SMs stay free for the other slots
   const int by_work = (int)(ctx->n / 4096);
   if (by_work < rgrid) rgrid = by_work > ctx->sm_count / 2 ? by_work : ctx->sm_count / 2;
-  launch_resolve(ra, fp, rgrid, st);
+  HT(2, launch_resolve(ra, fp, rgrid, st));
   if (pe) CU(cudaEventRecord(pe[3], st));
-  CU(cudaEventRecord(slot.ev_done, st));
+  if (batch && ctx->prm.accum_mode == PCP_ACCUM_SUM) ctx->batch_pending |= 1u << si;  // recorded once, by pcp_ctx::end_batch
+  else HT(3, CU(cudaEventRecord(slot.ev_done, st)));
   slot.used = true;
   if (img_free) CU(cudaEventRecord(img_free, st));
   ctx->last_done = slot.ev_done;
@@ -218,13 +234,53 @@ static int submit_device(pcp_ctx* ctx, const double pose7[7], const double* T_op
   }
   CU(cudaSetDevice(ctx->device));
   FrameParams fp;
-  int rc = frame_params_for_pose(ctx, pose7, T_opt16, fp);
+  int rc = PCP_OK;
+  HT(4, rc = frame_params_for_pose(ctx, pose7, T_opt16, fp));
   if (rc != PCP_OK) return rc;
-  rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true,
-                 out && !(out->flags & PCP_OUT_SKIP_CANDIDATES), img_ready, img_free);
+  HT(5, rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true,
+                       out && !(out->flags & PCP_OUT_SKIP_CANDIDATES), img_ready, img_free));
   if (rc != PCP_OK) return rc;
   ctx->frame_index += ctx->frame_stride;
   if (out) return fetch_outputs(ctx, out);
+  return PCP_OK;
+}
+
+// SUM finalize on ctx->stream.  With a pre-binned cloud the sums (sorted order) and the outputs (caller's order) are a permutation apart
+// and the cost is the gather's locality (tools/bench_finalize.py):
+//   * caller's order spatially coherent (a voxel-grid filter's output, a scan-ordered map): one kernel gathers the 16-byte sums, 69 us
+//     at 1e7 points and 656 us at 1e8 = 0.60 / 0.64 of the HBM peak on 27 B per point (packing first: 102 / 1023 us);
+//   * caller's order random (the synthetic clouds): every gather is its own DRAM sector and, past a few hundred MB, its own TLB
+//     entry.  Up to 32 M points it pays to pack the sums to 8 bytes per point first (coalesced) and gather from that array, which is
+//     mostly still in L2: 139 against 156 us at 1e7 points, 620 / 654 at 3e7, 1212 / 1161 at 5e7, 3141 / 2448 at 1e8.
+// Which case a cloud is was measured when it was pre-binned (inv_locality_kernel).
+constexpr size_t kPackedMaxBytes = 256u << 20;
+static int finalize_sum_on_stream(pcp_ctx* ctx, uint8_t* d_rgb, uint32_t* d_cnt) {
+  const uint32_t n = (uint32_t)ctx->n;
+  const int fixed88 = ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR;
+  const int dbg = ctx->prm.debug_flags;
+  if (ctx->d_perm && ctx->inv_local < 0.0f) {
+    uint32_t h[2] = {0, 0};
+    cudaError_t e = cudaMemcpyAsync(h, ctx->d_inv_local, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { ctx->fail("pcp_finalize: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+    ctx->inv_local = h[1] ? (float)h[0] / (float)h[1] : 1.0f;
+  }
+  const bool random_order = ctx->d_perm && ctx->inv_local < 0.5f;
+  const bool two_pass = ctx->d_perm && !(dbg & PCP_DEBUG_FINALIZE_ONEPASS) &&
+                        ((dbg & PCP_DEBUG_FINALIZE_TWOPASS) || (random_order && sizeof(uint2) * ctx->n <= kPackedMaxBytes));
+  if (!two_pass) {
+    launch_finalize_sum(ctx->d_acc, ctx->d_perm ? ctx->d_inv : nullptr, n, d_rgb, d_cnt, fixed88, ctx->stream);
+    ctx->launches++;
+    return PCP_OK;
+  }
+  if (ctx->xchg_points < ctx->n) {
+    if (ctx->d_xchg) { cudaFree(ctx->d_xchg); ctx->d_xchg = nullptr; ctx->xchg_points = 0; }
+    if (cudaMalloc(&ctx->d_xchg, sizeof(uint2) * ctx->n) != cudaSuccess) { ctx->fail("pcp_finalize: out of device memory (%zu bytes)", sizeof(uint2) * ctx->n); return PCP_ENOMEM; }
+    ctx->xchg_points = ctx->n;
+  }
+  launch_pack_sum(ctx->d_acc, 0, n, ctx->d_xchg, fixed88, ctx->stream);
+  launch_unpack_colours(ctx->d_xchg, ctx->d_inv, n, d_rgb, d_cnt, ctx->stream);
+  ctx->launches += 2;
   return PCP_OK;
 }
 
@@ -242,11 +298,24 @@ int pcp_submit_frames_device(pcp_ctx* ctx, size_t n_frames, const double* poses7
                              const uint8_t* const* d_mask, size_t mask_pitch) {
   if (!ctx) return PCP_EINVAL;
   if (n_frames && (!poses7 || !d_bgr)) { ctx->fail("pcp_submit_frames_device: null argument"); return PCP_EINVAL; }
-  for (size_t i = 0; i < n_frames; i++) {
-    const int rc = submit_device(ctx, poses7 + 7 * i, T_opt16, d_bgr[i], pitch, d_mask ? d_mask[i] : nullptr, mask_pitch, nullptr, nullptr, nullptr);
-    if (rc != PCP_OK) return rc;
+  ctx->in_batch = true;
+  ctx->batch_forked = 0;
+  ctx->batch_pending = 0;
+  int rc = PCP_OK;
+  for (size_t i = 0; i < n_frames && rc == PCP_OK; i++)
+    rc = submit_device(ctx, poses7 + 7 * i, T_opt16, d_bgr[i], pitch, d_mask ? d_mask[i] : nullptr, mask_pitch, nullptr, nullptr, nullptr);
+  HT(6, ctx->end_batch());  // also after an error: the frames submitted so far stay joinable
+#ifdef PCP_HOST_TIMING
+  g_ht_frames += n_frames;
+  if (g_ht_frames >= 1000) {
+    std::fprintf(stderr, "[host us per frame] fork %.2f | classify+scan launch %.2f | resolve launch %.2f | done event %.2f | pose->params %.2f | run_frame total %.2f | end_batch %.2f (%llu frames; sizeof FrameParams %zu ScanArgs %zu ResolveArgs %zu)\n",
+                 g_ht[0] / g_ht_frames, g_ht[1] / g_ht_frames, g_ht[2] / g_ht_frames, g_ht[3] / g_ht_frames, g_ht[4] / g_ht_frames, g_ht[5] / g_ht_frames, g_ht[6] / g_ht_frames,
+                 (unsigned long long)g_ht_frames, sizeof(FrameParams), sizeof(ScanArgs), sizeof(ResolveArgs));
+    for (double& v : g_ht) v = 0;
+    g_ht_frames = 0;
   }
-  return PCP_OK;
+#endif
+  return rc;
 }
 
 int pcp_submit_frame(pcp_ctx* ctx, const double pose7[7], const double* T_opt16, const uint8_t* bgr, size_t pitch,
@@ -412,6 +481,7 @@ int pcp_debug_counters(pcp_ctx* ctx, uint32_t out16[16]) {
   CU(cudaSetDevice(ctx->device));
   CU(ctx->drain());
   CU(cudaMemcpy(out16, ctx->d_counters + ctx->last_counters, 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  if (ctx->d_inv_local) CU(cudaMemcpy(out16 + 14, ctx->d_inv_local, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
   return PCP_OK;
 }
 
@@ -447,9 +517,13 @@ int pcp_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_count_out)
   if (ctx->acc_scattered) { ctx->fail("pcp_finalize: the accumulators were consumed by pcp_exchange_finalize"); return PCP_EINVAL; }
   if (ctx->n == 0) return PCP_OK;
   CU(ctx->join());
-  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm ? ctx->d_inv : nullptr, (uint32_t)ctx->n, d_rgb_out, d_count_out, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
-  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
-  ctx->launches++;
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) {
+    const int rc = finalize_sum_on_stream(ctx, d_rgb_out, d_count_out);
+    if (rc != PCP_OK) return rc;
+  } else {
+    launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)ctx->n, ctx->prm.top_m, d_rgb_out, d_count_out, ctx->stream);
+    ctx->launches++;
+  }
   CU(cudaGetLastError());
   return PCP_OK;
 }
@@ -518,9 +592,13 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out) {
   }
   uint8_t* d_rgb = rgb_out ? ctx->d_out_rgb : nullptr;
   uint32_t* d_cnt = count_out ? ctx->d_out_cnt : nullptr;
-  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) launch_finalize_sum(ctx->d_acc, ctx->d_perm ? ctx->d_inv : nullptr, (uint32_t)n, d_rgb, d_cnt, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, ctx->stream);
-  else launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
-  ctx->launches++;
+  if (ctx->prm.accum_mode == PCP_ACCUM_SUM) {
+    const int rc = finalize_sum_on_stream(ctx, d_rgb, d_cnt);
+    if (rc != PCP_OK) return rc;
+  } else {
+    launch_finalize_top(ctx->d_top_score, ctx->d_top_rgbf, ctx->d_top_frame, ctx->d_perm, (uint32_t)n, ctx->prm.top_m, d_rgb, d_cnt, ctx->stream);
+    ctx->launches++;
+  }
   if (rgb_out) CU(cudaMemcpyAsync(rgb_out, d_rgb, n * 3, cudaMemcpyDeviceToHost, ctx->stream));
   if (count_out) CU(cudaMemcpyAsync(count_out, d_cnt, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));

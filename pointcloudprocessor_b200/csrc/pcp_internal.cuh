@@ -113,6 +113,8 @@ int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, int sm_count
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);
 void launch_finalize_sum(const uint4* acc, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
+void launch_pack_sum(const uint4* acc, uint32_t j0, uint32_t j1, uint2* packed, int fixed88, cudaStream_t s);
+void launch_unpack_colours(const uint2* packed, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
 // generateColorMap's 8-bit HSV round trip (pcp_image.cu); src and dst may alias
@@ -122,6 +124,7 @@ void launch_hsv_roundtrip(const uint8_t* src, size_t spitch, uint8_t* dst, size_
 cudaError_t prebin_cloud(float4* d_cloud, uint32_t n, uint32_t* d_perm, float4* d_aabb, uint32_t* d_order, void** scratch, size_t* scratch_bytes,
                          int sm_count, cudaStream_t s);
 void launch_invert_perm(const uint32_t* perm, uint32_t n, uint32_t* inv, cudaStream_t s);
+void launch_inv_locality(const uint32_t* inv, uint32_t n, uint32_t* out2, cudaStream_t s);
 void launch_unpermute(const uint32_t* src, const uint32_t* perm, uint32_t n, int elem_words, uint32_t* dst, cudaStream_t s);
 // ascending index list from a visibility bitmask; returns through d_total the number of set bits
 void launch_compact_bits(const uint32_t* bits, uint32_t n, uint32_t* word_offsets, uint32_t* block_sums, int32_t* idx_out,

@@ -1304,24 +1304,107 @@ void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t iof
 // Finalize.
 // ---------------------------------------------------------------------------------------------------------------------
 // `fixed88`: the sums hold 8.8 fixed-point samples (PCP_SAMPLE_BILINEAR): the integer mean is rounded to 8 bits.
-// The outputs are walked in the caller's order (coalesced writes); the sums are gathered through `inv` (original index -> sorted
-// position).  Scattering the 3-byte colours through perm instead measured 331 us per 1e7 points (partial-sector writes).
-__global__ void finalize_sum_kernel(const uint4* __restrict__ acc, const uint32_t* __restrict__ inv, uint32_t n, uint8_t* __restrict__ rgb,
-                                    uint32_t* __restrict__ count, int fixed88) {
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t j = inv ? __ldg(inv + i) : i;
-    const uint4 s = acc[j];
-    uint32_t r = 0, g = 0, b = 0;
-    if (s.w) { r = s.x / s.w; g = s.y / s.w; b = s.z / s.w; }
-    if (fixed88) { r = min((r + 128u) >> 8, 255u); g = min((g + 128u) >> 8, 255u); b = min((b + 128u) >> 8, 255u); }
-    if (rgb) { rgb[3 * (size_t)i] = (uint8_t)r; rgb[3 * (size_t)i + 1] = (uint8_t)g; rgb[3 * (size_t)i + 2] = (uint8_t)b; }
-    if (count) count[i] = s.w;
+// The outputs are in the caller's order, the sums in sorted (Morton) order: a permutation between them.  Three ways were measured at
+// 1e7 points (tools/bench_finalize.py): scattering the 3-byte colours through perm (331 us, partial-sector writes); one
+// kernel that walks the outputs and gathers the 16-byte sums through inv (143 us: every gather costs a 32-byte DRAM sector and the
+// colours leave as byte stores); and the two kernels below, which are what runs:
+//   pack:   sorted order, fully coalesced: 16-byte sums -> 8-byte {r | g << 8 | b << 16, count};
+//   unpack: output order, four points per thread: one 16-byte load of inv, four independent 8-byte gathers from the packed array (80 MB
+//           at 1e7 points: it was just written and is served from L2), 12 + 16 bytes of vector stores.
+// The same pair is the middle of pcp_exchange_finalize (pack the rank's slice, all-gather, unpack).
+__device__ __forceinline__ uint2 pack_mean(const uint4 s, int fixed88) {
+  uint32_t r = 0, g = 0, b = 0;
+  if (s.w) { r = s.x / s.w; g = s.y / s.w; b = s.z / s.w; }
+  if (fixed88) { r = min((r + 128u) >> 8, 255u); g = min((g + 128u) >> 8, 255u); b = min((b + 128u) >> 8, 255u); }
+  return make_uint2(r | (g << 8) | (b << 16), s.w);
+}
+__device__ __forceinline__ void store_one(uint8_t* rgb, uint32_t* count, uint32_t i, const uint2 v) {
+  if (rgb) { rgb[3 * (size_t)i] = (uint8_t)(v.x & 255u); rgb[3 * (size_t)i + 1] = (uint8_t)((v.x >> 8) & 255u); rgb[3 * (size_t)i + 2] = (uint8_t)(v.x >> 16); }
+  if (count) count[i] = v.y;
+}
+__global__ void __launch_bounds__(256) pack_sum_kernel(const uint4* __restrict__ acc, uint32_t j0, uint32_t j1, uint2* __restrict__ packed,
+                                                       int fixed88) {
+  for (uint32_t j = j0 + blockIdx.x * blockDim.x + threadIdx.x; j < j1; j += gridDim.x * blockDim.x) packed[j] = pack_mean(__ldcs(acc + j), fixed88);
+}
+// Outputs in the caller's order for 16-byte aligned output pointers.  A CTA takes tiles of 1024 points: every thread fetches four
+// points (one 16-byte load of inv, four independent gathers), the counts leave as one 16-byte store per thread and the 3072 colour
+// bytes of the tile go through shared memory and leave as 192 16-byte stores (byte or 12-byte-strided word stores reach L2 as partial
+// sectors: measured 212 us against 162 us for the byte form at 1e7 points).  kFromAcc: gather the 16-byte sums themselves and take the
+// mean here (the one-kernel form); otherwise gather the packed 8-byte values of pack_sum_kernel.
+template <bool kFromAcc>
+__global__ void __launch_bounds__(256) finalize_tiles_kernel(const void* __restrict__ src, const uint32_t* __restrict__ inv, uint32_t n,
+                                                             uint8_t* __restrict__ rgb, uint32_t* __restrict__ count, int fixed88) {
+  __shared__ __align__(16) uint32_t s_rgb[768];
+  const uint4* acc = reinterpret_cast<const uint4*>(src);
+  const uint2* packed = reinterpret_cast<const uint2*>(src);
+  const uint32_t n_tiles = (n + 1023u) / 1024u;
+  const uint32_t t = threadIdx.x;
+  for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const uint32_t base = tile * 1024u, i = base + 4u * t;
+    uint2 v[4] = {make_uint2(0, 0), make_uint2(0, 0), make_uint2(0, 0), make_uint2(0, 0)};
+    if (i + 3u < n) {
+      uint4 j = make_uint4(i, i + 1, i + 2, i + 3);
+      if (inv) j = __ldcs(reinterpret_cast<const uint4*>(inv) + (i >> 2));
+      if (kFromAcc) {
+        const uint4 sa = acc[j.x], sb = acc[j.y], sc = acc[j.z], sd = acc[j.w];
+        v[0] = pack_mean(sa, fixed88); v[1] = pack_mean(sb, fixed88); v[2] = pack_mean(sc, fixed88); v[3] = pack_mean(sd, fixed88);
+      } else {
+        v[0] = packed[j.x]; v[1] = packed[j.y]; v[2] = packed[j.z]; v[3] = packed[j.w];
+      }
+      if (count) reinterpret_cast<uint4*>(count)[i >> 2] = make_uint4(v[0].y, v[1].y, v[2].y, v[3].y);
+    } else {
+      for (uint32_t k = 0; k < 4u && i + k < n; k++) {
+        const uint32_t j = inv ? inv[i + k] : i + k;
+        v[k] = kFromAcc ? pack_mean(acc[j], fixed88) : packed[j];
+        if (count) count[i + k] = v[k].y;
+      }
+    }
+    if (rgb) {
+      // 12 bytes r g b r | g b r g | b r g b
+      s_rgb[3 * t] = (v[0].x & 0xffffffu) | (v[1].x << 24);
+      s_rgb[3 * t + 1] = ((v[1].x >> 8) & 0xffffu) | (v[2].x << 16);
+      s_rgb[3 * t + 2] = ((v[2].x >> 16) & 0xffu) | (v[3].x << 8);
+      __syncthreads();
+      const uint32_t bytes = 3u * min(1024u, n - base);
+      uint8_t* out = rgb + 3 * (size_t)base;
+      if (t < 192u) {
+        if (16u * t + 16u <= bytes) reinterpret_cast<uint4*>(out)[t] = reinterpret_cast<const uint4*>(s_rgb)[t];
+        else for (uint32_t b = 16u * t; b < bytes; b++) out[b] = reinterpret_cast<const uint8_t*>(s_rgb)[b];
+      }
+      __syncthreads();
+    }
   }
 }
+// any output alignment (a caller's sub-range): one point per thread, byte stores
+__global__ void unpack_colours_bytes_kernel(const uint2* __restrict__ packed, const uint32_t* __restrict__ inv, uint32_t n,
+                                            uint8_t* __restrict__ rgb, uint32_t* __restrict__ count) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) store_one(rgb, count, i, packed[inv ? __ldg(inv + i) : i]);
+}
+__global__ void finalize_sum_kernel(const uint4* __restrict__ acc, const uint32_t* __restrict__ inv, uint32_t n, uint8_t* __restrict__ rgb,
+                                    uint32_t* __restrict__ count, int fixed88) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    store_one(rgb, count, i, pack_mean(acc[inv ? __ldg(inv + i) : i], fixed88));
+}
+static int grid_for(size_t items, int per_cta, int cap) {
+  const size_t g = (items + per_cta - 1) / per_cta;
+  return (int)(g < (size_t)cap ? (g ? g : 1) : (size_t)cap);
+}
+static bool quad_aligned(const uint8_t* rgb, const uint32_t* count, const uint32_t* inv) {
+  return ((uintptr_t)rgb % 16 == 0) && ((uintptr_t)count % 16 == 0) && ((uintptr_t)inv % 16 == 0);
+}
 void launch_finalize_sum(const uint4* acc, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s) {
-  if (n == 0) return;
-  const int grid = (n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16;
-  finalize_sum_kernel<<<grid, 256, 0, s>>>(acc, inv, n, rgb, count, fixed88);
+  if (n == 0 || (!rgb && !count)) return;
+  if (quad_aligned(rgb, count, inv)) finalize_tiles_kernel<true><<<grid_for(n, 1024, 148 * 16), 256, 0, s>>>(acc, inv, n, rgb, count, fixed88);
+  else finalize_sum_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(acc, inv, n, rgb, count, fixed88);
+}
+void launch_pack_sum(const uint4* acc, uint32_t j0, uint32_t j1, uint2* packed, int fixed88, cudaStream_t s) {
+  if (j1 <= j0) return;
+  pack_sum_kernel<<<grid_for(j1 - j0, 256, 148 * 16), 256, 0, s>>>(acc, j0, j1, packed, fixed88);
+}
+void launch_unpack_colours(const uint2* packed, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s) {
+  if (n == 0 || (!rgb && !count)) return;
+  if (quad_aligned(rgb, count, inv)) finalize_tiles_kernel<false><<<grid_for(n, 1024, 148 * 16), 256, 0, s>>>(packed, inv, n, rgb, count, 0);
+  else unpack_colours_bytes_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, s>>>(packed, inv, n, rgb, count);
 }
 
 // smoothColors (cpp:612-629): slots are already sorted by (score desc, frame asc); weighted mean in float, truncation.

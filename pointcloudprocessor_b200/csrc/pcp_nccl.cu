@@ -16,6 +16,8 @@
 #include "../../include/pcp/pcp.h"
 #include "pcp_ctx.hpp"
 
+using namespace pcp;
+
 namespace {
 
 struct NcclId { char internal[128]; };
@@ -89,26 +91,8 @@ __global__ void top_pack_kernel(const float* __restrict__ score, const uint32_t*
   }
 }
 
-// ---- SUM: finalize of the rank's slice after the reduce-scatter, and the un-permuting unpack after the all-gather ------------------
-// packed[j] = {r | g << 8 | b << 16, count} of sorted position j (the integer mean of finalize_sum_kernel; `fixed88`: 8.8 sums, rounded)
-__global__ void finalize_slice_kernel(const uint4* __restrict__ acc, uint32_t j0, uint32_t j1, uint2* __restrict__ packed, int fixed88) {
-  for (uint32_t j = j0 + blockIdx.x * blockDim.x + threadIdx.x; j < j1; j += gridDim.x * blockDim.x) {
-    const uint4 s = acc[j];
-    uint32_t r = 0, g = 0, b = 0;
-    if (s.w) { r = s.x / s.w; g = s.y / s.w; b = s.z / s.w; }
-    if (fixed88) { r = min((r + 128u) >> 8, 255u); g = min((g + 128u) >> 8, 255u); b = min((b + 128u) >> 8, 255u); }
-    packed[j] = make_uint2(r | (g << 8) | (b << 16), s.w);
-  }
-}
-// outputs in the caller's point order: walks the output index (coalesced writes) and gathers through inv (null: identity)
-__global__ void unpack_colours_kernel(const uint2* __restrict__ packed, const uint32_t* __restrict__ inv, uint32_t n, uint8_t* __restrict__ rgb,
-                                      uint32_t* __restrict__ count) {
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint2 v = packed[inv ? __ldg(inv + i) : i];
-    if (rgb) { rgb[3 * (size_t)i] = (uint8_t)(v.x & 255u); rgb[3 * (size_t)i + 1] = (uint8_t)((v.x >> 8) & 255u); rgb[3 * (size_t)i + 2] = (uint8_t)(v.x >> 16); }
-    if (count) count[i] = v.y;
-  }
-}
+// SUM: the rank's slice is packed after the reduce-scatter and everything is un-permuted after the all-gather by launch_pack_sum /
+// launch_unpack_colours (pcp_kernels.cu), the same pair pcp_finalize runs on one GPU.
 
 constexpr int kMaxTopM = 16;  // pcp_create refuses more
 
@@ -322,12 +306,12 @@ int pcp_exchange_finalize_device(pcp_ctx* ctx, uint8_t* d_rgb_out, uint32_t* d_c
   if (xe) cudaEventRecord(xe[1], st);
   if (rc != 0) return nccl_fail("ncclReduceScatter", rc);
   const uint32_t j0 = r * slice, j1 = (r + 1) * slice < n ? (r + 1) * slice : n;
-  if (j1 > j0) finalize_slice_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_acc, j0, j1, ctx->d_xchg, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR);
+  launch_pack_sum(ctx->d_acc, j0, j1, ctx->d_xchg, ctx->prm.sample_mode == PCP_SAMPLE_BILINEAR, st);
   if (xe) cudaEventRecord(xe[2], st);
   rc = api().all_gather(ctx->d_xchg + (size_t)r * slice, ctx->d_xchg, (size_t)slice * 2, kNcclUint32, comm, st);  // in place
   if (xe) cudaEventRecord(xe[3], st);
   if (rc != 0) return nccl_fail("ncclAllGather", rc);
-  if (d_rgb_out || d_count_out) unpack_colours_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_xchg, ctx->d_perm ? ctx->d_inv : nullptr, n, d_rgb_out, d_count_out);
+  launch_unpack_colours(ctx->d_xchg, ctx->d_perm ? ctx->d_inv : nullptr, n, d_rgb_out, d_count_out, st);
   if (xe) { cudaEventRecord(xe[4], st); ctx->xchg_timed = true; }
   ctx->launches += 4;
   ctx->reduced = true;

@@ -186,4 +186,22 @@ void launch_invert_perm(const uint32_t* perm, uint32_t n, uint32_t* inv, cudaStr
   invert_perm_kernel<<<blocks < 148u * 16u ? blocks : 148u * 16u, 256, 0, s>>>(perm, n, inv);
 }
 
+// How local is the caller's point order?  out[0] = among up to 65536 evenly spaced neighbours (i, i + 1) of the caller's order, the number
+// whose sorted positions are less than 65536 apart (1 MB of accumulators); out[1] = the number of pairs looked at.  A voxel-grid
+// filter's output or a scan-ordered map scores near 1, a shuffled cloud near 0: pcp_finalize picks its gather by it.
+__global__ void inv_locality_kernel(const uint32_t* __restrict__ inv, uint32_t n, uint32_t samples, uint32_t stride, uint32_t* __restrict__ out) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k == 0) out[1] = samples;
+  if (k >= samples) return;
+  const uint32_t i = k * stride;
+  const uint32_t a = inv[i], b = inv[i + 1];
+  if ((a > b ? a - b : b - a) < 65536u) atomicAdd(out, 1u);
+}
+void launch_inv_locality(const uint32_t* inv, uint32_t n, uint32_t* out2, cudaStream_t s) {
+  cudaMemsetAsync(out2, 0, 2 * sizeof(uint32_t), s);
+  if (n < 2) return;
+  const uint32_t samples = n - 1 < 65536u ? n - 1 : 65536u;
+  inv_locality_kernel<<<(samples + 255) / 256, 256, 0, s>>>(inv, n, samples, (n - 1) / samples, out2);
+}
+
 }  // namespace pcp

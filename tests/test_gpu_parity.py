@@ -121,6 +121,77 @@ def test_frames_in_flight_are_all_joined(built_lib):
     assert accs["cnt"].sum() > 10_000
 
 
+@pytest.mark.parametrize("n", [20_003, 20_000, 7])
+@pytest.mark.parametrize("bilinear", [False, True])
+def test_finalize_forms_agree_with_oracle(oracle, built_lib, n, bilinear):
+    """pcp_finalize_device has three kernels behind it (pack + unpack, the four-points-per-thread gather, the byte-store gather for
+    unaligned output pointers): every one of them, with colours only / counts only / both and a point count that is not a multiple
+    of four, must produce the oracle's integer means (smoothColors, cpp:604-631)."""
+    import torch
+    from pointcloudprocessor_b200 import _capi, api
+    W, H = 320, 240
+    sc = make_scene(n, 3, W, H)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    oc = oracle.Colorizer(cam_o, W, H, sc["cloud"], bilinear=bilinear)
+    for i, pose in enumerate(sc["poses"]):
+        oc.frame(pose, sc["images"][i])
+    rgb_o, cnt_o = oc.finalize_sum(), oc.accumulators()[0][:, 3]
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    sm = api.SAMPLE_BILINEAR if bilinear else api.SAMPLE_NEAREST
+    for flags in (0, _capi.DEBUG_FINALIZE_ONEPASS, _capi.DEBUG_FINALIZE_TWOPASS):
+        with api.Colorizer(cam, api.default_params(image_size=(W, H), sample_mode=sm, debug_flags=flags)) as gc:
+            gc.set_cloud(sc["cloud"])
+            for i, pose in enumerate(sc["poses"]):
+                gc.submit_frame(pose, sc["images"][i])
+            for off in (0, 1):  # 1: an output pointer that is not 4-byte aligned
+                d_rgb = torch.full((n * 3 + 16,), 77, dtype=torch.uint8, device="cuda")
+                d_cnt = torch.full((n + 4,), -1, dtype=torch.int32, device="cuda")
+                for want_rgb, want_cnt in ((True, True), (True, False), (False, True)):
+                    d_rgb.fill_(77)
+                    d_cnt.fill_(-1)
+                    gc.finalize_device(d_rgb.data_ptr() + off if want_rgb else 0, d_cnt.data_ptr() if want_cnt else 0)
+                    gc.synchronize()
+                    r, c = d_rgb.cpu().numpy(), d_cnt.cpu().numpy()
+                    if want_rgb:
+                        assert np.array_equal(r[off:off + 3 * n].reshape(n, 3), rgb_o), (flags, off)
+                        assert (r[:off] == 77).all() and (r[off + 3 * n:] == 77).all(), "wrote outside the colour array"
+                    else:
+                        assert (r == 77).all()
+                    if want_cnt:
+                        assert np.array_equal(c[:n].view(np.uint32), cnt_o) and (c[n:] == -1).all(), (flags, off)
+                    else:
+                        assert (c == -1).all()
+    assert cnt_o.sum() > 0 or n < 100
+
+
+def test_finalize_picks_gather_by_point_order(oracle, built_lib):
+    """The same 1e6 points in a shuffled and in a voxel-grid order: the locality measured at pre-binning tells them apart, and the
+    colours (whatever gather pcp_finalize picks) equal the oracle's in the caller's order both times."""
+    from pointcloudprocessor_b200 import api
+    W, H = 320, 240
+    sc = make_scene(1_000_000, 3, W, H)
+    cloud = sc["cloud"]
+    cell = np.floor(cloud[:, :3] / 0.5).astype(np.int64)
+    cell -= cell.min(axis=0)
+    ext = cell.max(axis=0) + 1
+    voxel = np.ascontiguousarray(cloud[np.argsort((cell[:, 2] * ext[1] + cell[:, 1]) * ext[0] + cell[:, 0], kind="stable")])
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    loc = {}
+    for name, pts in (("shuffled", cloud), ("voxel", voxel)):
+        oc = oracle.Colorizer(cam_o, W, H, pts)
+        with api.Colorizer(cam, api.default_params(image_size=(W, H))) as gc:
+            gc.set_cloud(pts)
+            for i, pose in enumerate(sc["poses"]):
+                oc.frame(pose, sc["images"][i])
+                gc.submit_frame(pose, sc["images"][i])
+            rgb, cnt = gc.finalize()
+            loc[name] = gc.debug_counters()["order_locality"]
+        assert np.array_equal(rgb, oc.finalize_sum()) and np.array_equal(cnt, oc.accumulators()[0][:, 3]), name
+        assert cnt.sum() > 0
+    assert loc["shuffled"] < 0.5 < loc["voxel"], loc
+
+
 def _big_shape_parity(oracle, n, f, W, H, n_images, flight):
     """Accumulators of f frames over an n-point cloud against the oracle (all host threads), frames submitted without per-frame
     outputs so that `flight` of them are in flight; images are cycled (the kernels see the same work)."""

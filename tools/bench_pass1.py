@@ -68,9 +68,12 @@ def main():
         gc.synchronize()
         gc.profile_enable(flight == 1)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        import time
         e0.record(stream)
+        t0 = time.perf_counter()
         for _ in range(a.reps):
             step()
+        host_us = 1e6 * (time.perf_counter() - t0) / (a.reps * f)  # time the submitting thread spends per frame (launches, events)
         e1.record(stream)
         gc.synchronize()
         torch.cuda.synchronize()
@@ -84,7 +87,7 @@ def main():
             out["sha"] = hashlib.sha1(acc.tobytes()).hexdigest()[:16]
             out["counters_last_frame"] = gc.debug_counters()
         else:
-            out["pipelined" if flight == 3 else f"pipelined_flight{flight}"] = {"frame_us": round(per_frame_us, 2), "pf_per_s": float(f"{n / (per_frame_us * 1e-6):.4g}")}
+            out["pipelined" if flight == 3 else f"pipelined_flight{flight}"] = {"frame_us": round(per_frame_us, 2), "host_submit_us": round(host_us, 2), "pf_per_s": float(f"{n / (per_frame_us * 1e-6):.4g}")}
             acc, _, _ = gc.accumulators()
             out["sha3"] = hashlib.sha1(acc.tobytes()).hexdigest()[:16]
         gc.close()
