@@ -653,7 +653,7 @@ def run_native(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if strong and world > 1 else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": cfg,
             "host": {"affinity": (f"rank bound to the {numa} CPUs NVML lists for its GPU" if numa else "unbound"), "threads": threads},
-            "frames_in_flight": (int(prm.frames_in_flight) or "auto (6 for clouds <= 4e6 points, else 3)"), "frames_per_rank": f,
+            "frames_in_flight": (int(prm.frames_in_flight) or "auto (12 slots and 4 frames per launch for clouds <= 4e6 points, else 3 slots)"), "frames_per_rank": f,
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "colours_equal_device_path": e2e_matches_device,

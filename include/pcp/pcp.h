@@ -51,7 +51,7 @@ typedef struct {
   int prebin;                      /* 1 (default): Morton-sort the device copy of the cloud into 64-point chunks with bounding
                                     * boxes at set_cloud; chunks certainly behind the camera / outside the z-grid are skipped per
                                     * frame.  Every output stays in the caller's point order.  0: keep the caller's order. */
-  int frames_in_flight;            /* 1..6; 0 (default) = chosen per cloud: 6 for clouds of <= 4e6 points, else 3.  Frames run on that many internal streams, each with its own z-grid / record
+  int frames_in_flight;            /* 1..24; 0 (default) = chosen per cloud: 12 for clouds of <= 4e6 points, else 3.  Frames run on that many internal slots, each with its own z-grid / record
                                     * scratch, so that the scan of frame f+1 overlaps the tail of frame f and its resolve pass.
                                     * Accumulator updates stay in frame order; results do not depend on this value. */
   int hsv_adjust;                  /* 1: pcp_submit_frame applies generateColorMap's 8-bit BGR->HSV->BGR round trip (cpp:722-741) to the
@@ -61,7 +61,10 @@ typedef struct {
   int hsv_vector_block;            /* pixels per vector iteration of the OpenCV build to reproduce (its scalar row tail rounds
                                     * differently from its vector body): 32 = cv2 4.13 AVX2 build; 0 = whole row is vector body */
   int debug_flags;                 /* PCP_DEBUG_*: 0 in production.  Test hooks that select a slower path with identical results. */
-  int reserved;
+  int frames_per_launch;           /* pcp_submit_frames_device, SUM mode, pre-binned cloud: 1, 2 or 4 consecutive frames share one launch of
+                                    * each of the frame's three kernels (they run on neighbouring slots; results do not depend on it).
+                                    * 0 (default) = chosen per cloud: for <= 4e6 points 4 when frames_in_flight >= 8, 2 when >= 4; else 1.
+                                    * For small clouds the launches, not the GPU, bound the frame rate. */
 } pcp_params;
 /* PCP_DEBUG_NO_PREFILTER: every point takes the exact FP64 path of pass 1 (no FP32 pre-filter, no chunk skipping by distance).
  * PCP_DEBUG_NO_SEED: the previous frame's nearest points are not sent through pass 1 first.

@@ -25,7 +25,7 @@ class Params(C.Structure):
         ("image_width", C.c_int), ("image_height", C.c_int), ("cull_width", C.c_int), ("cull_height", C.c_int),
         ("downsample", C.c_int), ("depth_tolerance", C.c_double), ("enable_depth_buffer_culling", C.c_int),
         ("accum_mode", C.c_int), ("sample_mode", C.c_int), ("top_m", C.c_int), ("prebin", C.c_int), ("frames_in_flight", C.c_int), ("hsv_adjust", C.c_int), ("saturation_scale", C.c_float),
-        ("brightness_scale", C.c_float), ("hsv_vector_block", C.c_int), ("debug_flags", C.c_int), ("reserved", C.c_int),
+        ("brightness_scale", C.c_float), ("hsv_vector_block", C.c_int), ("debug_flags", C.c_int), ("frames_per_launch", C.c_int),
     ]
 
 

@@ -66,7 +66,8 @@ int pcp_create(pcp_ctx** out, int device, const pcp_camera* cam, const pcp_param
       params->downsample <= 0 || params->top_m < 1 || params->top_m > 16 ||
       (params->accum_mode != PCP_ACCUM_SUM && params->accum_mode != PCP_ACCUM_TOP5) ||
       (params->sample_mode != PCP_SAMPLE_NEAREST && params->sample_mode != PCP_SAMPLE_BILINEAR) || params->frames_in_flight < 0 ||
-      params->frames_in_flight > pcp_ctx::kMaxFlight || params->hsv_vector_block < 0) {
+      params->frames_in_flight > pcp_ctx::kMaxFlight || params->hsv_vector_block < 0 ||
+      (params->frames_per_launch != 0 && params->frames_per_launch != 1 && params->frames_per_launch != 2 && params->frames_per_launch != 4)) {
     g_create_error = "pcp_create: invalid params";
     return PCP_EINVAL;
   }
@@ -239,6 +240,16 @@ void pcp_ctx::free_cloud() {
 }
 
 // Sort the uploaded cloud into Morton chunks (pcp_prebin.cu).  Called after every upload, before the accumulators are reset.
+// Frames in flight and frames per launch, when left to the library.  Small clouds are latency-bound (three dependent kernels per frame
+// of a few us each) and their launches cost the submitting thread more than the GPU needs: twelve slots, four frames per launch
+// (C1: 17.7 us per frame with 3 slots, 12.2 with 6).  Large clouds fill the GPU with three frames in flight.
+static void choose_flight(pcp_ctx* ctx, size_t n) {
+  const bool small = n <= 4000000;
+  if (ctx->flight_auto) ctx->flight = small ? 12 : 3;
+  ctx->group = ctx->prm.frames_per_launch > 0 ? ctx->prm.frames_per_launch : (small ? (ctx->flight >= 8 ? 4 : (ctx->flight >= 4 ? 2 : 1)) : 1);
+  while (ctx->group > 1 && ctx->group > ctx->flight) ctx->group /= 2;
+}
+
 static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   const bool on = ctx->prm.prebin != 0 && n > 0;
   if (!on) {
@@ -256,7 +267,7 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
   if (!ctx->d_inv) CU(cudaMalloc(&ctx->d_inv, sizeof(uint32_t) * n));
   if (!ctx->d_aabb) CU(cudaMalloc(&ctx->d_aabb, sizeof(float4) * 2 * n_chunks));
   if (!ctx->d_order) CU(cudaMalloc(&ctx->d_order, sizeof(uint32_t) * n_chunks));
-  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks * pcp_ctx::kMaxFlight));
+  if (!ctx->d_active) CU(cudaMalloc(&ctx->d_active, sizeof(uint4) * n_chunks * (size_t)ctx->flight));
   CU(prebin_cloud(ctx->d_cloud, (uint32_t)n, ctx->d_perm, ctx->d_aabb, ctx->d_order, &ctx->d_prebin_scratch, &ctx->prebin_scratch_bytes, ctx->sm_count,
                   ctx->stream));
   launch_invert_perm(ctx->d_perm, (uint32_t)n, ctx->d_inv, ctx->stream);
@@ -270,9 +281,6 @@ static int prebin_if_enabled(pcp_ctx* ctx, size_t n) {
 
 static int alloc_cloud_state(pcp_ctx* ctx, size_t n) {
   const size_t n1 = n ? n : 1;
-  // frames in flight, when left to the library: small clouds are latency-bound (three dependent kernels per frame of a few us
-  // each), six slots keep the GPU busy (C1: 17.7 -> 12.2 us per frame); large clouds fill the GPU with three
-  if (ctx->flight_auto) ctx->flight = n <= 4000000 ? pcp_ctx::kMaxFlight : 3;
   CU(cudaMalloc(&ctx->d_acc, sizeof(uint4) * (n1 + pcp_ctx::kAccPad)));
   CU(cudaMalloc(&ctx->d_records, sizeof(Record) * (n1 + 64) * ctx->flight));
   if (ctx->prm.accum_mode == PCP_ACCUM_TOP5) {
@@ -345,6 +353,7 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
       ctx->launches++;
     }
   }
+  choose_flight(ctx, n);
   {
     const int rc = prebin_if_enabled(ctx, n);
     if (rc != PCP_OK) return rc;
@@ -360,6 +369,7 @@ int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n) {
   ctx->free_cloud();
   CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * (n ? n : 1)));
   if (n) CU(cudaMemcpyAsync(ctx->d_cloud, d_xyzi, sizeof(float4) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+  choose_flight(ctx, n);
   {
     const int rc = prebin_if_enabled(ctx, n);
     if (rc != PCP_OK) return rc;

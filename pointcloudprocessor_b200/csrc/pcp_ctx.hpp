@@ -66,16 +66,18 @@ struct pcp_ctx {
   // Frame slots: frame f runs on slot f % flight, each slot with its own stream, z-grid, counters, record region and
   // active-chunk list.  The scan of frame f+1 therefore overlaps the tail of the scan of frame f and its resolve kernel
   // (whose accumulator updates stay ordered: resolve f+1 waits for resolve f).  Work is forked from / joined to ctx->stream.
-  static constexpr int kMaxFlight = 6;
+  static constexpr int kMaxFlight = 24;
   struct FrameSlot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_done = nullptr;
     int parity = 0;               // which of the slot's two z-grids / counter blocks the next frame uses
-    bool used = false;            // ev_done has been recorded at least once
+    bool used = false;            // ev_done has been recorded at least once (or is pending in a loop call)
+    int owner = -1;               // slot whose STREAM last ran work on this slot's z-grids / lists / records (-1: none yet)
   };
   FrameSlot fs[kMaxFlight];
   int flight = 3;                 // frames in flight (pcp_params.frames_in_flight)
-  bool flight_auto = false;       // frames_in_flight = 0: chosen per cloud (6 for <= 4e6 points, else 3)
+  bool flight_auto = false;       // frames_in_flight = 0: chosen per cloud (12 for <= 4e6 points, else 3)
+  int group = 1;                  // frames per launch in pcp_submit_frames_device (1, 2 or 4; pcp_params.frames_per_launch, 0 = per cloud)
   uint64_t frames_run = 0;        // frames submitted since creation (slot = frames_run % flight)
   int last_slot = 0;              // slot of the last submitted frame
   int last_counters = 0;          // index of its counter block in d_counters

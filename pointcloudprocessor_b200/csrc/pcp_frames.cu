@@ -84,6 +84,80 @@ int ensure_outputs(pcp_ctx* ctx, bool vis, bool pix) {
 
 // Enqueue z-grid clear + classify/scan + resolve for one frame on its frame slot's stream (forked from ctx->stream).
 // img_ready: event the resolve kernel must wait for (the image upload), or null; img_free: recorded after the resolve kernel.
+// Arguments of one frame on slot `si`: the slot's z-grids, counter blocks (by parity), record buffer and chunk list.  Two z-grids and
+// counter blocks per slot: this frame's pair was cleared by the slot's previous frame (or at set-up), the other pair holds that
+// frame's final grid (the seed points) and is cleared by this frame's classify_kernel for the next one.
+void fill_frame_args(pcp_ctx* ctx, int si, const FrameParams& fp, const uint8_t* d_bgr, size_t pitch, const uint8_t* d_mask, size_t mask_pitch,
+                     bool want_vis, bool want_pix, bool accumulate, ScanArgs& sa, ResolveArgs& ra, int* counters_index) {
+  const int cells = ctx->Wc * ctx->Hc;
+  const size_t c1 = cells ? cells : 1;
+  const int par = ctx->fs[si].parity;
+  unsigned long long* zg = (par ? ctx->d_zprev : ctx->d_zgrid) + (size_t)si * c1;
+  unsigned long long* zp = (par ? ctx->d_zgrid : ctx->d_zprev) + (size_t)si * c1;
+  FrameCounters* ctr = ctx->d_counters + 2 * si + par;
+  FrameCounters* ctr_next = ctx->d_counters + 2 * si + (par ^ 1);
+  Record* recs = ctx->d_records + (size_t)si * ((ctx->n ? ctx->n : 1) + 64);
+  const bool binned = ctx->d_perm != nullptr;
+  if (binned) ctx->fs[si].parity ^= 1;
+  *counters_index = 2 * si + par;
+  std::memset(&sa, 0, sizeof(sa));
+  sa.cloud = ctx->d_cloud;
+  sa.perm = ctx->d_perm;
+  sa.aabb = ctx->d_perm ? ctx->d_aabb : nullptr;
+  sa.active = ctx->d_active ? ctx->d_active + (size_t)si * ctx->n_chunks : nullptr;
+  sa.n_chunks = ctx->n_chunks;
+  sa.order = ctx->d_order;
+  sa.seed_blocks = binned ? ((cells > 16 ? cells : 16) + 255) / 256 : 0;
+  sa.counters_next = ctr_next;
+  sa.seed = (ctx->use_seed && fp.depth_culling) ? 1 : 0;
+  sa.zgrid = zg;
+  sa.zprev = zp;
+  sa.cells = cells;
+  sa.records = recs;
+  sa.counters = ctr;
+  sa.n = (uint32_t)ctx->n;
+  std::memset(&ra, 0, sizeof(ra));
+  ra.records = recs;
+  ra.zgrid = zg;
+  ra.counters = ctr;
+  ra.perm = ctx->d_perm;
+  ra.bgr = accumulate ? d_bgr : nullptr;
+  ra.pitch = pitch;
+  ra.mask = accumulate ? d_mask : nullptr;
+  ra.mask_pitch = mask_pitch;
+  ra.acc = ctx->d_acc;
+  ra.mask_acc = ctx->d_mask_acc;
+  ra.top_score = ctx->d_top_score;
+  ra.top_rgbf = ctx->d_top_rgbf;
+  ra.top_frame = ctx->d_top_frame;
+  ra.vis_bits = want_vis ? ctx->d_vis_bits : nullptr;
+  ra.pix_out = want_pix ? ctx->d_pix : nullptr;
+  ra.n = (uint32_t)ctx->n;
+  ra.top_m = ctx->prm.top_m;
+  ra.accum_mode = ctx->prm.accum_mode;
+  ra.sample_mode = ctx->prm.sample_mode;
+}
+
+// small clouds: fewer resolve CTAs (the records are a fraction of the points), SMs stay free for the frames on the other slots
+int resolve_grid_for(const pcp_ctx* ctx) {
+  int rgrid = ctx->resolve_grid;
+  const int by_work = (int)(ctx->n / 4096);
+  if (by_work < rgrid) rgrid = by_work > ctx->sm_count / 2 ? by_work : ctx->sm_count / 2;
+  return rgrid;
+}
+
+// The resources of slot `si` (z-grids, lists, records) were last used by work on the stream of slot fs[si].owner: `st` waits for it.
+int wait_for_owner(pcp_ctx* ctx, int si, cudaStream_t st) {
+  const int o = ctx->fs[si].owner;
+  if (o < 0 || ctx->fs[o].stream == st || !ctx->fs[o].used) return PCP_OK;
+  if ((ctx->batch_pending >> o) & 1u) {  // its done-event was being saved up for the end of the loop call
+    CU(cudaEventRecord(ctx->fs[o].ev_done, ctx->fs[o].stream));
+    ctx->batch_pending &= ~(1u << o);
+  }
+  CU(cudaStreamWaitEvent(st, ctx->fs[o].ev_done, 0));
+  return PCP_OK;
+}
+
 int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t pitch, const uint8_t* d_mask, size_t mask_pitch,
               bool want_vis, bool want_pix, bool accumulate, bool count_candidates, cudaEvent_t img_ready = nullptr,
               cudaEvent_t img_free = nullptr) {
@@ -119,37 +193,16 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
     pe = &ctx->prof_events[ctx->prof_used];
     ctx->prof_used += 4;
   }
-  const int cells = ctx->Wc * ctx->Hc;
-  // two z-grids and counter blocks per slot: this frame's pair was cleared by the slot's previous frame (or at set-up), the other
-  // pair holds that frame's final grid (the seed points) and is cleared by this frame's classify_kernel for the next one
-  const size_t c1 = cells ? cells : 1;
-  const int par = ctx->fs[si].parity;
-  unsigned long long* zg = (par ? ctx->d_zprev : ctx->d_zgrid) + (size_t)si * c1;
-  unsigned long long* zp = (par ? ctx->d_zgrid : ctx->d_zprev) + (size_t)si * c1;
-  FrameCounters* ctr = ctx->d_counters + 2 * si + par;
-  FrameCounters* ctr_next = ctx->d_counters + 2 * si + (par ^ 1);
-  Record* recs = ctx->d_records + (size_t)si * ((ctx->n ? ctx->n : 1) + 64);
-  const bool binned = ctx->d_perm != nullptr;
-  if (binned) ctx->fs[si].parity ^= 1;
-  else launch_zgrid_init(zg, cells, ctr, st);  // unbinned path: no classify_kernel, the grid is cleared per frame
-  if (pe) CU(cudaEventRecord(pe[1], st));
+  {
+    const int rc_o = wait_for_owner(ctx, si, st);
+    if (rc_o != PCP_OK) return rc_o;
+  }
   ScanArgs sa;
-  std::memset(&sa, 0, sizeof(sa));
-  sa.cloud = ctx->d_cloud;
-  sa.perm = ctx->d_perm;
-  sa.aabb = ctx->d_perm ? ctx->d_aabb : nullptr;
-  sa.active = ctx->d_active ? ctx->d_active + (size_t)si * ctx->n_chunks : nullptr;
-  sa.n_chunks = ctx->n_chunks;
-  sa.order = ctx->d_order;
-  sa.seed_blocks = binned ? ((cells > 16 ? cells : 16) + 255) / 256 : 0;
-  sa.counters_next = ctr_next;
-  sa.seed = (ctx->use_seed && fp.depth_culling) ? 1 : 0;
-  sa.zgrid = zg;
-  sa.zprev = zp;
-  sa.cells = cells;
-  sa.records = recs;
-  sa.counters = ctr;
-  sa.n = (uint32_t)ctx->n;
+  ResolveArgs ra;
+  int counters_index = 0;
+  fill_frame_args(ctx, si, fp, d_bgr, pitch, d_mask, mask_pitch, want_vis, want_pix, accumulate, sa, ra, &counters_index);
+  if (!ctx->d_perm) launch_zgrid_init(sa.zgrid, sa.cells, sa.counters, st);  // unbinned path: no classify_kernel, the grid is cleared per frame
+  if (pe) CU(cudaEventRecord(pe[1], st));
   int scan_rc = 0;
   HT(1, scan_rc = launch_scan(sa, fp, ctx->scan_grid, ctx->sm_count, count_candidates, ctx->device, st));
   if (scan_rc != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
@@ -159,30 +212,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   if (ctx->last_done && ctx->flight > 1 && ctx->prm.accum_mode != PCP_ACCUM_SUM) CU(cudaStreamWaitEvent(st, ctx->last_done, 0));
   if (img_ready) CU(cudaStreamWaitEvent(st, img_ready, 0));
 
-  ResolveArgs ra;
-  std::memset(&ra, 0, sizeof(ra));
-  ra.records = recs;
-  ra.zgrid = zg;
-  ra.counters = ctr;
-  ra.perm = ctx->d_perm;
-  ra.bgr = accumulate ? d_bgr : nullptr;
-  ra.pitch = pitch;
-  ra.mask = accumulate ? d_mask : nullptr;
-  ra.mask_pitch = mask_pitch;
-  ra.acc = ctx->d_acc;
-  ra.mask_acc = ctx->d_mask_acc;
-  ra.top_score = ctx->d_top_score;
-  ra.top_rgbf = ctx->d_top_rgbf;
-  ra.top_frame = ctx->d_top_frame;
-  ra.vis_bits = want_vis ? ctx->d_vis_bits : nullptr;
-  ra.pix_out = want_pix ? ctx->d_pix : nullptr;
-  ra.n = (uint32_t)ctx->n;
-  ra.top_m = ctx->prm.top_m;
-  ra.accum_mode = ctx->prm.accum_mode;
-  ra.sample_mode = ctx->prm.sample_mode;
-  int rgrid = ctx->resolve_grid;  // small clouds: fewer CTAs (the records are a fraction of the points), SMs stay free for the other slots
-  const int by_work = (int)(ctx->n / 4096);
-  if (by_work < rgrid) rgrid = by_work > ctx->sm_count / 2 ? by_work : ctx->sm_count / 2;
+  const int rgrid = resolve_grid_for(ctx);
   HT(2, launch_resolve(ra, fp, rgrid, st));
   if (pe) CU(cudaEventRecord(pe[3], st));
   if (batch && ctx->prm.accum_mode == PCP_ACCUM_SUM) ctx->batch_pending |= 1u << si;  // recorded once, by pcp_ctx::end_batch
@@ -191,9 +221,53 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   if (img_free) CU(cudaEventRecord(img_free, st));
   ctx->last_done = slot.ev_done;
   ctx->last_slot = si;
-  ctx->last_counters = 2 * si + par;
+  ctx->last_counters = counters_index;
+  slot.owner = si;
   ctx->frames_run++;
   ctx->launches += 3;  // classify + scan + resolve, or clear + scan + resolve (unbinned)
+  CU(cudaGetLastError());
+  return PCP_OK;
+}
+
+// k = 2 or 4 consecutive frames of a loop call in ONE classify, ONE scan and ONE resolve launch (blockIdx.y = frame), on the slots
+// base .. base + k - 1 and the stream of slot `base`.  SUM mode, pre-binned cloud, no per-frame outputs.  For small clouds the three
+// launches of a frame cost the submitting thread more (~9 us) than the GPU needs for the frame: see DESIGN 4.5.
+int run_group(pcp_ctx* ctx, int k, const FrameParams* fps, const uint8_t* const* d_bgr, size_t pitch, const uint8_t* const* d_mask, size_t mask_pitch) {
+  if (!ctx->d_cloud) { ctx->fail("no cloud: call pcp_set_cloud first"); return PCP_EINVAL; }
+  if (ctx->acc_scattered) { ctx->fail("the accumulators were consumed by pcp_exchange_finalize: call pcp_reset_accumulators first"); return PCP_EINVAL; }
+  bool any_mask = false;
+  for (int j = 0; j < k; j++) any_mask = any_mask || (d_mask && d_mask[j]);
+  if (any_mask && !ctx->d_mask_acc) {
+    CU(cudaMalloc(&ctx->d_mask_acc, sizeof(uint2) * (ctx->n ? ctx->n : 1)));
+    CU(cudaMemsetAsync(ctx->d_mask_acc, 0, sizeof(uint2) * (ctx->n ? ctx->n : 1), ctx->stream));
+    ctx->batch_forked = 0;  // every slot has to see this memset
+  }
+  const int base = (int)(ctx->frames_run % (uint64_t)ctx->flight);
+  pcp_ctx::FrameSlot& slot = ctx->fs[base];
+  cudaStream_t st = slot.stream;
+  if (!((ctx->batch_forked >> base) & 1u)) {
+    CU(cudaEventRecord(slot.ev_fork, ctx->stream));
+    CU(cudaStreamWaitEvent(st, slot.ev_fork, 0));
+    ctx->batch_forked |= 1u << base;
+  }
+  ScanArgs sa[kGroupMax];
+  ResolveArgs ra[kGroupMax];
+  int counters_index = 0;
+  for (int j = 0; j < k; j++) {
+    const int rc = wait_for_owner(ctx, base + j, st);
+    if (rc != PCP_OK) return rc;
+    fill_frame_args(ctx, base + j, fps[j], d_bgr[j], pitch, d_mask ? d_mask[j] : nullptr, mask_pitch, false, false, true, sa[j], ra[j], &counters_index);
+  }
+  if (launch_scan_group(sa, fps, k, ctx->sm_count, false, ctx->device, st) != 0) { ctx->fail("pass 1: kernel launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PCP_ECUDA; }
+  if (launch_resolve_group(ra, fps, k, resolve_grid_for(ctx), st) != 0) { ctx->fail("resolve: kernel launch failed"); return PCP_ECUDA; }
+  ctx->batch_pending |= 1u << base;  // the done-event of the group's stream is recorded once, by pcp_ctx::end_batch
+  slot.used = true;
+  for (int j = 0; j < k; j++) ctx->fs[base + j].owner = base;
+  ctx->last_done = slot.ev_done;
+  ctx->last_slot = base + k - 1;
+  ctx->last_counters = counters_index;
+  ctx->frames_run += (uint64_t)k;
+  ctx->launches += 3;
   CU(cudaGetLastError());
   return PCP_OK;
 }
@@ -298,12 +372,37 @@ int pcp_submit_frames_device(pcp_ctx* ctx, size_t n_frames, const double* poses7
                              const uint8_t* const* d_mask, size_t mask_pitch) {
   if (!ctx) return PCP_EINVAL;
   if (n_frames && (!poses7 || !d_bgr)) { ctx->fail("pcp_submit_frames_device: null argument"); return PCP_EINVAL; }
+  if (n_frames && (pitch < (size_t)ctx->prm.image_width * 3 || (d_mask && mask_pitch < (size_t)ctx->prm.image_width))) {
+    ctx->fail("pcp_submit_frames_device: bad image/pitch");
+    return PCP_EINVAL;
+  }
+  CU(cudaSetDevice(ctx->device));
   ctx->in_batch = true;
   ctx->batch_forked = 0;
   ctx->batch_pending = 0;
+  const int group = (ctx->prm.accum_mode == PCP_ACCUM_SUM && ctx->d_perm && !ctx->profiling) ? ctx->group : 1;
   int rc = PCP_OK;
-  for (size_t i = 0; i < n_frames && rc == PCP_OK; i++)
-    rc = submit_device(ctx, poses7 + 7 * i, T_opt16, d_bgr[i], pitch, d_mask ? d_mask[i] : nullptr, mask_pitch, nullptr, nullptr, nullptr);
+  size_t i = 0;
+  while (i < n_frames && rc == PCP_OK) {
+    const int base = (int)(ctx->frames_run % (uint64_t)ctx->flight);
+    int k = 1;
+    if (group >= 4 && base % 4 == 0 && base + 4 <= ctx->flight && n_frames - i >= 4) k = 4;
+    else if (group >= 2 && base % 2 == 0 && base + 2 <= ctx->flight && n_frames - i >= 2) k = 2;
+    if (k == 1) {
+      rc = submit_device(ctx, poses7 + 7 * i, T_opt16, d_bgr[i], pitch, d_mask ? d_mask[i] : nullptr, mask_pitch, nullptr, nullptr, nullptr);
+    } else {
+      FrameParams fps[kGroupMax];
+      const int frame_index0 = ctx->frame_index;
+      for (int j = 0; j < k && rc == PCP_OK; j++) {
+        if (!d_bgr[i + j]) { ctx->fail("pcp_submit_frames_device: null image"); rc = PCP_EINVAL; break; }
+        rc = frame_params_for_pose(ctx, poses7 + 7 * (i + j), T_opt16, fps[j]);
+        ctx->frame_index += ctx->frame_stride;
+      }
+      if (rc == PCP_OK) HT(5, rc = run_group(ctx, k, fps, d_bgr + i, pitch, d_mask ? d_mask + i : nullptr, mask_pitch));
+      if (rc != PCP_OK) ctx->frame_index = frame_index0;  // none of the group's frames was submitted
+    }
+    i += (size_t)k;
+  }
   HT(6, ctx->end_batch());  // also after an error: the frames submitted so far stay joinable
 #ifdef PCP_HOST_TIMING
   g_ht_frames += n_frames;

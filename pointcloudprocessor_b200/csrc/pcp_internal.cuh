@@ -108,7 +108,18 @@ struct ResolveArgs {
   int sample_mode;
 };
 
+// Arguments of up to kGroupMax frames for one launch (classify / scan / resolve _multi_kernel: blockIdx.y = frame of the group)
+template <typename A, int K>
+struct FramePack {
+  A a[K];
+  FrameParams fp[K];
+};
+constexpr int kGroupMax = 4;  // 4 x (112 + 400) bytes = half of the 4 KB a kernel may take as parameters
+
 void launch_zgrid_init(unsigned long long* zgrid, int cells, FrameCounters* counters, cudaStream_t s);
+// k = 2 or 4 frames of the same cloud on different slots in one launch each (pre-binned cloud only)
+int launch_scan_group(const ScanArgs* a, const FrameParams* fp, int k, int sm_count, bool count_candidates, int device, cudaStream_t s);
+int launch_resolve_group(const ResolveArgs* a, const FrameParams* fp, int k, int grid, cudaStream_t s);
 int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, int sm_count, bool count_candidates, int device, cudaStream_t s);
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s);
 void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t ioff, float4* out, cudaStream_t s);

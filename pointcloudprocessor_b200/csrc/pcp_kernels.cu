@@ -231,7 +231,7 @@ static_assert(kGroups >= 1 && kGroups * 32 == kChunk, "chunk size must be a mult
 // count to n_candidates.  Slot s of the sequence is chunk (s * chunk_mul) % n_chunks.
 // ---------------------------------------------------------------------------------------------------------------------
 template <bool kCount>
-__global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+__device__ __forceinline__ void classify_body(const ScanArgs& a, const FrameParams& fp) {
   const int lane = threadIdx.x & 31;
   unsigned int ncand = 0;
   pdl_launch_dependents();  // the scan kernel's CTAs may take their places (they wait for this grid before reading its list)
@@ -295,6 +295,16 @@ __global__ void __launch_bounds__(256) classify_kernel(const ScanArgs a, const _
     for (int o = 16; o > 0; o >>= 1) ncand += __shfl_down_sync(0xffffffffu, ncand, o);
     if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
   }
+}
+template <bool kCount>
+__global__ void __launch_bounds__(256) classify_kernel(const __grid_constant__ ScanArgs a, const __grid_constant__ FrameParams fp) {
+  classify_body<kCount>(a, fp);
+}
+// Several frames per launch (small clouds, pcp_submit_frames_device): blockIdx.y picks the frame's arguments.  The frames are on
+// different slots (own z-grids, lists, record buffers), so their CTAs are as independent as CTAs of different launches would be.
+template <bool kCount, int K>
+__global__ void __launch_bounds__(256) classify_multi_kernel(const __grid_constant__ FramePack<ScanArgs, K> p) {
+  classify_body<kCount>(p.a[blockIdx.y], p.fp[blockIdx.y]);
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -757,7 +767,7 @@ __device__ __forceinline__ void sts_volatile_v2(uint2* p, uint2 v) {
 }
 
 template <bool kCount>
-__global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_kernel(const ScanArgs a, const __grid_constant__ FrameParams fp) {
+__device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FrameParams& fp) {
   extern __shared__ __align__(128) unsigned char ring_smem[];
   __shared__ __align__(8) uint64_t s_bar[kWorkers][2];  // completion of the bulk copy into buffer b of worker w
   __shared__ __align__(8) uint2 s_work[kWorkCap];       // {chunk id, ticket number} or {_, kWorkFree}
@@ -1003,6 +1013,14 @@ __global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_kernel(
     if (lane == 0 && ncand) atomicAdd(&a.counters->n_candidates, ncand);
   }
 }
+template <bool kCount>
+__global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_kernel(const __grid_constant__ ScanArgs a, const __grid_constant__ FrameParams fp) {
+  scan_ring_body<kCount>(a, fp);
+}
+template <bool kCount, int K>
+__global__ void __launch_bounds__(kRingThreads, PCP_RING_CTAS) scan_ring_multi_kernel(const __grid_constant__ FramePack<ScanArgs, K> p) {
+  scan_ring_body<kCount>(p.a[blockIdx.y], p.fp[blockIdx.y]);
+}
 
 // Launch with the programmatic-stream-serialization attribute: the kernel's CTAs may start while the previous kernel of the
 // stream drains; the kernel itself waits (griddepcontrol.wait) before it touches anything its predecessor wrote.
@@ -1021,26 +1039,61 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
+// grids of the pre-binned pass 1: one persistent CTA per resident slot for a large cloud; a small cloud takes fewer CTAs
+// (>= PCP_CHUNKS_PER_CTA chunks each), so that the kernels of the frames in flight on the other slots find free SMs instead of
+// queueing behind a grid that fills the GPU (measured at C1, 15.6 k chunks: 64 / 128 per CTA)
+static void pass1_grids(const ScanArgs& a, int sm_count, int* cgrid, int* rgrid) {
+  int g = sm_count * PCP_RING_CTAS;
+  const int by_work = (int)(a.n_chunks / (unsigned)PCP_CHUNKS_PER_CTA);
+  if (by_work < g) g = by_work > sm_count / 2 ? by_work : sm_count / 2;
+  *rgrid = g;
+  *cgrid = a.seed_blocks + (int)((a.n_chunks + 255) / 256);
+}
+// the opt-in to > 48 KB of dynamic shared memory is a per-device attribute: one flag per device, not per process
+static int configure_pass1(int device) {
+  static bool configured[64] = {};
+  if (device >= 0 && device < 64 && configured[device]) return 0;
+#ifdef PCP_SCAN_V1
+  if (cudaFuncSetAttribute(scan_binned_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(scan_binned_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem) != cudaSuccess) return 1;
+#endif
+  if (cudaFuncSetAttribute(scan_ring_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(scan_ring_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(scan_ring_multi_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(scan_ring_multi_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(scan_ring_multi_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+  if (cudaFuncSetAttribute(scan_ring_multi_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
+  if (device >= 0 && device < 64) configured[device] = true;
+  return 0;
+}
+
+template <int K>
+static int launch_scan_group_k(const ScanArgs* a, const FrameParams* fp, int sm_count, bool count_candidates, cudaStream_t s) {
+  FramePack<ScanArgs, K> p;
+  for (int k = 0; k < K; k++) { p.a[k] = a[k]; p.fp[k] = fp[k]; }
+  int cgrid, rgrid;
+  pass1_grids(a[0], sm_count, &cgrid, &rgrid);
+  cudaError_t e;
+  if (count_candidates) e = launch_pdl(classify_multi_kernel<true, K>, dim3(cgrid, K), dim3(256), 0, s, p);
+  else e = launch_pdl(classify_multi_kernel<false, K>, dim3(cgrid, K), dim3(256), 0, s, p);
+  if (e != cudaSuccess) return 1;
+  if (count_candidates) e = launch_pdl(scan_ring_multi_kernel<true, K>, dim3(rgrid, K), dim3(kRingThreads), kRingSmem, s, p);
+  else e = launch_pdl(scan_ring_multi_kernel<false, K>, dim3(rgrid, K), dim3(kRingThreads), kRingSmem, s, p);
+  return e == cudaSuccess ? 0 : 1;
+}
+int launch_scan_group(const ScanArgs* a, const FrameParams* fp, int k, int sm_count, bool count_candidates, int device, cudaStream_t s) {
+  if (!a[0].aabb || configure_pass1(device) != 0) return 1;
+  if (k == 2) return launch_scan_group_k<2>(a, fp, sm_count, count_candidates, s);
+  if (k == 4) return launch_scan_group_k<4>(a, fp, sm_count, count_candidates, s);
+  return 1;
+}
+
 int launch_scan(const ScanArgs& a, const FrameParams& fp, int grid, int sm_count, bool count_candidates, int device, cudaStream_t s) {
   if (a.aabb) {
-    // one persistent CTA per resident slot for a large cloud; a small cloud takes fewer CTAs (>= PCP_CHUNKS_PER_CTA chunks each), so
-    // that the kernels of the frames in flight on the other slots find free SMs instead of queueing behind a grid that fills the GPU
-    int rgrid = sm_count * PCP_RING_CTAS;
-    const int by_work = (int)(a.n_chunks / (unsigned)PCP_CHUNKS_PER_CTA);  // measured at C1 (15.6 k chunks): 64 / 128 per CTA, see DESIGN 4.5
-    if (by_work < rgrid) rgrid = by_work > sm_count / 2 ? by_work : sm_count / 2;
+    int cgrid, rgrid;
+    pass1_grids(a, sm_count, &cgrid, &rgrid);
     (void)rgrid;
-    const int cgrid = a.seed_blocks + (int)((a.n_chunks + 255) / 256);
-    // the opt-in to > 48 KB of dynamic shared memory is a per-device attribute: one flag per device, not per process
-    static bool configured[64] = {};
-    if (device < 0 || device >= 64 || !configured[device]) {
-#ifdef PCP_SCAN_V1
-      if (cudaFuncSetAttribute(scan_binned_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem) != cudaSuccess) return 1;
-      if (cudaFuncSetAttribute(scan_binned_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinnedSmem) != cudaSuccess) return 1;
-#endif
-      if (cudaFuncSetAttribute(scan_ring_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
-      if (cudaFuncSetAttribute(scan_ring_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem) != cudaSuccess) return 1;
-      if (device >= 0 && device < 64) configured[device] = true;
-    }
+    if (configure_pass1(device) != 0) return 1;
     cudaError_t e;
     if (count_candidates) e = launch_pdl(classify_kernel<true>, dim3(cgrid), dim3(256), 0, s, a, fp);
     else e = launch_pdl(classify_kernel<false>, dim3(cgrid), dim3(256), 0, s, a, fp);
@@ -1130,7 +1183,7 @@ __device__ __noinline__ void bilinear_sample(const uint8_t* __restrict__ bgr, si
 #endif
 static constexpr int kRes = PCP_RES;
 
-__global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const ResolveArgs a, const __grid_constant__ FrameParams fp) {
+__device__ __forceinline__ void resolve_body(const ResolveArgs& a, const FrameParams& fp) {
   const unsigned int nrec = a.counters->n_records;
   unsigned int nvis = 0, ncol = 0;
   const unsigned int tile = blockDim.x * kRes;
@@ -1267,9 +1320,28 @@ __global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const Resolv
     if (cta_counts[1]) atomicAdd(&a.counters->n_colored, cta_counts[1]);
   }
 }
+__global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_kernel(const __grid_constant__ ResolveArgs a, const __grid_constant__ FrameParams fp) {
+  resolve_body(a, fp);
+}
+template <int K>
+__global__ void __launch_bounds__(256, PCP_RES_CTAS) resolve_multi_kernel(const __grid_constant__ FramePack<ResolveArgs, K> p) {
+  resolve_body(p.a[blockIdx.y], p.fp[blockIdx.y]);
+}
 
 void launch_resolve(const ResolveArgs& a, const FrameParams& fp, int grid, cudaStream_t s) {
   resolve_kernel<<<grid, 256, 0, s>>>(a, fp);
+}
+template <int K>
+static int launch_resolve_group_k(const ResolveArgs* a, const FrameParams* fp, int grid, cudaStream_t s) {
+  FramePack<ResolveArgs, K> p;
+  for (int k = 0; k < K; k++) { p.a[k] = a[k]; p.fp[k] = fp[k]; }
+  resolve_multi_kernel<K><<<dim3(grid, K), 256, 0, s>>>(p);
+  return 0;
+}
+int launch_resolve_group(const ResolveArgs* a, const FrameParams* fp, int k, int grid, cudaStream_t s) {
+  if (k == 2) return launch_resolve_group_k<2>(a, fp, grid, s);
+  if (k == 4) return launch_resolve_group_k<4>(a, fp, grid, s);
+  return 1;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

@@ -192,6 +192,46 @@ def test_finalize_picks_gather_by_point_order(oracle, built_lib):
     assert loc["shuffled"] < 0.5 < loc["voxel"], loc
 
 
+@pytest.mark.parametrize("flight,group", [(0, 0), (12, 4), (6, 2), (4, 4), (6, 4), (3, 1), (8, 1)])
+def test_frames_per_launch_invariant(oracle, built_lib, flight, group):
+    """pcp_submit_frames_device may put 2 or 4 consecutive frames into one launch of each kernel (small clouds: the launches bound the
+    frame rate).  Whatever the grouping, the slot count, the way the calls cut the frame list (groups that do not line up with the
+    slots fall back to single frames) and single host-image frames in between: the accumulators, mask accumulators included, are the
+    oracle's, bit for bit."""
+    import torch
+    from pointcloudprocessor_b200 import api
+    W, H = 320, 240
+    f = 23
+    sc = make_scene(150_000, f, W, H, masks=True)
+    cam_o = oracle.camera(sc["intr"], sc["dist"])
+    oc = oracle.Colorizer(cam_o, W, H, sc["cloud"])
+    for i, pose in enumerate(sc["poses"]):
+        oc.frame(pose, sc["images"][i], mask=sc["masks"][i] if i >= 9 else None)
+    acc_o, mh_o, mm_o = oc.accumulators()
+    d_img = torch.from_numpy(np.stack(sc["images"])).cuda()
+    d_msk = torch.from_numpy(np.stack(sc["masks"])).cuda()
+    iptr = np.array([d_img.data_ptr() + i * H * W * 3 for i in range(f)], np.uint64)
+    mptr = np.array([d_msk.data_ptr() + i * H * W for i in range(f)], np.uint64)
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    prm = api.default_params(image_size=(W, H), frames_in_flight=flight, frames_per_launch=group)
+    with api.Colorizer(cam, prm) as gc:
+        gc.set_cloud(sc["cloud"])
+        for rep in range(2):
+            gc.reset_accumulators()
+            poses = np.asarray(sc["poses"], np.float64)
+            gc.submit_frames_device(poses[0:5], iptr[0:5], W * 3)                       # 4 + 1 (or 2 + 2 + 1)
+            gc.submit_frame(sc["poses"][5], sc["images"][5])                            # a single frame from a host image in between
+            gc.submit_frames_device(poses[6:9], iptr[6:9], W * 3)                       # starts on a slot that is not a group boundary
+            gc.submit_frames_device(poses[9:22], iptr[9:22], W * 3, d_mask_ptrs=mptr[9:22], mask_pitch=W)   # masks begin mid-way
+            gc.submit_frame(sc["poses"][22], sc["images"][22], mask=sc["masks"][22])
+            acc_g, mh_g, mm_g = gc.accumulators()
+            assert np.array_equal(acc_g, acc_o), (flight, group, rep)
+            assert np.array_equal(mh_g, mh_o) and np.array_equal(mm_g, mm_o), (flight, group, rep)
+            rgb, cnt = gc.finalize()
+            assert np.array_equal(rgb, oc.finalize_sum()) and np.array_equal(cnt, acc_o[:, 3])
+    assert acc_o[:, 3].sum() > 0 and mh_o.sum() > 0
+
+
 def _big_shape_parity(oracle, n, f, W, H, n_images, flight):
     """Accumulators of f frames over an n-point cloud against the oracle (all host threads), frames submitted without per-frame
     outputs so that `flight` of them are in flight; images are cycled (the kernels see the same work)."""

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--sample", default="nearest", choices=["nearest", "bilinear"])
     ap.add_argument("--tag", default="")
     ap.add_argument("--flight", type=int, default=3, help="an extra frames_in_flight setting to time (1 and 3 always run)")
+    ap.add_argument("--group", type=int, default=0, help="frames_per_launch of the extra setting (0 = the library's choice)")
     ap.add_argument("--per-frame-calls", action="store_true", help="one pcp_submit_frame_device call per frame instead of the loop call")
     a = ap.parse_args()
     n, f, W, H = synth.CONFIGS[a.workload]
@@ -47,8 +48,9 @@ def main():
     out = {"lib": os.path.basename(_capi.LIB_PATH), "tag": a.tag, "workload": f"{a.workload}: {n} x {f} @ {W}x{H}", "sample": a.sample}
     stream = torch.cuda.Stream()
     sm = api.SAMPLE_BILINEAR if a.sample == "bilinear" else api.SAMPLE_NEAREST
-    for flight in (1, 3) + ((a.flight,) if a.flight not in (1, 3) else ()):
-        prm = api.default_params(image_size=(W, H), frames_in_flight=flight, sample_mode=sm)
+    for flight in (1, 3) + ((a.flight,) if a.flight not in (1, 3) else ()):  # --flight 0: slots and frames per launch chosen by the library
+        prm = api.default_params(image_size=(W, H), frames_in_flight=flight, sample_mode=sm,
+                                 frames_per_launch=(a.group if flight == a.flight else 1))
         gc = api.Colorizer(cam, prm, device=0)
         gc.set_stream(stream.cuda_stream)
         gc.set_cloud_device(cloud.data_ptr(), n)
@@ -87,7 +89,7 @@ def main():
             out["sha"] = hashlib.sha1(acc.tobytes()).hexdigest()[:16]
             out["counters_last_frame"] = gc.debug_counters()
         else:
-            out["pipelined" if flight == 3 else f"pipelined_flight{flight}"] = {"frame_us": round(per_frame_us, 2), "host_submit_us": round(host_us, 2), "pf_per_s": float(f"{n / (per_frame_us * 1e-6):.4g}")}
+            out["pipelined" if flight == 3 else f"pipelined_flight{flight}_group{a.group}"] = {"frame_us": round(per_frame_us, 2), "host_submit_us": round(host_us, 2), "pf_per_s": float(f"{n / (per_frame_us * 1e-6):.4g}")}
             acc, _, _ = gc.accumulators()
             out["sha3"] = hashlib.sha1(acc.tobytes()).hexdigest()[:16]
         gc.close()
