@@ -324,11 +324,18 @@ def run_native(args):
         else:
             gc.finalize_device(d_rgb.data_ptr(), d_cnt.data_ptr())
 
+    # N > 1: the map crosses the host link once in total — every rank uploads its slice, the slices are all-gathered over NVLink
+    # (pcp_set_cloud_sharded); --cloud-upload replicated: every rank uploads the whole map (round 2's first form, host-link bound)
+    sharded_upload = world > 1 and args.cloud_upload == "sharded"
+    slice_first, _slice_count = api.cloud_slice(n, rank, world)
+
     def step_e2e():
-        if pcl_layout:
-            gc.set_cloud_ptr(h_cloud32.data_ptr(), n, stride=32, intensity_offset=16)   # H2D cloud as pcl::PointXYZI (resets the accumulators)
+        stride, ioff = (32, 16) if pcl_layout else (16, 12)   # pcl::PointXYZI records, or float4
+        base = (h_cloud32 if pcl_layout else h_cloud).data_ptr()
+        if sharded_upload:
+            gc.set_cloud_sharded_ptr(base + slice_first * stride, n, stride=stride, intensity_offset=ioff)
         else:
-            gc.set_cloud_ptr(h_cloud.data_ptr(), n)      # H2D cloud as float4
+            gc.set_cloud_ptr(base, n, stride=stride, intensity_offset=ioff)   # H2D cloud (resets the accumulators)
         for g in mine:
             gc.submit_frame_ptr(poses_all[g], himg(g), W * 3)  # H2D image per frame, overlapped on the copy stream
         if world > 1:
@@ -477,7 +484,7 @@ def run_native(args):
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
     e2e_value = n * F * e2e_steps / e2e_s
-    h2d = world * n * (32 if pcl_layout else 16) + F * img_bytes   # every rank uploads the cloud; every frame's image goes up once
+    h2d = (1 if sharded_upload else world) * n * (32 if pcl_layout else 16) + F * img_bytes   # the cloud once (sharded) or per rank; every frame's image once
     d2h = n * 3 + n * 4                        # colours + counts, read back once (rank 0 when N > 1)
     e2e_matches_device = None
     if rank == 0:
@@ -657,7 +664,9 @@ def run_native(args):
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "colours_equal_device_path": e2e_matches_device,
-                    "cloud_layout": "pcl::PointXYZI, 32-byte records (the reference's)" if pcl_layout else "float4 {x,y,z,intensity}"},
+                    "cloud_layout": "pcl::PointXYZI, 32-byte records (the reference's)" if pcl_layout else "float4 {x,y,z,intensity}",
+                    "cloud_upload": ("each rank uploads 1/N of the map, ncclAllGather over NVLink (pcp_set_cloud_sharded)" if sharded_upload
+                                     else ("every rank uploads the whole map" if world > 1 else "whole map"))},
             "roofline": roofline,
         }
         if exchange_ms is not None:
@@ -713,6 +722,8 @@ def main():
     ap.add_argument("--no-rebalance", action="store_true", help="strong scaling: keep the equal-count dealing of the frame blocks")
     ap.add_argument("--frame-block", type=int, default=0, help="strong scaling: consecutive keyframes per dealt block (default 25)")
     ap.add_argument("--sample", default="nearest", choices=["nearest", "bilinear"])
+    ap.add_argument("--cloud-upload", default="sharded", choices=["sharded", "replicated"],
+                    help="e2e leg at N > 1: each rank uploads its slice of the map and the slices are all-gathered, or every rank uploads all of it")
     ap.add_argument("--cloud-layout", default="pcl", choices=["pcl", "float4"], help="record layout of the cloud handed over in the e2e leg")
     ap.add_argument("--parity-frames", type=int, default=2, help="N>1: frames per rank of the oracle check of the exchanged accumulators")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")

@@ -111,6 +111,13 @@ int pcp_host_free(void* p);
  * Copies (asynchronously when `points` is pinned memory: keep it valid until the next synchronising call, e.g.
  * pcp_synchronize or pcp_finalize); converts to float4 SoA on the device; resets the accumulators. */
 int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset);
+/* Multi-GPU hand-over of the same map (after pcp_nccl_init; no counterpart in the reference, which is one process): the map crosses the
+ * host link ONCE in total instead of once per GPU.  Rank r of G passes only ITS slice of the records — points [first, first + count) as
+ * pcp_cloud_slice computes them (G equal slices of ceil(n_total / G) points, the last one shorter) — and the slices are all-gathered
+ * over NVLink (ncclAllGather, in place) into every rank's full copy; everything else is pcp_set_cloud.  Collective: every rank calls
+ * it, with the same n_total and layout.  Measured host-link bandwidth per rank halves from 2 to 4 ranks on these boxes. */
+int pcp_set_cloud_sharded(pcp_ctx* ctx, const void* slice_points, size_t n_total, size_t stride_bytes, size_t intensity_offset);
+int pcp_cloud_slice(size_t n_total, int rank, int nranks, size_t* first, size_t* count);
 /* Same with a device-resident float4 {x,y,z,intensity} array (no host copy). */
 int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n);
 size_t pcp_num_points(const pcp_ctx* ctx);

@@ -49,6 +49,14 @@ def _ptr(a):
     return None if a is None else C.c_void_p(a.ctypes.data)
 
 
+def cloud_slice(n_total: int, rank: int, world: int):
+    """(first, count) of rank's slice of an n_total-point map (pcp_cloud_slice)."""
+    f, c = C.c_size_t(0), C.c_size_t(0)
+    if _capi.load().pcp_cloud_slice(n_total, rank, world, C.byref(f), C.byref(c)) != 0:
+        raise PcpError("pcp_cloud_slice: bad arguments")
+    return int(f.value), int(c.value)
+
+
 class Colorizer:
     """Device-resident state of pcdColorizationAndSmooth (src/PointCloudProcessor.cpp:474-602) on one GPU."""
 
@@ -206,6 +214,22 @@ class Colorizer:
         """set_cloud from a raw (e.g. pinned) host pointer."""
         self._check(self._L.pcp_set_cloud(self._h, C.c_void_p(host_ptr), n, stride, intensity_offset), "pcp_set_cloud")
         self.n = n
+
+    def set_cloud_sharded_ptr(self, slice_host_ptr: int, n_total: int, stride: int = 16, intensity_offset: int = 12):
+        """Multi-GPU hand-over (after nccl_init): this rank uploads only its slice of the map (`cloud_slice`), the slices are
+        all-gathered over NVLink.  Collective: every rank calls it."""
+        self._check(self._L.pcp_set_cloud_sharded(self._h, C.c_void_p(slice_host_ptr), n_total, stride, intensity_offset), "pcp_set_cloud_sharded")
+        self.n = n_total
+
+    def set_cloud_sharded(self, points: np.ndarray, rank: int, world: int, intensity_offset: int | None = None):
+        """`points`: the WHOLE (N,k) float32 array; only this rank's slice of it is uploaded."""
+        pts = np.ascontiguousarray(points, np.float32)
+        stride = pts.shape[1] * 4
+        if intensity_offset is None:
+            intensity_offset = 12 if pts.shape[1] == 4 else (16 if pts.shape[1] >= 5 else 8)
+        first, count = cloud_slice(pts.shape[0], rank, world)
+        self._cloud_keepalive = pts
+        self.set_cloud_sharded_ptr(pts.ctypes.data + first * stride, pts.shape[0], stride, intensity_offset)
 
     def submit_frame_ptr(self, pose7, bgr_ptr: int, pitch: int, mask_ptr: int = 0, mask_pitch: int = 0, T_opt=None):
         """submit_frame from raw (e.g. pinned) host pointers; asynchronous."""

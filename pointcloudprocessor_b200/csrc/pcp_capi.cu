@@ -320,13 +320,10 @@ int pcp_reset_accumulators(pcp_ctx* ctx) {
   return PCP_OK;
 }
 
-int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset) {
-  if (!ctx) return PCP_EINVAL;
-  if ((!points && n) || stride_bytes < 12 || (stride_bytes & 3) || (intensity_offset & 3) || intensity_offset + 4 > stride_bytes ||
-      n >= 0xfffffff0ull) {
-    ctx->fail("pcp_set_cloud: invalid layout (n=%zu stride=%zu intensity_offset=%zu)", n, stride_bytes, intensity_offset);
-    return PCP_EINVAL;
-  }
+// pcp_set_cloud and pcp_set_cloud_sharded.  `first` / `count`: the part of the cloud `points` holds (everything, or the rank's slice);
+// slice > 0: all-gather the slices over NCCL afterwards (every rank's slice is `slice` points, the last one possibly shorter).
+static int set_cloud_impl(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset, size_t first, size_t count,
+                          size_t slice) {
   CU(cudaSetDevice(ctx->device));
   const bool reuse = ctx->d_cloud && ctx->n == n && n > 0;  // same-size cloud: keep every allocation, only re-upload
   const size_t n1 = n ? n : 1;
@@ -334,24 +331,28 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
   if (!reuse) {
     CU(ctx->drain());
     ctx->free_cloud();
-    CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * n1));
+    CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * (n1 + pcp_ctx::kAccPad)));  // padded like the accumulators: nranks equal slices fit
   }
-  if (n) {
+  if (count) {
     if (stride_bytes == 16 && intensity_offset == 12) {
-      CU(cudaMemcpyAsync(ctx->d_cloud, points, sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
+      CU(cudaMemcpyAsync(ctx->d_cloud + first, points, sizeof(float4) * count, cudaMemcpyHostToDevice, ctx->stream));
     } else {
       // record layouts other than float4 (pcl::PointXYZI: 32 bytes, intensity at 16) are staged on the device and converted there; the
       // staging buffer is kept across uploads and nothing synchronises (the copy, the conversion and the pre-binning are stream-ordered)
-      const size_t need = n * stride_bytes;
+      const size_t need = count * stride_bytes;
       if (ctx->aos_bytes < need) {
         if (ctx->d_aos) { CU(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_aos); ctx->d_aos = nullptr; ctx->aos_bytes = 0; }
         CU(cudaMalloc(&ctx->d_aos, need));
         ctx->aos_bytes = need;
       }
       CU(cudaMemcpyAsync(ctx->d_aos, points, need, cudaMemcpyHostToDevice, ctx->stream));
-      launch_aos_to_soa(ctx->d_aos, n, stride_bytes, intensity_offset, ctx->d_cloud, ctx->stream);
+      launch_aos_to_soa(ctx->d_aos, count, stride_bytes, intensity_offset, ctx->d_cloud + first, ctx->stream);
       ctx->launches++;
     }
+  }
+  if (slice && n) {
+    const int rc = nccl_all_gather_cloud(ctx, ctx->d_cloud, slice);
+    if (rc != PCP_OK) return rc;
   }
   choose_flight(ctx, n);
   {
@@ -362,12 +363,51 @@ int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_byte
   return alloc_cloud_state(ctx, n);
 }
 
+static int check_cloud_layout(pcp_ctx* ctx, bool points_missing, size_t n, size_t stride_bytes, size_t intensity_offset, const char* who) {
+  if (points_missing || stride_bytes < 12 || (stride_bytes & 3) || (intensity_offset & 3) || intensity_offset + 4 > stride_bytes ||
+      n >= 0xfffffff0ull) {
+    ctx->fail("%s: invalid layout (n=%zu stride=%zu intensity_offset=%zu)", who, n, stride_bytes, intensity_offset);
+    return PCP_EINVAL;
+  }
+  return PCP_OK;
+}
+
+int pcp_set_cloud(pcp_ctx* ctx, const void* points, size_t n, size_t stride_bytes, size_t intensity_offset) {
+  if (!ctx) return PCP_EINVAL;
+  const int rc = check_cloud_layout(ctx, !points && n, n, stride_bytes, intensity_offset, "pcp_set_cloud");
+  if (rc != PCP_OK) return rc;
+  return set_cloud_impl(ctx, points, n, stride_bytes, intensity_offset, 0, n, 0);
+}
+
+int pcp_cloud_slice(size_t n_total, int rank, int nranks, size_t* first, size_t* count) {
+  if (nranks < 1 || rank < 0 || rank >= nranks || !first || !count) return PCP_EINVAL;
+  const size_t slice = (n_total + (size_t)nranks - 1) / (size_t)nranks;
+  const size_t f = (size_t)rank * slice < n_total ? (size_t)rank * slice : n_total;
+  *first = f;
+  *count = n_total - f < slice ? n_total - f : slice;
+  return PCP_OK;
+}
+
+/* The map of a multi-GPU job crosses the host link ONCE in total: every rank uploads only its slice (pcp_cloud_slice) and the slices
+ * are all-gathered over NVLink into every rank's full copy.  Collective: every rank of the communicator calls it with the same n_total. */
+int pcp_set_cloud_sharded(pcp_ctx* ctx, const void* slice_points, size_t n_total, size_t stride_bytes, size_t intensity_offset) {
+  if (!ctx) return PCP_EINVAL;
+  if (!ctx->nccl_comm) { ctx->fail("pcp_set_cloud_sharded: call pcp_nccl_init first"); return PCP_EINVAL; }
+  if (ctx->nccl_nranks > pcp_ctx::kAccPad) { ctx->fail("pcp_set_cloud_sharded: more than %d ranks", (int)pcp_ctx::kAccPad); return PCP_EINVAL; }
+  size_t first = 0, count = 0;
+  pcp_cloud_slice(n_total, ctx->nccl_rank, ctx->nccl_nranks, &first, &count);
+  const int rc = check_cloud_layout(ctx, !slice_points && count, n_total, stride_bytes, intensity_offset, "pcp_set_cloud_sharded");
+  if (rc != PCP_OK) return rc;
+  const size_t slice = (n_total + (size_t)ctx->nccl_nranks - 1) / (size_t)ctx->nccl_nranks;
+  return set_cloud_impl(ctx, slice_points, n_total, stride_bytes, intensity_offset, first, count, slice);
+}
+
 int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n) {
   if (!ctx || (!d_xyzi && n) || n >= 0xfffffff0ull) return PCP_EINVAL;
   CU(cudaSetDevice(ctx->device));
   CU(ctx->drain());
   ctx->free_cloud();
-  CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * (n ? n : 1)));
+  CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * ((n ? n : 1) + pcp_ctx::kAccPad)));
   if (n) CU(cudaMemcpyAsync(ctx->d_cloud, d_xyzi, sizeof(float4) * n, cudaMemcpyDeviceToDevice, ctx->stream));
   choose_flight(ctx, n);
   {

@@ -121,3 +121,5 @@ struct pcp_ctx {
 
 int scan_ctas_per_sm();
 void nccl_teardown(pcp_ctx* ctx);
+// in-place all-gather of `slice` float4 points per rank on ctx->stream (rank r's points sit at d_cloud + r * slice); PCP_* code
+int nccl_all_gather_cloud(pcp_ctx* ctx, float4* d_cloud, size_t slice);

@@ -137,6 +137,13 @@ void nccl_teardown(pcp_ctx* ctx) {
   ctx->nccl_comm = nullptr;
 }
 
+int nccl_all_gather_cloud(pcp_ctx* ctx, float4* d_cloud, size_t slice) {
+  if (!ctx->nccl_comm || !api().ok) { ctx->fail("pcp_set_cloud_sharded: call pcp_nccl_init first"); return PCP_EINVAL; }
+  const int rc = api().all_gather(d_cloud + (size_t)ctx->nccl_rank * slice, d_cloud, slice * 4, kNcclUint32, (NcclComm)ctx->nccl_comm, ctx->stream);
+  if (rc != 0) { ctx->fail("ncclAllGather (cloud): %s", api().error_string ? api().error_string(rc) : "error"); return PCP_ENCCL; }
+  return PCP_OK;
+}
+
 // mask accumulators {hits, max}: split into two planes, all-reduced with sum and max, joined (every rank makes the same calls)
 static int exchange_masks(pcp_ctx* ctx) {
   NcclComm comm = (NcclComm)ctx->nccl_comm;

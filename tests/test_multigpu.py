@@ -9,7 +9,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-N_POINTS, N_FRAMES, W, H = 60_000, 9, 480, 360
+N_POINTS, N_FRAMES, W, H = 60_001, 9, 480, 360
 
 
 def _free_port():
@@ -60,7 +60,18 @@ def _worker(rank, world, port, mode, sharding, exchange, out_dir):
         ids = [gc.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         gc.nccl_init(ids[0], rank, world)
-        gc.set_cloud(sc["cloud"])
+        if exchange == "exchange_finalize":
+            # the map crosses the host link once: every rank uploads its slice, the slices are all-gathered (pcp_set_cloud_sharded);
+            # float4 records for one sharding, the reference's 32-byte pcl::PointXYZI records for the other; the point count is
+            # odd, so the last slice is the shorter one
+            cloud = sc["cloud"]
+            if sharding == "blocks":
+                pcl = np.zeros((cloud.shape[0], 8), np.float32)
+                pcl[:, :3], pcl[:, 3], pcl[:, 4] = cloud[:, :3], 1.0, cloud[:, 3]
+                cloud = pcl
+            gc.set_cloud_sharded(cloud, rank, world)
+        else:
+            gc.set_cloud(sc["cloud"])
         mine = frames_of_rank(N_FRAMES, rank, world, sharding)
         if sharding == "interleaved":
             gc.set_frame_numbering(rank, world)
