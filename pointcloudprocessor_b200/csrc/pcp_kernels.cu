@@ -766,6 +766,20 @@ __device__ __forceinline__ void sts_volatile_v2(uint2* p, uint2 v) {
   asm volatile("st.volatile.shared.v2.u32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "r"(v.x), "r"(v.y) : "memory");
 }
 
+#ifdef PCP_TIMELINE  // tools/ variant only (tools/scan_timeline.py): when each CTA of the last scan_ring launch reached its milestones
+__device__ unsigned long long g_timeline[2048][8];
+__device__ __forceinline__ void tl_stamp(int k) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  if (blockIdx.x < 2048u) g_timeline[blockIdx.x][k] = t;
+}
+#define TL(k) tl_stamp(k)
+#define TLV(k, v) do { if (blockIdx.x < 2048u) g_timeline[blockIdx.x][k] = (unsigned long long)(v); } while (0)
+#else
+#define TL(k) ((void)0)
+#define TLV(k, v) ((void)0)
+#endif
+
 template <bool kCount>
 __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FrameParams& fp) {
   extern __shared__ __align__(128) unsigned char ring_smem[];
@@ -784,6 +798,7 @@ __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FramePar
 
   if (threadIdx.x < kWorkCap) s_work[threadIdx.x] = make_uint2(0u, kWorkFree);
   if (threadIdx.x == 0) {
+    TL(0);
     for (int w = 0; w < kWorkers; w++) { mbar_init(&s_bar[w][0], 1u); mbar_init(&s_bar[w][1], 1u); }
     s_ticket = 0u;
     s_total = 0xffffffffu;
@@ -793,6 +808,7 @@ __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FramePar
   pdl_wait();  // everything above overlaps the tail of classify_kernel (programmatic dependent launch); its list is read from here on
   // this CTA may have been resident since before classify_kernel wrote its list: read that data from L2, never through L1 / the
   // read-only path (ld.global.nc promises data that is constant for the lifetime of THIS kernel, which started earlier)
+  if (threadIdx.x == 0) TL(1);
   const uint32_t n_active = __ldcg(&a.counters->n_active_blocks);
   const uint32_t G = gridDim.x;
   // static share: entries c + G j, j < n_static (the same count for every CTA); pool: entries [n_static * G, n_active)
@@ -861,6 +877,7 @@ __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FramePar
       if (valid) ent = j < (uint32_t)kEntCap ? s_ent[j] : __ldcg(a.active + blockIdx.x + G * j);
       offer(valid, ent);
     }
+    if (lane == 0) { TL(2); TLV(6, count); }
     for (;;) {  // the common pool
       uint32_t i0 = 0;
       if (lane == 0) i0 = pool0 + atomicAdd(&a.counters->pool_next, (unsigned int)kPoolBatch);
@@ -873,6 +890,7 @@ __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FramePar
       offer(valid, ent);
     }
     if (lane == 0) {
+      TL(3); TLV(7, count);
       s_total = count;  // tickets >= count find no work
       if (count) atomicAdd(&a.counters->stats[1], count);  // chunks fetched (1 KB bulk copies) by this CTA: the kernel's cloud traffic
     }
@@ -947,9 +965,16 @@ __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FramePar
     have[0] = fetch(0, base[0], cnt[0]);
     have[1] = have[0] ? fetch(1, base[1], cnt[1]) : false;
     // one chunk out of buffer B (a compile-time index: base / cnt / phase / have stay in registers)
+#ifdef PCP_TIMELINE
+    bool tl_first = true;
+#endif
     auto step = [&](auto B) {
       constexpr int b = decltype(B)::value;
       mbar_wait(&s_bar[warp][b], phase[b]);
+#ifdef PCP_TIMELINE
+      if (tl_first && warp == 0 && lane == 0) TL(4);
+      tl_first = false;
+#endif
       phase[b] ^= 1u;
       float4 p[kGroups];
 #pragma unroll
@@ -1001,6 +1026,7 @@ __device__ __forceinline__ void scan_ring_body(const ScanArgs& a, const FramePar
     }
     __syncwarp();
     if (n1 > 0) stage_b(n1);
+    if (warp == 0 && lane == 0) TL(5);
     if (rn > 0) {
       unsigned int rbase = 0;
       if (lane == 0) rbase = atomicAdd(&a.counters->n_records, (unsigned int)rn);
@@ -1672,3 +1698,10 @@ int scan_ctas_per_sm() {
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcp::scan_kernel<false>, pcp::kScanThreads, 0) != cudaSuccess || occ < 1) occ = 2;
   return occ;
 }
+
+#ifdef PCP_TIMELINE
+extern "C" int pcp_debug_timeline(unsigned long long* out, size_t ctas) {
+  if (!out || ctas > 2048) return 1;
+  return cudaMemcpyFromSymbol(out, pcp::g_timeline, ctas * 8 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2;
+}
+#endif
