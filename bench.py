@@ -435,7 +435,11 @@ def run_native(args):
                              "with the ranks' measured relative speeds; untimed steps after the warm-up; results do not depend on the partition" % B_}
 
     sampler = ClockSampler(local) if rank == 0 else None
-    gc.profile_enable(True)
+    # per-kernel events inside the timed region (informative: "kernel_ms_per_frame_in_timed_region") only for large clouds: they are four
+    # event records per frame on the submitting thread and keep the library from putting several small frames into one launch, and for
+    # clouds of <= 4e6 points the submitting thread is what bounds the frame rate
+    timed_profile = n > 4_000_000
+    gc.profile_enable(timed_profile)
     l0 = gc.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -583,7 +587,7 @@ def run_native(args):
     if rank == 0:
         peak, peak_src = _peaks()
         frames_prof = max(prof["frames"], 1)
-        kern_ms_pipelined = {"scan": prof["scan_ms"] / frames_prof, "resolve": prof["resolve_ms"] / frames_prof}
+        kern_ms_pipelined = {"scan": prof["scan_ms"] / frames_prof, "resolve": prof["resolve_ms"] / frames_prof} if timed_profile else None
         prm1 = api.default_params(image_size=(W, H), frames_in_flight=1, sample_mode=sample_mode)
         gc1 = api.Colorizer(cam, prm1, device=local)
         gc1.set_stream(stream.cuda_stream)

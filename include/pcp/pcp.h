@@ -85,7 +85,7 @@ typedef struct {
 /* n_candidates is an internal of the reference (indices.size() before its second pass) that nothing downstream reads;
  * counting it exactly costs a wider FP32 classification per point.  Frames submitted without a pcp_frame_out, or with
  * this flag, use the kernel variant that skips the count.  Every other output is identical. */
-enum { PCP_OUT_SKIP_CANDIDATES = 1 };
+enum { PCP_OUT_SKIP_CANDIDATES = 1, PCP_OUT_PIXELS_ON_DEVICE = 2 /* keep the frame's pixel indices on the device (for pcp_frame_mask_cloud) without copying them out */ };
 
 void pcp_default_params(pcp_params* p);
 int pcp_abi_version(void);
@@ -206,6 +206,14 @@ int pcp_finalize(pcp_ctx* ctx, uint8_t* rgb_out, uint32_t* count_out);
  * not (0,0,0), in the caller's point order, as pcl::PointXYZRGB payloads {x, y, z, b | g << 8 | r << 16 | 255 << 24} (16 bytes each).
  * *n_out = their number; at most `cap` records are written to points_out (NULL: count only).  Synchronises. */
 int pcp_finalize_compact(pcp_ctx* ctx, void* points_out, size_t cap, size_t* n_out);
+
+/* generateSegmentMap (cpp:769-816) and the per-keyframe cloud of cpp:533-546 for the frame JUST submitted, built on the device: the
+ * points that received a pixel, in the map's order, as 20-byte PointXYZRGBMask records (include/FrameData.hpp:68-87): {float x, y, z in
+ * the camera frame (pcl::transformPointCloud, cpp:521); uint8 b, g, r of the (adjusted) image; uint8 255; uint16 mask value; 2 bytes
+ * of padding}; mask == 255 paints the point red (cpp:806-811).  The frame must have been submitted alone (pcp_submit_frame or
+ * pcp_submit_frame_device) with a mask and with pcp_frame_out.pixel_index or flags & PCP_OUT_PIXELS_ON_DEVICE; anything else returns
+ * PCP_EINVAL.  *n_out = the number of such points; at most `cap` records are written (records_out NULL: count only).  Synchronises. */
+int pcp_frame_mask_cloud(pcp_ctx* ctx, void* records_out, size_t cap, size_t* n_out);
 
 /* pcp_compact_bits_noalloc — NO COUNTERPART IN THE REFERENCE: added for callers that cannot
  * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).

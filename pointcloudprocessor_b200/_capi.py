@@ -35,6 +35,7 @@ class FrameOut(C.Structure):
 
 
 OUT_SKIP_CANDIDATES = 1
+OUT_SKIP_CANDIDATES, OUT_PIXELS_ON_DEVICE = 1, 2
 DEBUG_NO_PREFILTER, DEBUG_NO_SEED, DEBUG_FINALIZE_ONEPASS, DEBUG_FINALIZE_TWOPASS = 1, 2, 4, 8
 
 
@@ -60,7 +61,7 @@ class ProcessStats(C.Structure):
 
 SYMBOLS = [
     "pcp_default_params", "pcp_abi_version", "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_set_stream", "pcp_get_stream",
-    "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_set_cloud", "pcp_set_cloud_sharded", "pcp_cloud_slice", "pcp_set_cloud_device", "pcp_num_points",
+    "pcp_synchronize", "pcp_host_alloc", "pcp_host_free", "pcp_frame_mask_cloud", "pcp_set_cloud", "pcp_set_cloud_sharded", "pcp_cloud_slice", "pcp_set_cloud_device", "pcp_num_points",
     "pcp_submit_frame", "pcp_submit_frame_device", "pcp_cull", "pcp_cull_pose", "pcp_pose_matrices", "pcp_get_accumulators",
     "pcp_accumulators_device", "pcp_reset_accumulators", "pcp_nccl_unique_id", "pcp_nccl_init", "pcp_allreduce", "pcp_finalize", "pcp_finalize_device", "pcp_profile_enable", "pcp_profile_read",
     "pcp_nid_create", "pcp_nid_destroy", "pcp_nid_eval", "pcp_nid_eval_multi", "pcp_nid_eval_grad", "pcp_nid_eval_multi_grad", "pcp_launch_count", "pcp_debug_counters", "pcp_hsv_roundtrip", "pcp_process", "pcp_pcd_read_xyzi", "pcp_pcd_write_xyzi", "pcp_image_read", "pcp_io_free",
@@ -129,6 +130,7 @@ def load():
     L.pcp_host_free.argtypes = [vp]
     L.pcp_set_cloud.argtypes = [vp, vp, sz, sz, sz]
     L.pcp_set_cloud_device.argtypes = [vp, vp, sz]
+    L.pcp_frame_mask_cloud.argtypes = [vp, vp, sz, C.POINTER(sz)]
     L.pcp_set_cloud_sharded.argtypes = [vp, vp, sz, sz, sz]
     L.pcp_cloud_slice.argtypes = [sz, C.c_int, C.c_int, C.POINTER(sz), C.POINTER(sz)]
     L.pcp_num_points.argtypes = [vp]

@@ -150,7 +150,7 @@ class Colorizer:
         return None if T is None else np.ascontiguousarray(np.asarray(T, np.float64).T.reshape(-1))
 
     def submit_frame(self, pose7, bgr: np.ndarray, mask: np.ndarray | None = None, T_opt=None, want_vis=False, want_pix=False,
-                     want_counts=False, count_candidates=True):
+                     want_counts=False, count_candidates=True, keep_pix_on_device=False):
         pose = np.ascontiguousarray(pose7, np.float64)
         T = self._mat16(T_opt)
         if bgr.dtype != np.uint8 or bgr.ndim != 3 or bgr.shape[2] != 3 or bgr.strides[2] != 1 or bgr.strides[1] != 3:
@@ -164,9 +164,9 @@ class Colorizer:
             mp = mask.strides[0]
         out = None
         vis = pix = None
-        if want_vis or want_pix or want_counts:
+        if want_vis or want_pix or want_counts or keep_pix_on_device:
             out = FrameOut()
-            out.flags = 0 if count_candidates else _capi.OUT_SKIP_CANDIDATES
+            out.flags = (0 if count_candidates else _capi.OUT_SKIP_CANDIDATES) | (_capi.OUT_PIXELS_ON_DEVICE if keep_pix_on_device else 0)
             if want_vis:
                 vis = np.zeros((self.n + 31) // 32, np.uint32)
                 out.visible_bits = vis.ctypes.data
@@ -188,6 +188,18 @@ class Colorizer:
         if pix is not None:
             res["pix"] = pix
         return res
+
+    MASK_RECORD = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), ("g", "u1"), ("r", "u1"), ("a", "u1"), ("mask", "<u2"), ("pad", "<u2")])
+
+    def frame_mask_cloud(self) -> np.ndarray:
+        """generateSegmentMap (cpp:769-816) for the frame just submitted (alone, with a mask, with want_pix or keep_pix_on_device):
+        the points that received a pixel as PointXYZRGBMask records (camera-frame xyz, bgr, mask; mask 255 -> red), map order."""
+        m = C.c_size_t(0)
+        self._check(self._L.pcp_frame_mask_cloud(self._h, None, 0, C.byref(m)), "pcp_frame_mask_cloud")
+        out = np.empty(m.value, self.MASK_RECORD)
+        if m.value:
+            self._check(self._L.pcp_frame_mask_cloud(self._h, out.ctypes.data, m.value, C.byref(m)), "pcp_frame_mask_cloud")
+        return out
 
     def submit_frame_device(self, pose7, d_bgr: int, pitch: int, d_mask: int = 0, mask_pitch: int = 0, T_opt=None, want_counts=False):
         pose = np.ascontiguousarray(pose7, np.float64)

@@ -87,6 +87,11 @@ struct pcp_ctx {
   uint32_t batch_forked = 0;    // slots whose stream already waited for ctx->stream in this call
   uint32_t batch_pending = 0;   // slots whose ev_done is still to be recorded
   void end_batch();
+  // the last single frame, for pcp_frame_mask_cloud: its device image / mask, its float transform, and whether d_pix holds its pixels
+  const uint8_t* last_bgr = nullptr; size_t last_pitch = 0;
+  const uint8_t* last_mask = nullptr; size_t last_mask_pitch = 0;
+  pcp::Xf34 last_w2c = {};
+  bool pix_valid = false;
   cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
   unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys: grid 0 of every slot
   unsigned long long* d_zprev = nullptr;       // kMaxFlight x Wc*Hc: grid 1 of every slot (frames of a slot alternate; the other grid

@@ -222,6 +222,8 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ctx->last_done = slot.ev_done;
   ctx->last_slot = si;
   ctx->last_counters = counters_index;
+  ctx->pix_valid = want_pix && accumulate;
+  ctx->last_bgr = d_bgr; ctx->last_pitch = pitch; ctx->last_mask = d_mask; ctx->last_mask_pitch = mask_pitch; ctx->last_w2c = fp.w2c;
   slot.owner = si;
   ctx->frames_run++;
   ctx->launches += 3;  // classify + scan + resolve, or clear + scan + resolve (unbinned)
@@ -266,6 +268,7 @@ int run_group(pcp_ctx* ctx, int k, const FrameParams* fps, const uint8_t* const*
   ctx->last_done = slot.ev_done;
   ctx->last_slot = base + k - 1;
   ctx->last_counters = counters_index;
+  ctx->pix_valid = false;
   ctx->frames_run += (uint64_t)k;
   ctx->launches += 3;
   CU(cudaGetLastError());
@@ -311,7 +314,7 @@ static int submit_device(pcp_ctx* ctx, const double pose7[7], const double* T_op
   int rc = PCP_OK;
   HT(4, rc = frame_params_for_pose(ctx, pose7, T_opt16, fp));
   if (rc != PCP_OK) return rc;
-  HT(5, rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && out->pixel_index, true,
+  HT(5, rc = run_frame(ctx, fp, d_bgr, pitch, d_mask, mask_pitch, out && out->visible_bits, out && (out->pixel_index || (out->flags & PCP_OUT_PIXELS_ON_DEVICE)), true,
                        out && !(out->flags & PCP_OUT_SKIP_CANDIDATES), img_ready, img_free));
   if (rc != PCP_OK) return rc;
   ctx->frame_index += ctx->frame_stride;
@@ -671,6 +674,46 @@ int pcp_finalize_compact(pcp_ctx* ctx, void* points_out, size_t cap, size_t* n_o
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (own) cudaFree(d_pts);
   if (e != cudaSuccess) { ctx->fail("pcp_finalize_compact: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
+  return PCP_OK;
+}
+
+/* generateSegmentMap (cpp:769-816) + the per-frame part of cpp:533-551 for the frame just submitted, on the device: the points that
+ * received a pixel, as 20-byte PointXYZRGBMask records {x, y, z in the camera frame, b, g, r, 255, uint16 mask, 2 bytes of padding}
+ * in the map's order; mask == 255 paints the point red.  The frame must have been submitted alone (pcp_submit_frame[_device]) with a
+ * mask and with its pixel indices kept (pcp_frame_out.pixel_index, or flags & PCP_OUT_PIXELS_ON_DEVICE), and no frame after it.
+ * `*n_out` receives the number of records; at most `cap` are written (records_out = NULL: only count). */
+int pcp_frame_mask_cloud(pcp_ctx* ctx, void* records_out, size_t cap, size_t* n_out) {
+  if (!ctx || !n_out) return PCP_EINVAL;
+  CU(cudaSetDevice(ctx->device));
+  *n_out = 0;
+  if (!ctx->d_cloud || !ctx->pix_valid || !ctx->d_pix || !ctx->last_mask || !ctx->last_bgr) {
+    ctx->fail("pcp_frame_mask_cloud: the last frame was not a single frame with a mask and kept pixel indices");
+    return PCP_EINVAL;
+  }
+  const size_t n = ctx->n;
+  if (n == 0) return PCP_OK;
+  CU(ctx->join());
+  if (!ctx->d_vis_bits) CU(cudaMalloc(&ctx->d_vis_bits, sizeof(uint32_t) * ((n + 31) / 32)));
+  if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n));
+  if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)n)));
+  launch_pixel_bits(ctx->d_pix, (uint32_t)n, ctx->d_vis_bits, ctx->stream);
+  launch_compact_bits(ctx->d_vis_bits, (uint32_t)n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
+  uint32_t total = 0;
+  CU(cudaMemcpyAsync(&total, ctx->d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->launches += 4;
+  *n_out = total;
+  const uint32_t m = (uint32_t)(total < cap ? total : cap);
+  if (!records_out || m == 0) return PCP_OK;
+  uint32_t* d_rec = nullptr;
+  CU(cudaMalloc(&d_rec, (size_t)m * 20));
+  launch_gather_mask_cloud(ctx->d_idx, m, ctx->d_cloud, ctx->d_perm ? ctx->d_inv : nullptr, ctx->d_pix, ctx->last_bgr, ctx->last_pitch, ctx->last_mask,
+                           ctx->last_mask_pitch, ctx->prm.image_width, ctx->last_w2c, d_rec, ctx->stream);
+  ctx->launches++;
+  cudaError_t e = cudaMemcpyAsync(records_out, d_rec, (size_t)m * 20, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_rec);
+  if (e != cudaSuccess) { ctx->fail("pcp_frame_mask_cloud: %s", cudaGetErrorString(e)); return PCP_ECUDA; }
   return PCP_OK;
 }
 

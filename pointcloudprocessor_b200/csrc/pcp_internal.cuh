@@ -126,6 +126,9 @@ void launch_aos_to_soa(const uint8_t* d_aos, size_t n, size_t stride, size_t iof
 void launch_finalize_sum(const uint4* acc, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, int fixed88, cudaStream_t s);
 void launch_pack_sum(const uint4* acc, uint32_t j0, uint32_t j1, uint2* packed, int fixed88, cudaStream_t s);
 void launch_unpack_colours(const uint2* packed, const uint32_t* inv, uint32_t n, uint8_t* rgb, uint32_t* count, cudaStream_t s);
+void launch_pixel_bits(const int32_t* pix, uint32_t n, uint32_t* bits, cudaStream_t s);
+void launch_gather_mask_cloud(const int32_t* idx, uint32_t m, const float4* cloud, const uint32_t* inv, const int32_t* pix, const uint8_t* bgr,
+                              size_t pitch, const uint8_t* mask, size_t mask_pitch, int W, const Xf34& w2c, uint32_t* out, cudaStream_t s);
 void launch_finalize_top(const float* score, const uint32_t* rgbf, const uint32_t* frame, const uint32_t* perm, uint32_t n, int top_m,
                          uint8_t* rgb, uint32_t* count, cudaStream_t s);
 // generateColorMap's 8-bit HSV round trip (pcp_image.cu); src and dst may alias

@@ -1679,6 +1679,48 @@ __global__ void gather_coloured_kernel(const int32_t* __restrict__ idx, uint32_t
     out[k] = make_uint4(__float_as_uint(p.x), __float_as_uint(p.y), __float_as_uint(p.z), b | (g << 8) | (r << 16) | (255u << 24));
   }
 }
+// generateSegmentMap (cpp:769-816) on the device: bit i = point i received a pixel in the last frame; then, for the compacted indices,
+// the PointXYZRGBMask record {camera-frame position (pcl::transformPointCloud, cpp:521), the image's b g r, 255, the mask value; mask
+// 255 paints the point red (cpp:806-811)} of 20 bytes, in the map's point order.
+__global__ void pixel_bits_kernel(const int32_t* __restrict__ pix, uint32_t n, uint32_t* __restrict__ bits) {
+  const uint32_t words = (n + 31) / 32;
+  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < words * 32; base += gridDim.x * blockDim.x) {
+    const uint32_t i = base + (threadIdx.x & 31u);
+    const unsigned int m = __ballot_sync(0xffffffffu, i < n && pix[i] >= 0);
+    if ((threadIdx.x & 31u) == 0) bits[base >> 5] = m;
+  }
+}
+__global__ void gather_mask_cloud_kernel(const int32_t* __restrict__ idx, uint32_t m, const float4* __restrict__ cloud, const uint32_t* __restrict__ inv,
+                                         const int32_t* __restrict__ pix, const uint8_t* __restrict__ bgr, size_t pitch,
+                                         const uint8_t* __restrict__ mask, size_t mask_pitch, int W, const Xf34 w2c, uint32_t* __restrict__ out) {
+  for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < m; k += gridDim.x * blockDim.x) {
+    const uint32_t i = (uint32_t)idx[k];
+    const float4 p = cloud[inv ? inv[i] : i];  // the device copy of the cloud is in sorted order
+    float x, y, z;
+    transform_point(w2c, p.x, p.y, p.z, x, y, z);
+    const int q = pix[i], py = q / W, px = q - py * W;
+    const uint8_t* c = bgr + (size_t)py * pitch + 3 * (size_t)px;
+    uint32_t b = c[0], g = c[1], r = c[2];
+    const uint32_t mk = mask[(size_t)py * mask_pitch + (size_t)px];
+    if (mk == 255u) { r = 255u; g = 0u; b = 0u; }
+    uint32_t* o = out + 5 * (size_t)k;
+    o[0] = __float_as_uint(x); o[1] = __float_as_uint(y); o[2] = __float_as_uint(z);
+    o[3] = b | (g << 8) | (r << 16) | (255u << 24);
+    o[4] = mk;  // uint16 mask + two bytes of padding
+  }
+}
+void launch_pixel_bits(const int32_t* pix, uint32_t n, uint32_t* bits, cudaStream_t s) {
+  if (n == 0) return;
+  const uint32_t threads = ((n + 31) / 32) * 32;
+  const int grid = (threads + 255) / 256 < 148 * 16 ? (threads + 255) / 256 : 148 * 16;
+  pixel_bits_kernel<<<grid, 256, 0, s>>>(pix, n, bits);
+}
+void launch_gather_mask_cloud(const int32_t* idx, uint32_t m, const float4* cloud, const uint32_t* inv, const int32_t* pix, const uint8_t* bgr,
+                              size_t pitch, const uint8_t* mask, size_t mask_pitch, int W, const Xf34& w2c, uint32_t* out, cudaStream_t s) {
+  if (m == 0) return;
+  const int grid = (m + 255) / 256 < 148 * 8 ? (m + 255) / 256 : 148 * 8;
+  gather_mask_cloud_kernel<<<grid, 256, 0, s>>>(idx, m, cloud, inv, pix, bgr, pitch, mask, mask_pitch, W, w2c, out);
+}
 void launch_coloured_bits(const uint8_t* rgb, uint32_t n, uint32_t* bits, cudaStream_t s) {
   if (n == 0) return;
   const uint32_t words = (n + 31) / 32;

@@ -179,7 +179,7 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
   prm.cull_height = A.cull_height > 0 ? A.cull_height : 3000;
   prm.accum_mode = PCP_ACCUM_TOP5;                            // smoothColors, cpp:604-631
   prm.sample_mode = A.sample_mode;
-  prm.hsv_adjust = masks_on ? 0 : 1;  // with masks the host needs the adjusted pixels too (per-frame mask clouds): adjusted up front
+  prm.hsv_adjust = 1;  // generateColorMap's HSV round trip runs on the uploaded image; the per-frame mask clouds are built on the device from it
   CtxGuard G;
   {
     const int rc = pcp_create(&G.ctx, A.device, &cam, &prm);
@@ -269,9 +269,8 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
   // ---- pcdColorizationAndSmooth (cpp:474-602) ---------------------------------------------------------------------------
   const double t_col = now_s();
   const int W = prm.image_width, H = prm.image_height;
-  std::vector<int32_t> pix;
-  if (masks_on) pix.resize(N);
   std::vector<io::XYZRGBMask> world_mask_cloud, frame_mask_cloud;
+  static_assert(sizeof(io::XYZRGBMask) == 20, "pcp_frame_mask_cloud writes 20-byte records");
   // pinned staging for the images (two buffers: the upload of one frame overlaps the decode of the next)
   uint8_t* h_img[2] = {nullptr, nullptr};
   uint8_t* h_msk[2] = {nullptr, nullptr};
@@ -292,9 +291,6 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
     std::memcpy(h_img[sb], img.data.data(), (size_t)W * H * 3);
     bool have_mask = false;
     if (masks_on) {
-      // the host needs the adjusted colours for the per-frame mask cloud: run the device round trip on the staging buffer first
-      check(ctx, pcp_hsv_roundtrip(ctx, h_img[sb], (size_t)W * 3, h_img[sb], (size_t)W * 3, W, H, prm.saturation_scale, prm.brightness_scale),
-            "pcp_hsv_roundtrip");
       HostImage m;
       why.clear();
       if (load_image(kf->mask_path, true, m, why)) {
@@ -313,26 +309,20 @@ static void run_process(const pcp_process_args& A, pcp_process_stats& S) {
     }
     pcp_frame_out fo;
     std::memset(&fo, 0, sizeof(fo));
-    fo.flags = PCP_OUT_SKIP_CANDIDATES;
-    fo.pixel_index = have_mask ? pix.data() : nullptr;
+    fo.flags = PCP_OUT_SKIP_CANDIDATES | PCP_OUT_PIXELS_ON_DEVICE;  // the pixel indices stay on the device for pcp_frame_mask_cloud
     check(ctx, pcp_submit_frame(ctx, kf->pose, T_opt, h_img[sb], (size_t)W * 3, have_mask ? h_msk[sb] : nullptr, (size_t)W,
                                 have_mask ? &fo : nullptr),
           "pcp_submit_frame");
     if (!have_mask) continue;
-    // generateSegmentMap (cpp:769-816) for this keyframe + the concatenated world cloud (cpp:533-551)
+    // generateSegmentMap (cpp:769-816) for this keyframe, gathered on the device: only the points that received a pixel come back,
+    // as PointXYZRGBMask records in the camera frame (cloudInCameraPose, cpp:521), in the map's order
     host::M4f w2c, c2w;
     host::pose_matrices(kf->pose, T_opt, w2c, c2w);
-    frame_mask_cloud.clear();
-    for (size_t i = 0; i < N; i++) {
-      const int32_t p = pix[i];
-      if (p < 0) continue;
-      io::XYZRGBMask q;
-      xform(w2c, cloud[i].x, cloud[i].y, cloud[i].z, q.x, q.y, q.z);  // cloudInCameraPose (cpp:521)
-      const uint8_t* px = h_img[sb] + (size_t)p * 3;
-      q.b = px[0]; q.g = px[1]; q.r = px[2]; q.a = 255;               // cpp:760-762, :799-801
-      q.mask = h_msk[sb][p];                                          // cpp:804
-      if (q.mask == 255) { q.r = 255; q.g = 0; q.b = 0; }             // cpp:806-811
-      frame_mask_cloud.push_back(q);
+    {
+      size_t m = 0;
+      check(ctx, pcp_frame_mask_cloud(ctx, nullptr, 0, &m), "pcp_frame_mask_cloud");
+      frame_mask_cloud.resize(m);
+      if (m) check(ctx, pcp_frame_mask_cloud(ctx, frame_mask_cloud.data(), m, &m), "pcp_frame_mask_cloud");
     }
     S.n_mask_points += (int64_t)frame_mask_cloud.size();
     const double tw = now_s();

@@ -232,6 +232,50 @@ def test_frames_per_launch_invariant(oracle, built_lib, flight, group):
     assert acc_o[:, 3].sum() > 0 and mh_o.sum() > 0
 
 
+@pytest.mark.parametrize("n", [50_000, 31])
+def test_frame_mask_cloud_on_device(oracle, built_lib, n):
+    """pcp_frame_mask_cloud (generateSegmentMap, cpp:769-816, gathered on the device) against the same records built from the frame's
+    pixel indices with the oracle's transform: positions bit-exact, colours, mask values, red paint for mask 255, the map's order;
+    with the pixel indices copied out and with PCP_OUT_PIXELS_ON_DEVICE; and the calls that must be refused."""
+    from pointcloudprocessor_b200 import api
+    W, H = 320, 240
+    sc = make_scene(n, 3, W, H, masks=True)
+    cloud = sc["cloud"]
+    cam = api.create_camera("pinhole", sc["intr"], sc["dist"])
+    with api.Colorizer(cam, api.default_params(image_size=(W, H))) as gc:
+        gc.set_cloud(cloud)
+        with pytest.raises(api.PcpError):
+            gc.frame_mask_cloud()                                     # no frame yet
+        for i, pose in enumerate(sc["poses"]):
+            img, msk = sc["images"][i], sc["masks"][i].copy()
+            msk[::3, ::5] = 255                                       # some pixels of the class that is painted red
+            r = gc.submit_frame(pose, img, mask=msk, want_pix=True)
+            got = gc.frame_mask_cloud()
+            w2c, _ = oracle.pose_matrices(pose)
+            sel = np.nonzero(r["pix"] >= 0)[0]
+            pix = r["pix"][sel]
+            assert len(got) == len(sel) == r["n_colored"]
+            want_xyz = oracle.transform(cloud[sel, :3].copy(), w2c)
+            assert np.array_equal(np.stack([got["x"], got["y"], got["z"]], axis=1).view(np.uint32), want_xyz.view(np.uint32))
+            bgr = img.reshape(-1, 3)[pix]
+            mv = msk.reshape(-1)[pix]
+            red = mv == 255
+            assert np.array_equal(got["mask"], mv.astype(np.uint16)) and (got["a"] == 255).all() and (got["pad"] == 0).all()
+            assert np.array_equal(got["r"], np.where(red, 255, bgr[:, 2])) and np.array_equal(got["g"], np.where(red, 0, bgr[:, 1]))
+            assert np.array_equal(got["b"], np.where(red, 0, bgr[:, 0]))
+            if n > 1000:
+                assert red.any() and (~red).any()
+            # the same frame again with the indices left on the device: same records
+            gc.submit_frame(pose, img, mask=msk, keep_pix_on_device=True)
+            assert np.array_equal(gc.frame_mask_cloud(), got)
+        gc.submit_frame(sc["poses"][0], sc["images"][0], mask=sc["masks"][0])          # pixel indices not kept
+        with pytest.raises(api.PcpError):
+            gc.frame_mask_cloud()
+        gc.submit_frame(sc["poses"][0], sc["images"][0], want_pix=True)                 # no mask
+        with pytest.raises(api.PcpError):
+            gc.frame_mask_cloud()
+
+
 def _big_shape_parity(oracle, n, f, W, H, n_images, flight):
     """Accumulators of f frames over an n-point cloud against the oracle (all host threads), frames submitted without per-frame
     outputs so that `flight` of them are in flight; images are cycled (the kernels see the same work)."""
