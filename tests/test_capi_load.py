@@ -35,6 +35,24 @@ def test_default_params_match_reference(built_lib):
     assert p.top_m == 5 and p.enable_depth_buffer_culling == 1
 
 
+def test_cloud_slices_partition_the_map(built_lib):
+    """pcp_cloud_slice (host arithmetic of pcp_set_cloud_sharded): the ranks' slices are disjoint, in rank order, cover [0, n), have the
+    same length except for the last non-empty one, and bad arguments are refused."""
+    from pointcloudprocessor_b200 import api
+    for n in (0, 1, 7, 64, 60_001, 100_000_000, 4_294_967_279):
+        for world in (1, 2, 3, 4, 8, 64):
+            per = -(-n // world)
+            nxt = 0
+            for r in range(world):
+                first, count = api.cloud_slice(n, r, world)
+                assert first == min(r * per, n) == nxt and count == min(per, n - first)
+                nxt = first + count
+            assert nxt == n
+    for bad in ((10, -1, 4), (10, 4, 4), (10, 0, 0)):
+        with pytest.raises(api.PcpError):
+            api.cloud_slice(*bad)
+
+
 def test_no_cpu_fallback(built_lib):
     import torch
     if torch.cuda.is_available():
