@@ -153,6 +153,7 @@ void pcp_destroy(pcp_ctx* ctx) {
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   if (ctx->d_total) cudaFree(ctx->d_total);
+  if (ctx->d_tmp) cudaFree(ctx->d_tmp);
   for (cudaEvent_t e : ctx->prof_events) if (e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);

@@ -47,6 +47,8 @@ struct pcp_ctx {
   size_t out_points = 0;
   static constexpr size_t kAccPad = 64;  // d_acc holds N + kAccPad entries: the reduce-scatter of pcp_exchange_finalize works on G equal slices
   uint4* d_acc = nullptr;         // N x 16 B  {sum_r,sum_g,sum_b,count}
+  uint8_t* d_tmp = nullptr;       // staging for pcp_nid_create (image plane + bin table + non-float4 point records), kept until pcp_destroy
+  size_t tmp_bytes = 0;
   uint2* d_xchg = nullptr;        // pcp_exchange_finalize: packed {rgb, count} of every point in sorted order (all-gather buffer)
   size_t xchg_points = 0;
   cudaEvent_t xchg_ev[5] = {};    // phase timing of pcp_exchange_finalize while profiling is enabled

@@ -465,14 +465,27 @@ static int nid_create_impl(pcp_ctx* ctx, const void* points, size_t m, size_t st
   nid->ctx = ctx; nid->m = m; nid->W = width; nid->H = height; nid->bins = bins;
   cudaStream_t s = ctx->stream;
   const size_t npix = (size_t)width * height;
-  double* d_img = nullptr;
-  uint8_t* d_aos = nullptr;
-  uint8_t* d_u8 = nullptr;  // the 8-bit plane (W x H, packed) followed by the 256-entry bin table
-  auto cleanup = [&]() { if (d_img) cudaFree(d_img); if (d_aos) cudaFree(d_aos); if (d_u8) cudaFree(d_u8); };
+  // One persistent allocation per cost (points, then the binned image) and NO temporary ones: the staging buffers (8-bit or double
+  // plane, bin table, non-float4 point records) live in a context-owned scratch that is kept until pcp_destroy.  cudaFree synchronises
+  // the device: three of them per cost were most of the 9.6 ms that setting up 20 keyframes took.
+  const size_t pts_bytes = (sizeof(float4) * (m ? m : 1) + 255) & ~(size_t)255;
+  const size_t img_bytes = image_u8 ? ((npix + 256 + 255) & ~(size_t)255) : ((npix * sizeof(double) + 255) & ~(size_t)255);
+  const bool aos = m && !(stride_bytes == 16 && intensity_offset == 12);
+  const size_t need = img_bytes + (aos ? m * stride_bytes : 0);
   uint8_t lut[256];
   cudaError_t e;
-  if ((e = cudaMalloc(&nid->d_pts, sizeof(float4) * (m ? m : 1))) != cudaSuccess) goto fail;
-  if ((e = cudaMalloc(&nid->d_binimg, npix)) != cudaSuccess) goto fail;
+  if (ctx->tmp_bytes < need) {
+    if (ctx->d_tmp) { if ((e = cudaStreamSynchronize(s)) != cudaSuccess) goto fail; cudaFree(ctx->d_tmp); ctx->d_tmp = nullptr; ctx->tmp_bytes = 0; }
+    const size_t want = need + need / 4;
+    if ((e = cudaMalloc(&ctx->d_tmp, want)) != cudaSuccess) goto fail;
+    ctx->tmp_bytes = want;
+  }
+  {
+    uint8_t* block = nullptr;
+    if ((e = cudaMalloc(&block, pts_bytes + npix)) != cudaSuccess) goto fail;
+    nid->d_pts = reinterpret_cast<float4*>(block);
+    nid->d_binimg = block + pts_bytes;
+  }
   if (image_u8) {
     // byte -> bin, evaluated on the host in the operations of the double path: (double)v * (1.0 / 255.0), then * bins, truncation, clamp
     for (int v = 0; v < 256; v++) {
@@ -481,33 +494,31 @@ static int nid_create_impl(pcp_ctx* ctx, const void* points, size_t m, size_t st
       b = b < bins - 1 ? b : bins - 1;
       lut[v] = (uint8_t)(b < 0 ? 0 : b);
     }
-    if ((e = cudaMalloc(&d_u8, npix + 256)) != cudaSuccess) goto fail;
+    uint8_t* d_u8 = ctx->d_tmp;  // the 8-bit plane (W x H, packed) followed by the 256-entry bin table
     if ((e = cudaMemcpy2DAsync(d_u8, (size_t)width, image_u8, pitch_u8, (size_t)width, (size_t)height, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
     if ((e = cudaMemcpyAsync(d_u8 + npix, lut, 256, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
     nid_bin_image_u8_kernel<<<ctx->sm_count * 8, 256, 0, s>>>(d_u8, (size_t)width, width, height, d_u8 + npix, nid->d_binimg);
   } else {
-    if ((e = cudaMalloc(&d_img, npix * sizeof(double))) != cudaSuccess) goto fail;
+    double* d_img = reinterpret_cast<double*>(ctx->d_tmp);
     if ((e = cudaMemcpyAsync(d_img, image, npix * sizeof(double), cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
     nid_bin_image_kernel<<<ctx->sm_count * 8, 256, 0, s>>>(d_img, npix, bins, nid->d_binimg);
   }
   ctx->launches++;
   if (m) {
-    if (stride_bytes == 16 && intensity_offset == 12) {
+    if (!aos) {
       if ((e = cudaMemcpyAsync(nid->d_pts, points, sizeof(float4) * m, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
     } else {
-      if ((e = cudaMalloc(&d_aos, m * stride_bytes)) != cudaSuccess) goto fail;
+      uint8_t* d_aos = ctx->d_tmp + img_bytes;
       if ((e = cudaMemcpyAsync(d_aos, points, m * stride_bytes, cudaMemcpyHostToDevice, s)) != cudaSuccess) goto fail;
       launch_aos_to_soa(d_aos, m, stride_bytes, intensity_offset, nid->d_pts, s);
       ctx->launches++;
     }
   }
-  if ((e = cudaStreamSynchronize(s)) != cudaSuccess) goto fail;
-  cleanup();
+  if ((e = cudaStreamSynchronize(s)) != cudaSuccess) goto fail;  // the caller's host buffers (and `lut`) may go away; the scratch is free again
   *out = nid;
   return PCP_OK;
 fail:
   ctx->fail("pcp_nid_create: %s", cudaGetErrorString(e));
-  cleanup();
   pcp_nid_destroy(nid);
   return PCP_ECUDA;
 }
@@ -527,8 +538,7 @@ int pcp_nid_create_u8(pcp_ctx* ctx, const void* points, size_t m, size_t stride_
 void pcp_nid_destroy(pcp_nid* nid) {
   if (!nid) return;
   if (nid->ctx) cudaSetDevice(nid->ctx->device);
-  if (nid->d_pts) cudaFree(nid->d_pts);
-  if (nid->d_binimg) cudaFree(nid->d_binimg);
+  if (nid->d_pts) cudaFree(nid->d_pts);  // one block: the points, then the binned image
   if (nid->d_se3) cudaFree(nid->d_se3);
   if (nid->d_hist) cudaFree(nid->d_hist);
   if (nid->d_out) cudaFree(nid->d_out);
