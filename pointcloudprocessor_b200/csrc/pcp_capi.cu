@@ -329,6 +329,7 @@ static int set_cloud_impl(pcp_ctx* ctx, const void* points, size_t n, size_t str
   const bool reuse = ctx->d_cloud && ctx->n == n && n > 0;  // same-size cloud: keep every allocation, only re-upload
   const size_t n1 = n ? n : 1;
   CU(ctx->join());  // frames in flight still read the cloud
+  ctx->pix_valid = false;  // the kept pixel indices belong to a frame over the previous cloud
   if (!reuse) {
     CU(ctx->drain());
     ctx->free_cloud();
@@ -408,6 +409,7 @@ int pcp_set_cloud_device(pcp_ctx* ctx, const void* d_xyzi, size_t n) {
   CU(cudaSetDevice(ctx->device));
   CU(ctx->drain());
   ctx->free_cloud();
+  ctx->pix_valid = false;
   CU(cudaMalloc(&ctx->d_cloud, sizeof(float4) * ((n ? n : 1) + pcp_ctx::kAccPad)));
   if (n) CU(cudaMemcpyAsync(ctx->d_cloud, d_xyzi, sizeof(float4) * n, cudaMemcpyDeviceToDevice, ctx->stream));
   choose_flight(ctx, n);

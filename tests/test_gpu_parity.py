@@ -274,6 +274,11 @@ def test_frame_mask_cloud_on_device(oracle, built_lib, n):
         gc.submit_frame(sc["poses"][0], sc["images"][0], want_pix=True)                 # no mask
         with pytest.raises(api.PcpError):
             gc.frame_mask_cloud()
+        gc.submit_frame(sc["poses"][0], sc["images"][0], mask=sc["masks"][0], want_pix=True)
+        assert len(gc.frame_mask_cloud()) > 0 or n < 1000
+        gc.set_cloud(cloud)                                                             # a new map: the kept indices are stale
+        with pytest.raises(api.PcpError):
+            gc.frame_mask_cloud()
 
 
 def _big_shape_parity(oracle, n, f, W, H, n_images, flight):
