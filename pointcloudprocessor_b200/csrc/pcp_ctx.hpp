@@ -94,6 +94,8 @@ struct pcp_ctx {
   const uint8_t* last_mask = nullptr; size_t last_mask_pitch = 0;
   pcp::Xf34 last_w2c = {};
   bool pix_valid = false;
+  bool mask_idx_valid = false;    // d_idx / mask_idx_total hold the compacted indices of that frame (a count-only call came first)
+  uint32_t mask_idx_total = 0;
   cudaEvent_t last_done = nullptr;  // ev_done of the last submitted frame (null before the first)
   unsigned long long* d_zgrid = nullptr;       // kMaxFlight x Wc*Hc packed (fl32 depth, point index) keys: grid 0 of every slot
   unsigned long long* d_zprev = nullptr;       // kMaxFlight x Wc*Hc: grid 1 of every slot (frames of a slot alternate; the other grid

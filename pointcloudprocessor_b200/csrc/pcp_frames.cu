@@ -223,6 +223,7 @@ int run_frame(pcp_ctx* ctx, const FrameParams& fp, const uint8_t* d_bgr, size_t 
   ctx->last_slot = si;
   ctx->last_counters = counters_index;
   ctx->pix_valid = want_pix && accumulate;
+  ctx->mask_idx_valid = false;
   ctx->last_bgr = d_bgr; ctx->last_pitch = pitch; ctx->last_mask = d_mask; ctx->last_mask_pitch = mask_pitch; ctx->last_w2c = fp.w2c;
   slot.owner = si;
   ctx->frames_run++;
@@ -269,6 +270,7 @@ int run_group(pcp_ctx* ctx, int k, const FrameParams* fps, const uint8_t* const*
   ctx->last_slot = base + k - 1;
   ctx->last_counters = counters_index;
   ctx->pix_valid = false;
+  ctx->mask_idx_valid = false;
   ctx->frames_run += (uint64_t)k;
   ctx->launches += 3;
   CU(cudaGetLastError());
@@ -475,6 +477,7 @@ static int cull_common(pcp_ctx* ctx, const FrameParams& fp, int32_t* idx_out, si
   const size_t n1 = ctx->n ? ctx->n : 1;
   if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n1));
   if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)ctx->n)));
+  ctx->mask_idx_valid = false;  // d_idx is shared with pcp_frame_mask_cloud
   launch_compact_bits(ctx->d_vis_bits, (uint32_t)ctx->n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
   ctx->launches += 3;
   uint32_t total = 0;
@@ -653,6 +656,7 @@ int pcp_finalize_compact(pcp_ctx* ctx, void* points_out, size_t cap, size_t* n_o
   if (!ctx->d_vis_bits) CU(cudaMalloc(&ctx->d_vis_bits, sizeof(uint32_t) * ((n + 31) / 32)));
   if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n));
   if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)n)));
+  ctx->mask_idx_valid = false;  // d_idx is shared with pcp_frame_mask_cloud
   launch_coloured_bits(ctx->d_out_rgb, (uint32_t)n, ctx->d_vis_bits, ctx->stream);
   launch_compact_bits(ctx->d_vis_bits, (uint32_t)n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
   uint32_t total = 0;
@@ -693,15 +697,19 @@ int pcp_frame_mask_cloud(pcp_ctx* ctx, void* records_out, size_t cap, size_t* n_
   const size_t n = ctx->n;
   if (n == 0) return PCP_OK;
   CU(ctx->join());
-  if (!ctx->d_vis_bits) CU(cudaMalloc(&ctx->d_vis_bits, sizeof(uint32_t) * ((n + 31) / 32)));
-  if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n));
-  if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)n)));
-  launch_pixel_bits(ctx->d_pix, (uint32_t)n, ctx->d_vis_bits, ctx->stream);
-  launch_compact_bits(ctx->d_vis_bits, (uint32_t)n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
-  uint32_t total = 0;
-  CU(cudaMemcpyAsync(&total, ctx->d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
-  ctx->launches += 4;
+  uint32_t total = ctx->mask_idx_total;
+  if (!ctx->mask_idx_valid) {  // the usual second call (count first, then the records) finds the indices already compacted
+    if (!ctx->d_vis_bits) CU(cudaMalloc(&ctx->d_vis_bits, sizeof(uint32_t) * ((n + 31) / 32)));
+    if (!ctx->d_idx) CU(cudaMalloc(&ctx->d_idx, sizeof(int32_t) * n));
+    if (!ctx->d_scratch) CU(cudaMalloc(&ctx->d_scratch, sizeof(uint32_t) * compact_scratch_words((uint32_t)n)));
+    launch_pixel_bits(ctx->d_pix, (uint32_t)n, ctx->d_vis_bits, ctx->stream);
+    launch_compact_bits(ctx->d_vis_bits, (uint32_t)n, nullptr, ctx->d_scratch, ctx->d_idx, ctx->d_total, ctx->stream);
+    CU(cudaMemcpyAsync(&total, ctx->d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->launches += 4;
+    ctx->mask_idx_total = total;
+    ctx->mask_idx_valid = true;
+  }
   *n_out = total;
   const uint32_t m = (uint32_t)(total < cap ? total : cap);
   if (!records_out || m == 0) return PCP_OK;

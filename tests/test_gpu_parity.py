@@ -265,9 +265,15 @@ def test_frame_mask_cloud_on_device(oracle, built_lib, n):
             assert np.array_equal(got["b"], np.where(red, 0, bgr[:, 0]))
             if n > 1000:
                 assert red.any() and (~red).any()
-            # the same frame again with the indices left on the device: same records
+            # the same frame again with the indices left on the device: same records; and again after a call that shares its index
+            # scratch (the compacted final cloud)
             gc.submit_frame(pose, img, mask=msk, keep_pix_on_device=True)
             assert np.array_equal(gc.frame_mask_cloud(), got)
+            gc.finalize_compact()                                     # shares the index scratch; not a frame
+            assert np.array_equal(gc.frame_mask_cloud(), got)
+            gc.cull_pose(sc["poses"][(i + 1) % len(sc["poses"])])     # a frame of its own (no colours): the kept indices are gone
+            with pytest.raises(api.PcpError):
+                gc.frame_mask_cloud()
         gc.submit_frame(sc["poses"][0], sc["images"][0], mask=sc["masks"][0])          # pixel indices not kept
         with pytest.raises(api.PcpError):
             gc.frame_mask_cloud()
