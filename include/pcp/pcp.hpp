@@ -135,6 +135,54 @@ class Colorizer {
   }
   void allreduce() { check(pcp_allreduce(ctx_), ctx_, "pcp_allreduce"); }
 
+  // removePointsWithNoColor after smoothColors (hpp:238-252, cpp:604-631) with the compaction on the device: the coloured points
+  // only, as pcl::PointXYZRGB, in the map's order
+  std::vector<PointXYZRGB> coloredCloud() {
+    struct Rec { float x, y, z; uint8_t b, g, r, a; };
+    static_assert(sizeof(Rec) == 16, "pcp_finalize_compact writes 16-byte records");
+    size_t m = 0;
+    check(pcp_finalize_compact(ctx_, nullptr, 0, &m), ctx_, "pcp_finalize_compact");
+    std::vector<Rec> rec(m);
+    if (m) check(pcp_finalize_compact(ctx_, rec.data(), m, &m), ctx_, "pcp_finalize_compact");
+    std::vector<PointXYZRGB> out(m);
+    for (size_t i = 0; i < m; i++) out[i] = PointXYZRGB{rec[i].x, rec[i].y, rec[i].z, 1.0f, rec[i].b, rec[i].g, rec[i].r, rec[i].a, 0.0f, 0.0f, 0.0f};
+    return out;
+  }
+  // generateSegmentMap (cpp:769-816) for the keyframe just added: the points that received a pixel, in the camera frame, with the
+  // image's colour (red where the mask is 255) and the mask value.  Add that keyframe with a mask and `keepPixels(out)`.
+  static void keepPixels(pcp_frame_out& out) { out.flags |= PCP_OUT_PIXELS_ON_DEVICE | PCP_OUT_SKIP_CANDIDATES; }
+  std::vector<PointXYZRGBMask> segmentCloud() {
+    struct Rec { float x, y, z; uint8_t b, g, r, a; uint16_t mask, pad; };
+    static_assert(sizeof(Rec) == 20, "pcp_frame_mask_cloud writes 20-byte records");
+    size_t m = 0;
+    check(pcp_frame_mask_cloud(ctx_, nullptr, 0, &m), ctx_, "pcp_frame_mask_cloud");
+    std::vector<Rec> rec(m);
+    if (m) check(pcp_frame_mask_cloud(ctx_, rec.data(), m, &m), ctx_, "pcp_frame_mask_cloud");
+    std::vector<PointXYZRGBMask> out(m);
+    for (size_t i = 0; i < m; i++)
+      out[i] = PointXYZRGBMask{rec[i].x, rec[i].y, rec[i].z, 1.0f, rec[i].b, rec[i].g, rec[i].r, rec[i].a, rec[i].mask, 0, 0.0f, 0.0f};
+    return out;
+  }
+
+  // ---- several GPUs, one Colorizer per GPU (no counterpart in the reference, which is one process) ------------------------------
+  static void ncclUniqueId(uint8_t id128[128]) {
+    if (pcp_nccl_unique_id(id128) != PCP_OK) throw std::runtime_error("pcp_nccl_unique_id failed");
+  }
+  void ncclInit(const uint8_t id128[128], int rank, int nranks) { check(pcp_nccl_init(ctx_, id128, rank, nranks), ctx_, "pcp_nccl_init"); }
+  // keyframe numbers of this rank's share (global numbers break ties of equal scores as one process would)
+  void setFrameNumbering(int next, int stride) { check(pcp_set_frame_numbering(ctx_, next, stride), ctx_, "pcp_set_frame_numbering"); }
+  // every rank passes the WHOLE map and uploads only its slice of it; the slices are all-gathered over NVLink
+  void setCloudSharded(const std::vector<PointXYZI>& cloud, int rank, int nranks) {
+    size_t first = 0, count = 0;
+    if (pcp_cloud_slice(cloud.size(), rank, nranks, &first, &count) != PCP_OK) throw std::runtime_error("pcp_cloud_slice: bad rank");
+    check(pcp_set_cloud_sharded(ctx_, cloud.data() + first, cloud.size(), sizeof(PointXYZI), offsetof(PointXYZI, intensity)), ctx_, "pcp_set_cloud_sharded");
+  }
+  // smoothColors of the whole job on every rank: reduce-scatter of the sums, finalize of the rank's slice, all-gather
+  void exchangeAndSmoothColors(std::vector<uint8_t>& rgb, std::vector<uint32_t>& count) {
+    rgb.resize(3 * size()); count.resize(size());
+    check(pcp_exchange_finalize(ctx_, rgb.data(), count.data()), ctx_, "pcp_exchange_finalize");
+  }
+
  private:
   pcp_ctx* ctx_ = nullptr;
   pcp_params params_;

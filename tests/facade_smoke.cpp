@@ -35,7 +35,21 @@ int main() {
     const pcp::Isometry3d T = calib.calibrate(pcp::Isometry3d::Identity());
     const pcp_calib_summary& cs = calib.summary();
     if (!(cs.final_cost <= cs.initial_cost) || !(T.m[15] == 1.0)) { std::printf("calibrate: %f -> %f\n", cs.initial_cost, cs.final_cost); return 14; }
-    std::printf("facade ok: kept %zu of %zu, calibrate %d outer / %d evaluations\n", kept.size(), pts.size(), cs.outer_iterations, cs.cost_evaluations);
+    // one keyframe with a mask through the colouring calls: the per-keyframe mask cloud and the compacted final cloud
+    col.setCloud(pts);
+    std::vector<uint8_t> bgr(320 * 240 * 3), msk(320 * 240);
+    for (size_t i = 0; i < msk.size(); i++) { bgr[3 * i] = (uint8_t)(i % 251); bgr[3 * i + 1] = (uint8_t)(i % 241 + 1); bgr[3 * i + 2] = 7; msk[i] = (i % 5 == 0) ? 255 : (uint8_t)(i % 200); }
+    const pcp::Image im{bgr.data(), 320, 240, 3, 320 * 3}, mk{msk.data(), 320, 240, 1, 320};
+    pcp_frame_out fo{};
+    pcp::Colorizer::keepPixels(fo);
+    col.addFrame(pcp::Pose{0, 0, 0, 1, 0, 0, 0}, im, &mk, nullptr, &fo);
+    const auto seg = col.segmentCloud();
+    const auto coloured = col.coloredCloud();
+    if (seg.empty() || seg.size() != (size_t)fo.n_colored || coloured.size() != seg.size()) { std::printf("mask cloud %zu, coloured %zu, frame %lld\n", seg.size(), coloured.size(), (long long)fo.n_colored); return 15; }
+    for (const auto& q : seg)
+      if (q.a != 255 || (q.segmentMask == 255 && !(q.r == 255 && q.g == 0 && q.b == 0))) { std::printf("mask cloud: bad record\n"); return 16; }
+    std::printf("facade ok: kept %zu of %zu, calibrate %d outer / %d evaluations, mask cloud %zu points\n", kept.size(), pts.size(), cs.outer_iterations,
+                cs.cost_evaluations, seg.size());
     return kept.empty() ? 11 : 0;
   } catch (const std::runtime_error& e) {
     std::printf("facade error: %s\n", e.what());
